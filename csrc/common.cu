@@ -1,0 +1,35 @@
+#include "common.h"
+#include <mutex>
+
+char* b200_err_buf() {
+  static thread_local char buf[1024] = {0};
+  return buf;
+}
+
+B200_API const char* b200_last_error() { return b200_err_buf(); }
+
+int b200_num_sms() {
+  static int cached[64] = {0};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+  if (cached[dev] == 0) {
+    int n = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+    cached[dev] = n;
+  }
+  return cached[dev];
+}
+
+B200_API int b200_sm_count() { return b200_num_sms(); }
+
+// Writes > L2-size bytes so the next timed kernel starts from a cold L2
+// (B200_PROFILING.md timing hygiene).
+__global__ void l2_flush_kernel(float4* buf, size_t n4, float v) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x)
+    buf[i] = make_float4(v, v, v, v);
+}
+B200_API int b200_l2_flush(void* buf, size_t bytes, void* stream) {
+  l2_flush_kernel<<<b200_num_sms() * 8, 256, 0, (cudaStream_t)stream>>>((float4*)buf, bytes / 16, 1.0f);
+  B200_LAUNCH_CHECK();
+  return 0;
+}

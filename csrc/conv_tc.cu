@@ -1,0 +1,535 @@
+// tcgen05 / TMEM / TMA implicit-GEMM kernels for the 5x5, pad-2, stride-1 conv2
+// of the reference ConvNet (mnist_distributed.py:33-37: Conv2d(16, 32, 5, 1, 2))
+// at the 1500x1500 post-pool resolution: forward (K6), data gradient (K12a)
+// and weight gradient (K12b) of SURVEY.md 2.5.  The reference runs these as
+// cuDNN TF32 NCHW library kernels; here they are written for sm_100a.
+//
+// Design (B200-first, not an im2col GEMM):
+//  * Activations are bf16 NHWC.  A pixel's channel vector is split into 16-byte
+//    "planes" of 8 channels, and TMA (5-D tensor map {8ch, plane, W, H, B})
+//    drops one image row segment per plane into shared memory at a 16-byte
+//    pixel pitch.  With the NO-SWIZZLE K-major UMMA layout (row r of the A
+//    tile at r*16 B, the two 8-channel K-chunks one plane apart) a 128-pixel A
+//    operand for filter tap (dy,dx) is just "row slot dy, start + dx*16 B":
+//    the 5x5 halo is re-used straight from shared memory, every input row is
+//    fetched from L2 once per strip (a ROLLING ring of row slots), and the
+//    conv zero padding is TMA out-of-bounds fill.  No im2col tile is ever
+//    materialised, in HBM or in smem.
+//  * One CTA per SM, persistent over (image, 128-px column strip, row segment)
+//    work items.  Warp 0 = TMA producer, warp 1 = single-thread tcgen05.mma
+//    issuer (25 taps x CIN/16 MMAs of M=128,N=COUT,K=16 per output row),
+//    warps 2-5 = epilogue: tcgen05.ld the fp32 accumulator row out of TMEM
+//    (4-deep TMEM ring so MMA of row y+1..y+3 overlaps the epilogue of row y),
+//    add bias, round to bf16, store NHWC and - for the forward - accumulate the
+//    BatchNorm batch statistics (sum, sum of squares per channel) in registers
+//    (K4/K7 fused into the producing kernel).
+//  * wgrad contracts over PIXELS, so both operands are MN-major straight out of
+//    the same planar row slots: A[m=(dx,ci8), k=pixel] starts at "slot dy,
+//    plane, pixel k0" with a 16-byte M-stride (the dx shift IS the next core
+//    matrix), B[n=co, k=pixel] is the dx2 row.  The ten (dy, plane) 64x32 fp32
+//    accumulators live in TMEM for the whole kernel and are written once.
+#include "common.h"
+#include "ptx.cuh"
+#include <cuda.h>
+#include <cstdint>
+#include <mutex>
+
+namespace {
+
+using namespace b2;
+
+constexpr int kBM = 128;          // output pixels per row tile (UMMA M)
+constexpr int kPW = 136;          // pixels per smem plane row: 128 + 4 halo, padded to 8
+constexpr int kPlaneBytes = kPW * 16;
+constexpr int kTaps = 25;
+constexpr int kNumTmemStages = 4;
+constexpr int kThreads = 192;     // warp0 TMA, warp1 MMA, warps2-5 epilogue
+
+template <int CIN, int COUT>
+struct ConvCfg {
+  static constexpr int kPlanes = CIN / 8;
+  static constexpr int kSlotBytes = kPlanes * kPlaneBytes;
+  static constexpr int kSlots = 12;
+  static constexpr int kKSteps = CIN / 16;
+  static constexpr int kWTapBytes = kKSteps * 2 * COUT * 16;
+  static constexpr int kWBytes = kTaps * kWTapBytes;
+  static constexpr int kTmemCols = (kNumTmemStages * COUT) < 32 ? 32 : (kNumTmemStages * COUT);
+  static constexpr int kSmemBytes = kWBytes + kSlots * kSlotBytes + 2048 + 128;
+  static_assert(kWBytes % 128 == 0 && kSlotBytes % 128 == 0, "TMA destinations must stay 128-B aligned");
+  static_assert((kTmemCols & (kTmemCols - 1)) == 0, "TMEM allocation must be a power of two");
+};
+
+struct ConvGeom {
+  int B, H, W;
+  int nstrips;    // ceil(W / 128)
+  int rseg;       // output rows per work item
+  int nseg;       // ceil(H / rseg)
+  int nitems;
+};
+
+// ============================================================ fwd / dgrad ===
+// out[b,y,x,n] = bias[n] + sum_{dy,dx,k} act[b,y+dy-2,x+dx-2,k] * wsrc(n,k,dy,dx)
+//   TRANSPOSED=false: wsrc = w[n][k][dy][dx]            (forward,  w is [COUT][CIN][5][5])
+//   TRANSPOSED=true : wsrc = w[k][n][4-dy][4-dx]        (dgrad,    w is [CIN ][COUT][5][5])
+template <int CIN, int COUT, bool TRANSPOSED, bool STATS>
+__global__ void __launch_bounds__(kThreads, 1)
+conv5x5_tc_kernel(const __grid_constant__ CUtensorMap tm_act, const float* __restrict__ w,
+                  const float* __restrict__ bias, __nv_bfloat16* __restrict__ out,
+                  float* __restrict__ partials, ConvGeom g) {
+  using Cfg = ConvCfg<CIN, COUT>;
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((128u - (smem_u32(smem_raw) & 127u)) & 127u);   // TMA destinations: 128-B aligned
+  uint8_t* s_w = smem;
+  uint8_t* s_slots = smem + Cfg::kWBytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_slots + Cfg::kSlots * Cfg::kSlotBytes);
+  uint64_t* full = bars;                       // [kSlots]   TMA -> MMA
+  uint64_t* empty = bars + Cfg::kSlots;        // [kSlots]   MMA -> TMA
+  uint64_t* tfull = empty + Cfg::kSlots;       // [4]        MMA -> epilogue
+  uint64_t* tempty = tfull + kNumTmemStages;   // [4]        epilogue -> MMA
+  uint32_t* s_tmem = reinterpret_cast<uint32_t*>(tempty + kNumTmemStages);
+  float* s_bias = reinterpret_cast<float*>(s_tmem + 4);           // [COUT]
+  float* s_stat = s_bias + COUT;                                  // [4][2*COUT]
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  // ---- prologue: pack weights (fp32 -> bf16, UMMA K-major no-swizzle B tiles)
+  // byte(tap, kk, c, n, e) = ((tap*KSTEPS + kk)*2 + c)*COUT*16 + n*16 + e*2,  k = kk*16 + c*8 + e
+  for (int i = threadIdx.x; i < kTaps * CIN * COUT; i += kThreads) {
+    const int e = i & 7;
+    int r = i >> 3;
+    const int n = r % COUT; r /= COUT;
+    const int c = r & 1; r >>= 1;
+    const int kk = r % Cfg::kKSteps;
+    const int tap = r / Cfg::kKSteps;
+    const int k = kk * 16 + c * 8 + e;
+    const float v = TRANSPOSED ? w[((size_t)k * COUT + n) * kTaps + (kTaps - 1 - tap)]
+                               : w[((size_t)n * CIN + k) * kTaps + tap];
+    reinterpret_cast<__nv_bfloat16*>(s_w)[i] = __float2bfloat16_rn(v);
+  }
+  if (threadIdx.x < COUT) s_bias[threadIdx.x] = bias ? bias[threadIdx.x] : 0.f;
+  fence_proxy_async_smem();
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < Cfg::kSlots; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+    for (int i = 0; i < kNumTmemStages; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], 128); }
+    mbar_fence_init();
+    tma_prefetch_desc(&tm_act);
+  }
+  if (warp == 1) tmem_alloc<Cfg::kTmemCols>(s_tmem);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *s_tmem;
+
+  if (warp == 0) {
+    // ===================== TMA producer (one lane) =====================
+    if (lane == 0) {
+      uint32_t gcount = 0;
+      for (int item = blockIdx.x; item < g.nitems; item += gridDim.x) {
+        const int seg = item % g.nseg;
+        const int strip = (item / g.nseg) % g.nstrips;
+        const int b = item / (g.nseg * g.nstrips);
+        const int y0 = seg * g.rseg;
+        const int rows = min(g.rseg, g.H - y0);
+        const int x0 = strip * kBM;
+        for (int i = 0; i < rows + 4; ++i, ++gcount) {
+          const uint32_t slot = gcount % Cfg::kSlots, use = gcount / Cfg::kSlots;
+          mbar_wait(&empty[slot], (use & 1) ^ 1);
+          mbar_expect_tx(&full[slot], Cfg::kSlotBytes);
+          uint8_t* dst = s_slots + slot * Cfg::kSlotBytes;
+#pragma unroll
+          for (int p = 0; p < Cfg::kPlanes; ++p)
+            tma_load_5d(dst + p * kPlaneBytes, &tm_act, &full[slot], 0, p, x0 - 2, y0 - 2 + i, b);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer (one lane) =====================
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(kBM, COUT, 0, 0);
+      const uint32_t slots_addr = smem_u32(s_slots);
+      // descriptor templates: A: LBO = plane stride, SBO = 128 B;  B: LBO = COUT*16, SBO = 128 B
+      const uint64_t a_tmpl = smem_desc_noswz(0, kPlaneBytes, 128);
+      const uint64_t b_tmpl = smem_desc_noswz(smem_u32(s_w), COUT * 16, 128);
+      uint32_t gbase = 0, q = 0;
+      for (int item = blockIdx.x; item < g.nitems; item += gridDim.x) {
+        const int seg = item % g.nseg;
+        const int y0 = seg * g.rseg;
+        const int rows = min(g.rseg, g.H - y0);
+        for (int j = 0; j < rows; ++j, ++q) {
+          // input rows j..j+4 (local) must have landed; rows arrive in order
+          for (int i = (j == 0 ? 0 : 4); i < 5; ++i) {
+            const uint32_t gc = gbase + j + i;
+            mbar_wait(&full[gc % Cfg::kSlots], (gc / Cfg::kSlots) & 1);
+          }
+          const uint32_t stage = q % kNumTmemStages, use = q / kNumTmemStages;
+          mbar_wait(&tempty[stage], (use & 1) ^ 1);
+          tc_fence_after();
+          const uint32_t d_tmem = tmem_base + stage * COUT;
+          uint32_t accum = 0;
+#pragma unroll
+          for (int dy = 0; dy < 5; ++dy) {
+            const uint32_t slot = (gbase + j + dy) % Cfg::kSlots;
+            const uint32_t row_addr = slots_addr + slot * Cfg::kSlotBytes;
+#pragma unroll
+            for (int dx = 0; dx < 5; ++dx) {
+#pragma unroll
+              for (int kk = 0; kk < Cfg::kKSteps; ++kk) {
+                const uint32_t a_addr = row_addr + (2 * kk) * kPlaneBytes + dx * 16;
+                const uint64_t a_desc = a_tmpl | (uint64_t)((a_addr >> 4) & 0x3FFF);
+                const uint64_t b_desc = b_tmpl + (uint64_t)((((dy * 5 + dx) * Cfg::kKSteps + kk) * 2 * COUT * 16) >> 4);
+                umma_bf16(d_tmem, a_desc, b_desc, idesc, accum);
+                accum = 1;
+              }
+            }
+          }
+          umma_commit(&tfull[stage]);                               // accumulator row ready
+          umma_commit(&empty[(gbase + j) % Cfg::kSlots]);           // oldest input row is dead
+        }
+        for (int i = 0; i < 4; ++i) umma_commit(&empty[(gbase + rows + i) % Cfg::kSlots]);
+        gbase += rows + 4;
+      }
+    }
+  } else {
+    // ===================== epilogue warps (2..5) =====================
+    const int quarter = warp & 3;                 // TMEM lane quarter this warp may read
+    const int m = quarter * 32 + lane;            // pixel within the row tile
+    float ssum[STATS ? COUT : 1], ssq[STATS ? COUT : 1];
+    if (STATS) {
+#pragma unroll
+      for (int c = 0; c < COUT; ++c) { ssum[c] = 0.f; ssq[c] = 0.f; }
+    }
+    uint32_t q = 0;
+    for (int item = blockIdx.x; item < g.nitems; item += gridDim.x) {
+      const int seg = item % g.nseg;
+      const int strip = (item / g.nseg) % g.nstrips;
+      const int b = item / (g.nseg * g.nstrips);
+      const int y0 = seg * g.rseg;
+      const int rows = min(g.rseg, g.H - y0);
+      const int x = strip * kBM + m;
+      const bool valid = x < g.W;
+      for (int j = 0; j < rows; ++j, ++q) {
+        const uint32_t stage = q % kNumTmemStages, use = q / kNumTmemStages;
+        mbar_wait(&tfull[stage], use & 1);
+        tc_fence_after();
+        const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + stage * COUT;
+        uint32_t v[COUT];
+#pragma unroll
+        for (int c0 = 0; c0 < COUT; c0 += 16) tmem_ld16(taddr + c0, *reinterpret_cast<uint32_t(*)[16]>(&v[c0]));
+        tmem_ld_wait();
+        tc_fence_before();
+        mbar_arrive(&tempty[stage]);              // TMEM stage may be overwritten
+        uint32_t pk[COUT / 2];
+#pragma unroll
+        for (int c = 0; c < COUT; c += 2) {
+          pk[c / 2] = pack_bf16x2(__uint_as_float(v[c]) + s_bias[c], __uint_as_float(v[c + 1]) + s_bias[c + 1]);
+          if (STATS && valid) {
+            const float r0 = bf16_lo(pk[c / 2]), r1 = bf16_hi(pk[c / 2]);
+            ssum[c] += r0; ssq[c] = fmaf(r0, r0, ssq[c]);
+            ssum[c + 1] += r1; ssq[c + 1] = fmaf(r1, r1, ssq[c + 1]);
+          }
+        }
+        if (valid) {
+          uint4* o = reinterpret_cast<uint4*>(out + (((size_t)b * g.H + (y0 + j)) * g.W + x) * COUT);
+#pragma unroll
+          for (int i = 0; i < COUT / 8; ++i) o[i] = make_uint4(pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
+        }
+      }
+    }
+    if (STATS) {
+#pragma unroll
+      for (int c = 0; c < COUT; ++c) {
+        const float a = warp_sum(ssum[c]), s2 = warp_sum(ssq[c]);
+        if (lane == 0) { s_stat[quarter * 2 * COUT + c] = a; s_stat[quarter * 2 * COUT + COUT + c] = s2; }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  if (STATS && threadIdx.x < 2 * COUT) {
+    float a = 0.f;
+#pragma unroll
+    for (int w4 = 0; w4 < 4; ++w4) a += s_stat[w4 * 2 * COUT + threadIdx.x];
+    partials[(size_t)blockIdx.x * 2 * COUT + threadIdx.x] = a;
+  }
+  if (warp == 1) { __syncwarp(); tmem_dealloc<Cfg::kTmemCols>(tmem_base); }
+}
+
+// ================================================================== wgrad ===
+// dW[co][ci][dy][dx] = sum_{b,y,x} dxo[b,y,x,co] * act[b,y+dy-2,x+dx-2,ci]
+// act: bf16 NHWC, 16 channels (2 planes);  dxo: bf16 NHWC, 32 channels (4 planes).
+constexpr int kWgSlotsA = 10, kWgSlotsB = 4;
+constexpr int kWgSlotABytes = 2 * kPlaneBytes;        // 4352
+constexpr int kWgPlaneBBytes = kBM * 16;              // 2048
+constexpr int kWgSlotBBytes = 4 * kWgPlaneBBytes;     // 8192
+constexpr int kWgSmemBytes = kWgSlotsA * kWgSlotABytes + kWgSlotsB * kWgSlotBBytes + 1024 + 128;
+constexpr int kWgTmemCols = 512;                      // 10 accumulators x 32 columns -> next pow2
+
+__global__ void __launch_bounds__(kThreads, 1)
+conv5x5_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tm_act, const __grid_constant__ CUtensorMap tm_dxo,
+                        float* __restrict__ partials, ConvGeom g) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((128u - (smem_u32(smem_raw) & 127u)) & 127u);
+  uint8_t* s_a = smem;
+  uint8_t* s_b = smem + kWgSlotsA * kWgSlotABytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_b + kWgSlotsB * kWgSlotBBytes);
+  uint64_t* fullA = bars;
+  uint64_t* emptyA = fullA + kWgSlotsA;
+  uint64_t* fullB = emptyA + kWgSlotsA;
+  uint64_t* emptyB = fullB + kWgSlotsB;
+  uint64_t* done = emptyB + kWgSlotsB;
+  uint32_t* s_tmem = reinterpret_cast<uint32_t*>(done + 1);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < kWgSlotsA; ++i) { mbar_init(&fullA[i], 1); mbar_init(&emptyA[i], 1); }
+    for (int i = 0; i < kWgSlotsB; ++i) { mbar_init(&fullB[i], 1); mbar_init(&emptyB[i], 1); }
+    mbar_init(done, 1);
+    mbar_fence_init();
+    tma_prefetch_desc(&tm_act);
+    tma_prefetch_desc(&tm_dxo);
+  }
+  if (warp == 1) tmem_alloc<kWgTmemCols>(s_tmem);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *s_tmem;
+  const bool has_work = (int)blockIdx.x < g.nitems;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      uint32_t ga = 0, gb = 0;
+      for (int item = blockIdx.x; item < g.nitems; item += gridDim.x) {
+        const int seg = item % g.nseg;
+        const int strip = (item / g.nseg) % g.nstrips;
+        const int b = item / (g.nseg * g.nstrips);
+        const int y0 = seg * g.rseg;
+        const int rows = min(g.rseg, g.H - y0);
+        const int x0 = strip * kBM;
+        for (int i = 0; i < rows + 4; ++i) {
+          {
+            const uint32_t slot = ga % kWgSlotsA, use = ga / kWgSlotsA;
+            mbar_wait(&emptyA[slot], (use & 1) ^ 1);
+            mbar_expect_tx(&fullA[slot], kWgSlotABytes);
+            uint8_t* dst = s_a + slot * kWgSlotABytes;
+            tma_load_5d(dst, &tm_act, &fullA[slot], 0, 0, x0 - 2, y0 - 2 + i, b);
+            tma_load_5d(dst + kPlaneBytes, &tm_act, &fullA[slot], 0, 1, x0 - 2, y0 - 2 + i, b);
+            ++ga;
+          }
+          // dxo row j is consumed together with act rows j..j+4: issue it after act row j+2
+          if (i >= 2 && i - 2 < rows) {
+            const uint32_t slot = gb % kWgSlotsB, use = gb / kWgSlotsB;
+            mbar_wait(&emptyB[slot], (use & 1) ^ 1);
+            mbar_expect_tx(&fullB[slot], kWgSlotBBytes);
+            uint8_t* dst = s_b + slot * kWgSlotBBytes;
+#pragma unroll
+            for (int p = 0; p < 4; ++p)
+              tma_load_5d(dst + p * kWgPlaneBBytes, &tm_dxo, &fullB[slot], 0, p, x0, y0 + i - 2, b);
+            ++gb;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      // A: M=64 (8 dx-shifts x 8 channels of one plane), MN-major: SBO = 16 B (next dx), LBO = 128 B (next 8 pixels)
+      // B: N=32 (4 planes of 8 co),                      MN-major: SBO = plane stride,  LBO = 128 B
+      constexpr uint32_t idesc = umma_idesc_bf16(64, 32, 1, 1);
+      const uint64_t a_tmpl = smem_desc_noswz(0, 128, 16);
+      const uint64_t b_tmpl = smem_desc_noswz(0, 128, kWgPlaneBBytes);
+      const uint32_t a_base = smem_u32(s_a), b_base = smem_u32(s_b);
+      uint32_t gbase = 0, gb = 0;
+      uint32_t first = 1;
+      for (int item = blockIdx.x; item < g.nitems; item += gridDim.x) {
+        const int seg = item % g.nseg;
+        const int y0 = seg * g.rseg;
+        const int rows = min(g.rseg, g.H - y0);
+        for (int j = 0; j < rows; ++j, ++gb) {
+          for (int i = (j == 0 ? 0 : 4); i < 5; ++i) {
+            const uint32_t gc = gbase + j + i;
+            mbar_wait(&fullA[gc % kWgSlotsA], (gc / kWgSlotsA) & 1);
+          }
+          const uint32_t slotB = gb % kWgSlotsB;
+          mbar_wait(&fullB[slotB], (gb / kWgSlotsB) & 1);
+          tc_fence_after();
+          const uint32_t brow = b_base + slotB * kWgSlotBBytes;
+#pragma unroll 1
+          for (int kb = 0; kb < kBM / 16; ++kb) {
+            const uint64_t b_desc = b_tmpl | (uint64_t)(((brow + kb * 256) >> 4) & 0x3FFF);
+#pragma unroll
+            for (int dy = 0; dy < 5; ++dy) {
+              const uint32_t arow = a_base + ((gbase + j + dy) % kWgSlotsA) * kWgSlotABytes + kb * 256;
+#pragma unroll
+              for (int pl = 0; pl < 2; ++pl) {
+                const uint64_t a_desc = a_tmpl | (uint64_t)(((arow + pl * kPlaneBytes) >> 4) & 0x3FFF);
+                umma_bf16(tmem_base + (dy * 2 + pl) * 32, a_desc, b_desc, idesc, first ? 0u : 1u);
+              }
+            }
+            first = 0;
+          }
+          umma_commit(&emptyB[slotB]);
+          umma_commit(&emptyA[(gbase + j) % kWgSlotsA]);
+        }
+        for (int i = 0; i < 4; ++i) umma_commit(&emptyA[(gbase + rows + i) % kWgSlotsA]);
+        gbase += rows + 4;
+      }
+      umma_commit(done);
+    }
+  } else {
+    // epilogue: single pass at the very end.  M=64 accumulators occupy lanes
+    // {0-15, 32-47, 64-79, 96-111}: row r -> lane (r%16) + 32*(r/16).
+    const int quarter = warp & 3;
+    float* dst = partials + (size_t)blockIdx.x * (32 * 16 * kTaps);
+    if (has_work) {
+      mbar_wait(done, 0);
+      tc_fence_after();
+    }
+    const int r = quarter * 16 + (lane & 15);       // accumulator row for lanes 0..15
+    const int dxs = r >> 3, e = r & 7;
+    const bool row_valid = (lane < 16) && (dxs < 5);
+#pragma unroll 1
+    for (int acc = 0; acc < 10; ++acc) {
+      const int dy = acc >> 1, pl = acc & 1;
+      uint32_t v[32];
+      if (has_work) {
+        const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + acc * 32;
+        tmem_ld16(taddr, *reinterpret_cast<uint32_t(*)[16]>(&v[0]));
+        tmem_ld16(taddr + 16, *reinterpret_cast<uint32_t(*)[16]>(&v[16]));
+        tmem_ld_wait();
+      } else {
+#pragma unroll
+        for (int c = 0; c < 32; ++c) v[c] = 0u;
+      }
+      if (row_valid) {
+        const int ci = pl * 8 + e;
+#pragma unroll
+        for (int co = 0; co < 32; ++co)
+          dst[((size_t)co * 16 + ci) * kTaps + dy * 5 + dxs] = __uint_as_float(v[co]);
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  if (warp == 1) { __syncwarp(); tmem_dealloc<kWgTmemCols>(tmem_base); }
+}
+
+// ------------------------------------------------------------- host side ----
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = (EncodeTiledFn)p;
+  });
+  return fn;
+}
+
+// 5-D map over a bf16 NHWC activation: {8 ch, C/8 planes, W, H, B}; box {8,1,boxW,1,1}.
+int make_act_tmap(CUtensorMap* tm, const void* ptr, int B, int H, int W, int C, int boxW) {
+  EncodeTiledFn enc = get_encode_fn();
+  if (!enc) return b200_fail(-3, "cuTensorMapEncodeTiled entry point not available");
+  cuuint64_t gdim[5] = {8, (cuuint64_t)(C / 8), (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)B};
+  cuuint64_t gstr[4] = {16, (cuuint64_t)C * 2, (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2};
+  cuuint32_t box[5] = {8, 1, (cuuint32_t)boxW, 1, 1};
+  cuuint32_t estr[5] = {1, 1, 1, 1, 1};
+  CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, const_cast<void*>(ptr), gdim, gstr, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return b200_fail((int)r, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+  return 0;
+}
+
+// Pick the row-segment length that best fills the persistent grid.
+ConvGeom make_geom(int B, int H, int W, int nsm, int halo_rows) {
+  ConvGeom g;
+  g.B = B; g.H = H; g.W = W;
+  g.nstrips = (W + kBM - 1) / kBM;
+  double best = -1.0;
+  int best_rseg = H;
+  for (int nseg = 1; nseg <= H; ++nseg) {
+    const int rseg = (H + nseg - 1) / nseg;
+    if (rseg < 8 && nseg > 1) break;
+    const long items = (long)B * g.nstrips * ((H + rseg - 1) / rseg);
+    const long waves = (items + nsm - 1) / nsm;
+    const double eff = (double)items / (double)(waves * nsm) * (double)rseg / (double)(rseg + halo_rows);
+    if (eff > best + 1e-9) { best = eff; best_rseg = rseg; }
+  }
+  g.rseg = best_rseg;
+  g.nseg = (H + g.rseg - 1) / g.rseg;
+  g.nitems = B * g.nstrips * g.nseg;
+  return g;
+}
+
+template <int CIN, int COUT, bool TRANSPOSED, bool STATS>
+int launch_conv(const void* act, const void* w, const void* bias, void* out, void* partials, int B, int H, int W,
+                cudaStream_t s, int* grid_out) {
+  using Cfg = ConvCfg<CIN, COUT>;
+  auto kern = conv5x5_tc_kernel<CIN, COUT, TRANSPOSED, STATS>;
+  static std::once_flag once;
+  static cudaError_t attr_err = cudaSuccess;
+  std::call_once(once, [&] {
+    attr_err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes);
+  });
+  B200_CUDA(attr_err);
+  CUtensorMap tm;
+  int rc = make_act_tmap(&tm, act, B, H, W, CIN, kPW);
+  if (rc) return rc;
+  const int nsm = b200_num_sms();
+  ConvGeom g = make_geom(B, H, W, nsm, 4);
+  const int grid = g.nitems < nsm ? g.nitems : nsm;
+  kern<<<grid, kThreads, Cfg::kSmemBytes, s>>>(tm, (const float*)w, (const float*)bias, (__nv_bfloat16*)out,
+                                                (float*)partials, g);
+  B200_LAUNCH_CHECK();
+  if (grid_out) *grid_out = grid;
+  return 0;
+}
+
+}  // namespace
+
+// Number of partial-stat rows conv2_fwd writes (= its grid size); callers size
+// the partials buffer with b200_conv_tc_max_grid() x 2*COUT floats.
+B200_API int b200_conv_tc_max_grid() { return b200_num_sms(); }
+
+// *nparts_out receives the number of valid partial-stat rows (= grid size).
+B200_API int b200_conv2_fwd_tc(const void* p1_bf16, const void* w2, const void* b2, void* x2_bf16,
+                               void* partials, int B, int H, int W, int* nparts_out, void* stream) {
+  return launch_conv<16, 32, false, true>(p1_bf16, w2, b2, x2_bf16, partials, B, H, W, (cudaStream_t)stream,
+                                          nparts_out);
+}
+
+B200_API int b200_conv2_dgrad_tc(const void* dx2_bf16, const void* w2, void* dp1_bf16, int B, int H, int W,
+                                 void* stream) {
+  return launch_conv<32, 16, true, false>(dx2_bf16, w2, nullptr, dp1_bf16, nullptr, B, H, W, (cudaStream_t)stream,
+                                          nullptr);
+}
+
+// partials: [b200_conv_tc_max_grid()][32*16*25] floats of scratch; dw2: [32][16][5][5].
+B200_API int b200_conv2_wgrad_tc(const void* p1_bf16, const void* dx2_bf16, void* partials, void* dw2, int B,
+                                 int H, int W, float gscale, void* stream) {
+  cudaStream_t s = (cudaStream_t)stream;
+  static std::once_flag once;
+  static cudaError_t attr_err = cudaSuccess;
+  std::call_once(once, [&] {
+    attr_err = cudaFuncSetAttribute(conv5x5_wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kWgSmemBytes);
+  });
+  B200_CUDA(attr_err);
+  CUtensorMap tma, tmb;
+  int rc = make_act_tmap(&tma, p1_bf16, B, H, W, 16, kPW);
+  if (rc) return rc;
+  rc = make_act_tmap(&tmb, dx2_bf16, B, H, W, 32, kBM);
+  if (rc) return rc;
+  const int nsm = b200_num_sms();
+  ConvGeom g = make_geom(B, H, W, nsm, 4);
+  const int grid = g.nitems < nsm ? g.nitems : nsm;
+  conv5x5_wgrad_tc_kernel<<<grid, kThreads, kWgSmemBytes, s>>>(tma, tmb, (float*)partials, g);
+  B200_LAUNCH_CHECK();
+  return b200_reduce_partials(partials, grid, 32 * 16 * kTaps, dw2, gscale, stream);
+}

@@ -1,0 +1,923 @@
+// CUDA-core (non tensor-core) kernels of the b200dp ConvNet training step.
+//
+// The reference model (mnist_onegpu.py:11-31 / mnist_distributed.py:25-45) is
+//   conv(1->16,5x5,p2) BN ReLU pool2 | conv(16->32,5x5,p2) BN ReLU pool2 | fc(18M->10)
+// and the reference runs it as ~30 separate cuDNN/ATen/cuBLAS launches, each a
+// full HBM round trip over multi-GB fp32 NCHW tensors.
+// Here the step is re-cut for B200: activations are bf16 NHWC, BN statistics
+// are produced in the epilogue of the conv that feeds them, BN-apply+ReLU+pool
+// is one pass, max-pool indices are never stored (recomputed from the pre-BN
+// tensor in backward), the loss is fused with the fc tail and the fc backward
+// can apply SGD in place.  The two layers that are GEMM-shaped (conv2
+// fwd/dgrad/wgrad) live in conv_tc.cu on tcgen05; the ones here are either
+// bandwidth-bound or have Cin=1 (conv1: K=25, no tensor-core shape).
+#include "common.h"
+#include "ptx.cuh"
+#include <cstdint>
+
+using b2::bf16_hi;
+using b2::bf16_lo;
+using b2::pack_bf16x2;
+using b2::warp_sum;
+
+namespace {
+
+constexpr int kC1 = 16;       // conv1 output channels
+constexpr int kTaps = 25;     // 5x5
+__constant__ float c_w1[kC1 * kTaps];
+__constant__ float c_b1[kC1];
+
+__device__ __forceinline__ uint4 ldg_stream16(const void* p) {
+  uint4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+  return r;
+}
+__device__ __forceinline__ uint2 ldg_stream8(const void* p) {
+  uint2 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v2.u32 {%0,%1}, [%2];" : "=r"(r.x), "=r"(r.y) : "l"(p));
+  return r;
+}
+
+// ----------------------------------------------------------------- resize ---
+// K1/K2: the reference resizes 28x28 -> 3000x3000 on the CPU
+// with PIL (0.176 s/image) and ships 36 MB/image over PCIe.  Here the raw
+// uint8 digits go to the device (784 B/image) and this kernel reproduces PIL's
+// 8-bit bilinear resample bit for bit: horizontal pass then vertical pass,
+// 22-bit fixed-point coefficients, rounding to uint8 after EACH pass, then
+// ToTensor's /255.  The coefficient tables come from the host (data/resize.py).
+__device__ __forceinline__ int clip8(int v) { return v < 0 ? 0 : (v > 255 ? 255 : v); }
+
+__global__ void resize_pil_bilinear_kernel(const uint8_t* __restrict__ src, int sh, int sw,
+                                           const int* __restrict__ xtab, const int* __restrict__ ytab,
+                                           float* __restrict__ dst, int H, int W) {
+  int x = blockIdx.x * blockDim.x + threadIdx.x;
+  int y = blockIdx.y, b = blockIdx.z;
+  if (x >= W) return;
+  int xm = xtab[3 * x], kx0 = xtab[3 * x + 1], kx1 = xtab[3 * x + 2];
+  int ym = ytab[3 * y], ky0 = ytab[3 * y + 1], ky1 = ytab[3 * y + 2];
+  int xm1 = min(xm + 1, sw - 1), ym1 = min(ym + 1, sh - 1);
+  const uint8_t* s = src + (size_t)b * sh * sw;
+  int h0 = clip8((s[ym * sw + xm] * kx0 + s[ym * sw + xm1] * kx1 + (1 << 21)) >> 22);
+  int h1 = clip8((s[ym1 * sw + xm] * kx0 + s[ym1 * sw + xm1] * kx1 + (1 << 21)) >> 22);
+  int v = clip8((h0 * ky0 + h1 * ky1 + (1 << 21)) >> 22);
+  dst[((size_t)b * H + y) * W + x] = (float)v / 255.0f;
+}
+
+// -------------------------------------------------------------- conv1 fwd ---
+// K3 + K4-stats: direct 5x5 conv, Cin=1 -> 16 channels, fp32 FFMA with the 400
+// weights as constant-bank operands.  Each thread owns 4 consecutive pixels of
+// one row (a 5x8 register window) and all 16 channels; output is bf16 NHWC and
+// the per-channel sum / sum-of-squares of the ROUNDED outputs are accumulated
+// per thread and reduced once per block (deterministic: partials -> finalize).
+constexpr int kT1H = 16, kT1W = 64;
+
+__global__ void __launch_bounds__(256, 2)
+conv1_fwd_kernel(const float* __restrict__ in, __nv_bfloat16* __restrict__ x1,
+                 float* __restrict__ partials, int B, int H, int W, int tilesX, int tilesY) {
+  __shared__ __align__(16) float s_in[kT1H + 4][kT1W + 4];
+  __shared__ float s_red[8][2 * kC1];
+  const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+  float ssum[kC1], ssq[kC1];
+#pragma unroll
+  for (int c = 0; c < kC1; ++c) { ssum[c] = 0.f; ssq[c] = 0.f; }
+
+  const long total = (long)B * tilesX * tilesY;
+  for (long tile = blockIdx.x; tile < total; tile += gridDim.x) {
+    const int b = (int)(tile / (tilesX * tilesY));
+    const int r = (int)(tile % (tilesX * tilesY));
+    const int y0 = (r / tilesX) * kT1H, x0 = (r % tilesX) * kT1W;
+    __syncthreads();
+    for (int i = threadIdx.x; i < (kT1H + 4) * (kT1W + 4); i += 256) {
+      int ry = i / (kT1W + 4), rx = i % (kT1W + 4);
+      int gy = y0 + ry - 2, gx = x0 + rx - 2;
+      float v = 0.f;
+      if (gy >= 0 && gy < H && gx >= 0 && gx < W) v = __ldg(in + ((size_t)b * H + gy) * W + gx);
+      s_in[ry][rx] = v;
+    }
+    __syncthreads();
+    const int gy = y0 + ty, gx = x0 + 4 * tx;
+    const bool valid = (gy < H) && (gx < W);   // W % 4 == 0: a 4-pixel group is all-or-nothing
+    float win[5][8];
+#pragma unroll
+    for (int dy = 0; dy < 5; ++dy) {
+      float4 a = *reinterpret_cast<const float4*>(&s_in[ty + dy][4 * tx]);
+      float4 c = *reinterpret_cast<const float4*>(&s_in[ty + dy][4 * tx + 4]);
+      win[dy][0] = a.x; win[dy][1] = a.y; win[dy][2] = a.z; win[dy][3] = a.w;
+      win[dy][4] = c.x; win[dy][5] = c.y; win[dy][6] = c.z; win[dy][7] = c.w;
+    }
+    uint32_t packed[4][kC1 / 2];
+#pragma unroll
+    for (int c = 0; c < kC1; c += 2) {
+      float acc[2][4];
+#pragma unroll
+      for (int cc = 0; cc < 2; ++cc) {
+#pragma unroll
+        for (int p = 0; p < 4; ++p) acc[cc][p] = c_b1[c + cc];
+#pragma unroll
+        for (int dy = 0; dy < 5; ++dy)
+#pragma unroll
+          for (int dx = 0; dx < 5; ++dx) {
+            const float w = c_w1[(c + cc) * kTaps + dy * 5 + dx];
+#pragma unroll
+            for (int p = 0; p < 4; ++p) acc[cc][p] = fmaf(win[dy][dx + p], w, acc[cc][p]);
+          }
+      }
+#pragma unroll
+      for (int p = 0; p < 4; ++p) {
+        uint32_t pk = pack_bf16x2(acc[0][p], acc[1][p]);
+        packed[p][c / 2] = pk;
+        if (valid) {
+          float r0 = bf16_lo(pk), r1 = bf16_hi(pk);
+          ssum[c] += r0; ssq[c] = fmaf(r0, r0, ssq[c]);
+          ssum[c + 1] += r1; ssq[c + 1] = fmaf(r1, r1, ssq[c + 1]);
+        }
+      }
+    }
+    if (valid) {
+      uint4* o = reinterpret_cast<uint4*>(x1 + (((size_t)b * H + gy) * W + gx) * kC1);
+#pragma unroll
+      for (int p = 0; p < 4; ++p) {
+        o[2 * p] = make_uint4(packed[p][0], packed[p][1], packed[p][2], packed[p][3]);
+        o[2 * p + 1] = make_uint4(packed[p][4], packed[p][5], packed[p][6], packed[p][7]);
+      }
+    }
+  }
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+#pragma unroll
+  for (int c = 0; c < kC1; ++c) {
+    float a = warp_sum(ssum[c]), q = warp_sum(ssq[c]);
+    if (lane == 0) { s_red[warp][c] = a; s_red[warp][kC1 + c] = q; }
+  }
+  __syncthreads();
+  if (threadIdx.x < 2 * kC1) {
+    float a = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) a += s_red[w][threadIdx.x];
+    partials[(size_t)blockIdx.x * 2 * kC1 + threadIdx.x] = a;
+  }
+}
+
+// ------------------------------------------------------------ BN finalize ---
+// K4: per-channel batch statistics from the conv epilogue partials (summed in
+// fp64), the fused affine (scale = gamma*rstd, shift = beta - mean*scale) and
+// the running-stat update torch's BatchNorm2d does in train mode: momentum
+// 0.1, UNBIASED variance, num_batches_tracked += 1.
+// out = [scale | shift | mean | rstd], each C floats.
+__global__ void bn_finalize_kernel(const float* __restrict__ partials, int nparts, int C, double count,
+                                   const float* __restrict__ gamma, const float* __restrict__ beta,
+                                   float* running_mean, float* running_var, long long* nbt,
+                                   float momentum, float eps, float* __restrict__ out) {
+  const int c = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (c >= C) return;
+  double s = 0.0, q = 0.0;
+  for (int i = lane; i < nparts; i += 32) {
+    s += (double)partials[(size_t)i * 2 * C + c];
+    q += (double)partials[(size_t)i * 2 * C + C + c];
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    s += __shfl_xor_sync(0xffffffffu, s, o);
+    q += __shfl_xor_sync(0xffffffffu, q, o);
+  }
+  if (lane == 0) {
+    double mean = s / count;
+    double var = q / count - mean * mean;
+    if (var < 0.0) var = 0.0;
+    double rstd = 1.0 / sqrt(var + (double)eps);
+    float sc = (float)((double)gamma[c] * rstd);
+    out[c] = sc;
+    out[C + c] = (float)((double)beta[c] - mean * (double)gamma[c] * rstd);
+    out[2 * C + c] = (float)mean;
+    out[3 * C + c] = (float)rstd;
+    if (running_mean) {
+      double unbiased = count > 1.0 ? var * count / (count - 1.0) : var;
+      running_mean[c] = (float)((1.0 - momentum) * (double)running_mean[c] + momentum * mean);
+      running_var[c] = (float)((1.0 - momentum) * (double)running_var[c] + momentum * unbiased);
+    }
+    if (c == 0 && nbt) *nbt += 1;
+  }
+}
+
+// ------------------------------------------------- BN-apply + ReLU + pool ---
+// K5/K7: one pass, bf16 NHWC in -> bf16 NHWC out at quarter size; no argmax
+// tensor is written (the reference's ATen max-pool stores int64 indices, 8 B
+// per output element).  One thread = one pooled pixel x 8 channels (16 B).
+template <int C>
+__global__ void __launch_bounds__(256)
+bn_relu_pool_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ bn,
+                    __nv_bfloat16* __restrict__ p, int B, int H, int W) {
+  __shared__ float s_sc[C], s_sh[C];
+  if (threadIdx.x < C) { s_sc[threadIdx.x] = bn[threadIdx.x]; s_sh[threadIdx.x] = bn[C + threadIdx.x]; }
+  __syncthreads();
+  constexpr int CH = C / 8;
+  const int Ho = H / 2, Wo = W / 2;
+  const size_t total = (size_t)B * Ho * Wo * CH;
+  for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+       idx += (size_t)gridDim.x * blockDim.x) {
+    const int ch = (int)(idx % CH);
+    size_t pix = idx / CH;
+    const int xo = (int)(pix % Wo); pix /= Wo;
+    const int yo = (int)(pix % Ho);
+    const int b = (int)(pix / Ho);
+    const __nv_bfloat16* base = x + (((size_t)b * H + 2 * yo) * W + 2 * xo) * C + ch * 8;
+    uint4 v[4];
+    v[0] = ldg_stream16(base);
+    v[1] = ldg_stream16(base + C);
+    v[2] = ldg_stream16(base + (size_t)W * C);
+    v[3] = ldg_stream16(base + (size_t)W * C + C);
+    uint32_t o[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      float m0 = 0.f, m1 = 0.f;   // ReLU folded into the max: start from 0
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        uint32_t w = (&v[i].x)[e];
+        m0 = fmaxf(m0, fmaf(bf16_lo(w), s_sc[ch * 8 + 2 * e], s_sh[ch * 8 + 2 * e]));
+        m1 = fmaxf(m1, fmaf(bf16_hi(w), s_sc[ch * 8 + 2 * e + 1], s_sh[ch * 8 + 2 * e + 1]));
+      }
+      o[e] = pack_bf16x2(m0, m1);
+    }
+    *reinterpret_cast<uint4*>(p + (((size_t)b * Ho + yo) * Wo + xo) * C + ch * 8) =
+        make_uint4(o[0], o[1], o[2], o[3]);
+  }
+}
+
+// ------------------------------------ pool + ReLU + BN backward (two modes) --
+// K11/K13: the gradient of the pooled tensor is routed to the arg-max of each
+// 2x2 window (first maximum in row-major order, like ATen) when that maximum
+// is positive.  The arg-max is recomputed from the stored pre-BN tensor.
+//   MODE 0 (stats): per-channel  sum(dy), sum(dy * xhat)  -> partials
+//   MODE 1 (apply): dx = scale * (dy - mean(dy) - xhat * mean(dy*xhat)) -> bf16
+// bn = [scale | shift | mean | rstd]; red = [mean(dy) | mean(dy*xhat)].
+template <int C, int MODE>
+__global__ void __launch_bounds__(256)
+pool_bn_bwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dp,
+                   const float* __restrict__ bn, const float* __restrict__ red,
+                   float* __restrict__ partials, __nv_bfloat16* __restrict__ dx, int B, int H, int W) {
+  constexpr int CH = C / 8;
+  __shared__ float s_bn[4 * C];
+  __shared__ float s_red[2 * C];
+  __shared__ float s_part[8][2 * C];
+  for (int i = threadIdx.x; i < 4 * C; i += blockDim.x) s_bn[i] = bn[i];
+  if (MODE == 1) for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) s_red[i] = red[i];
+  __syncthreads();
+  const int Ho = H / 2, Wo = W / 2;
+  const size_t total = (size_t)B * Ho * Wo * CH;
+  const int ch = threadIdx.x % CH;   // blockDim (256) is a multiple of CH: fixed per thread
+  float a_dy[8], a_dyx[8];
+#pragma unroll
+  for (int e = 0; e < 8; ++e) { a_dy[e] = 0.f; a_dyx[e] = 0.f; }
+
+  for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+       idx += (size_t)gridDim.x * blockDim.x) {
+    size_t pix = idx / CH;
+    const int xo = (int)(pix % Wo); pix /= Wo;
+    const int yo = (int)(pix % Ho);
+    const int b = (int)(pix / Ho);
+    const size_t off0 = (((size_t)b * H + 2 * yo) * W + 2 * xo) * C + ch * 8;
+    const size_t offs[4] = {off0, off0 + C, off0 + (size_t)W * C, off0 + (size_t)W * C + C};
+    uint4 v[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) v[i] = ldg_stream16(x + offs[i]);
+    const uint4 g4 = ldg_stream16(dp + (((size_t)b * Ho + yo) * Wo + xo) * C + ch * 8);
+    uint32_t o[4][4];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      const int c = ch * 8 + e;
+      const float sc = s_bn[c], sh = s_bn[C + c], mu = s_bn[2 * C + c], rs = s_bn[3 * C + c];
+      float xv[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        uint32_t w = (&v[i].x)[e >> 1];
+        xv[i] = (e & 1) ? bf16_hi(w) : bf16_lo(w);
+      }
+      int am = 0;
+      float best = fmaf(xv[0], sc, sh);
+#pragma unroll
+      for (int i = 1; i < 4; ++i) {
+        float y = fmaf(xv[i], sc, sh);
+        if (y > best) { best = y; am = i; }
+      }
+      uint32_t gw = (&g4.x)[e >> 1];
+      float g = (e & 1) ? bf16_hi(gw) : bf16_lo(gw);
+      g = best > 0.f ? g : 0.f;
+      if (MODE == 0) {
+        float xa = xv[0];
+#pragma unroll
+        for (int i = 1; i < 4; ++i) xa = (am == i) ? xv[i] : xa;
+        a_dy[e] += g;
+        a_dyx[e] = fmaf(g, (xa - mu) * rs, a_dyx[e]);
+      } else {
+        const float mdy = s_red[c], mdyx = s_red[C + c];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          float xh = (xv[i] - mu) * rs;
+          float d = sc * (((am == i) ? g : 0.f) - mdy - xh * mdyx);
+          // pack: even e -> low half, odd e -> high half
+          uint32_t bits = (uint32_t)__bfloat16_as_ushort(__float2bfloat16_rn(d));
+          if (e & 1) o[i][e >> 1] |= bits << 16; else o[i][e >> 1] = bits;
+        }
+      }
+    }
+    if (MODE == 1) {
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+        *reinterpret_cast<uint4*>(dx + offs[i]) = make_uint4(o[i][0], o[i][1], o[i][2], o[i][3]);
+    }
+  }
+  if (MODE == 0) {
+    // threads with the same channel chunk are CH apart; reduce across the warp
+    // over lanes that share (lane % CH), then across warps through smem.
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      float a = a_dy[e], q = a_dyx[e];
+#pragma unroll
+      for (int o2 = 16; o2 >= CH; o2 >>= 1) {
+        a += __shfl_xor_sync(0xffffffffu, a, o2);
+        q += __shfl_xor_sync(0xffffffffu, q, o2);
+      }
+      if (lane < CH) { s_part[warp][lane * 8 + e] = a; s_part[warp][C + lane * 8 + e] = q; }
+    }
+    __syncthreads();
+    if (threadIdx.x < 2 * C) {
+      float a = 0.f;
+      for (int w = 0; w < (int)(blockDim.x >> 5); ++w) a += s_part[w][threadIdx.x];
+      partials[(size_t)blockIdx.x * 2 * C + threadIdx.x] = a;
+    }
+  }
+}
+
+// red = [mean(dy) | mean(dy*xhat)], dgamma = sum(dy*xhat), dbeta = sum(dy).
+__global__ void bn_bwd_finalize_kernel(const float* __restrict__ partials, int nparts, int C, double count,
+                                       float* __restrict__ red, float* __restrict__ dgamma,
+                                       float* __restrict__ dbeta, float gscale) {
+  const int c = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (c >= C) return;
+  double s = 0.0, q = 0.0;
+  for (int i = lane; i < nparts; i += 32) {
+    s += (double)partials[(size_t)i * 2 * C + c];
+    q += (double)partials[(size_t)i * 2 * C + C + c];
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    s += __shfl_xor_sync(0xffffffffu, s, o);
+    q += __shfl_xor_sync(0xffffffffu, q, o);
+  }
+  if (lane == 0) {
+    red[c] = (float)(s / count);
+    red[C + c] = (float)(q / count);
+    dgamma[c] = (float)(q * (double)gscale);
+    dbeta[c] = (float)(s * (double)gscale);
+  }
+}
+
+// ------------------------------------------------------------ conv1 wgrad ---
+// K13: pool1/ReLU1/BN1 backward fused with the conv1 weight gradient.  The
+// dense conv1-output gradient (16 x 9M per image) is never materialised: each
+// thread rebuilds it for a 2x2 window x 4 channels from (x1, dp1, BN stats) and
+// immediately contracts it with the 6x6 input patch: 400 FMA per window.
+// partials[block][c*25 + tap].
+constexpr int kWgT = 32;   // full-res tile edge
+
+__global__ void __launch_bounds__(256, 1)
+conv1_wgrad_kernel(const float* __restrict__ in, const __nv_bfloat16* __restrict__ x1,
+                   const __nv_bfloat16* __restrict__ dp1, const float* __restrict__ bn,
+                   const float* __restrict__ red, float* __restrict__ partials,
+                   int B, int H, int W, int tilesX, int tilesY) {
+  __shared__ float s_in[kWgT + 4][kWgT + 5];
+  __shared__ float s_acc[8][4][100];
+  const int cg = threadIdx.x & 3, wl = threadIdx.x >> 2;
+  float sc[4], sh[4], mu[4], rs[4], mdy[4], mdyx[4];
+#pragma unroll
+  for (int c = 0; c < 4; ++c) {
+    const int ch = cg * 4 + c;
+    sc[c] = bn[ch]; sh[c] = bn[kC1 + ch]; mu[c] = bn[2 * kC1 + ch]; rs[c] = bn[3 * kC1 + ch];
+    mdy[c] = red[ch]; mdyx[c] = red[kC1 + ch];
+  }
+  float acc[4][kTaps];
+#pragma unroll
+  for (int c = 0; c < 4; ++c)
+#pragma unroll
+    for (int t = 0; t < kTaps; ++t) acc[c][t] = 0.f;
+
+  const int Ho = H / 2, Wo = W / 2;
+  const long total = (long)B * tilesX * tilesY;
+  for (long tile = blockIdx.x; tile < total; tile += gridDim.x) {
+    const int b = (int)(tile / (tilesX * tilesY));
+    const int r = (int)(tile % (tilesX * tilesY));
+    const int y0 = (r / tilesX) * kWgT, x0 = (r % tilesX) * kWgT;
+    __syncthreads();
+    for (int i = threadIdx.x; i < (kWgT + 4) * (kWgT + 4); i += 256) {
+      int ry = i / (kWgT + 4), rx = i % (kWgT + 4);
+      int gy = y0 + ry - 2, gx = x0 + rx - 2;
+      float v = 0.f;
+      if (gy >= 0 && gy < H && gx >= 0 && gx < W) v = __ldg(in + ((size_t)b * H + gy) * W + gx);
+      s_in[ry][rx] = v;
+    }
+    __syncthreads();
+#pragma unroll 1
+    for (int k = 0; k < 4; ++k) {
+      const int widx = wl + 64 * k;           // 16 x 16 windows per tile
+      const int wy = widx >> 4, wx = widx & 15;
+      const int gy = y0 + 2 * wy, gx = x0 + 2 * wx;
+      if (gy >= H || gx >= W) continue;       // H, W even: windows are all-or-nothing
+      float dxv[4][4];                        // [pixel][channel]
+      {
+        uint2 xr[4];
+        const __nv_bfloat16* xb = x1 + (((size_t)b * H + gy) * W + gx) * kC1 + cg * 4;
+        xr[0] = ldg_stream8(xb);
+        xr[1] = ldg_stream8(xb + kC1);
+        xr[2] = ldg_stream8(xb + (size_t)W * kC1);
+        xr[3] = ldg_stream8(xb + (size_t)W * kC1 + kC1);
+        const uint2 gr = ldg_stream8(dp1 + (((size_t)b * Ho + (gy >> 1)) * Wo + (gx >> 1)) * kC1 + cg * 4);
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          float xv[4];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            uint32_t w = (c < 2) ? xr[i].x : xr[i].y;
+            xv[i] = (c & 1) ? bf16_hi(w) : bf16_lo(w);
+          }
+          int am = 0;
+          float best = fmaf(xv[0], sc[c], sh[c]);
+#pragma unroll
+          for (int i = 1; i < 4; ++i) {
+            float y = fmaf(xv[i], sc[c], sh[c]);
+            if (y > best) { best = y; am = i; }
+          }
+          uint32_t gw = (c < 2) ? gr.x : gr.y;
+          float g = (c & 1) ? bf16_hi(gw) : bf16_lo(gw);
+          g = best > 0.f ? g : 0.f;
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            float xh = (xv[i] - mu[c]) * rs[c];
+            dxv[i][c] = sc[c] * (((am == i) ? g : 0.f) - mdy[c] - xh * mdyx[c]);
+          }
+        }
+      }
+      float patch[6][6];
+#pragma unroll
+      for (int i = 0; i < 6; ++i)
+#pragma unroll
+        for (int j = 0; j < 6; ++j) patch[i][j] = s_in[2 * wy + i][2 * wx + j];
+#pragma unroll
+      for (int py = 0; py < 2; ++py)
+#pragma unroll
+        for (int px = 0; px < 2; ++px)
+#pragma unroll
+          for (int dy = 0; dy < 5; ++dy)
+#pragma unroll
+            for (int dxx = 0; dxx < 5; ++dxx) {
+              const float v = patch[py + dy][px + dxx];
+#pragma unroll
+              for (int c = 0; c < 4; ++c)
+                acc[c][dy * 5 + dxx] = fmaf(dxv[py * 2 + px][c], v, acc[c][dy * 5 + dxx]);
+            }
+    }
+  }
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+#pragma unroll
+  for (int c = 0; c < 4; ++c)
+#pragma unroll
+    for (int t = 0; t < kTaps; ++t) {
+      float a = acc[c][t];
+      a += __shfl_xor_sync(0xffffffffu, a, 4);
+      a += __shfl_xor_sync(0xffffffffu, a, 8);
+      a += __shfl_xor_sync(0xffffffffu, a, 16);
+      if (lane < 4) s_acc[warp][lane][c * kTaps + t] = a;   // lane == cg here
+    }
+  __syncthreads();
+  for (int i = threadIdx.x; i < 400; i += 256) {
+    const int g = i / 100, j = i % 100;    // channel = g*4 + j/25, tap = j%25  -> index i
+    float a = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) a += s_acc[w][g][j];
+    partials[(size_t)blockIdx.x * 400 + i] = a;
+  }
+}
+
+// out[j] = scale * sum_i partials[i][j]   (fp64 accumulation, deterministic)
+__global__ void reduce_partials_kernel(const float* __restrict__ partials, int nparts, int len,
+                                       float* __restrict__ out, float scale) {
+  int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= len) return;
+  double s = 0.0;
+  for (int i = 0; i < nparts; ++i) s += (double)partials[(size_t)i * len + j];
+  out[j] = (float)(s * (double)scale);
+}
+
+// ------------------------------------------------------------------ fc fwd ---
+// K8: logits[b][k] = sum_j p2[b][j] * W[k][j].  M = batch (5), N = 10,
+// K = 18,000,000: a pure weight-streaming problem (720 MB of fp32 W per pass),
+// so the roofline is HBM bandwidth, not the tensor pipe.  Split-K over the
+// grid; partial logits are reduced by fc_reduce_kernel.
+constexpr int kNC = 10;   // classes
+
+template <int BT>
+__global__ void __launch_bounds__(256)
+fc_fwd_kernel(const __nv_bfloat16* __restrict__ p2, const float* __restrict__ W,
+              float* __restrict__ partials, size_t F) {
+  float acc[BT][kNC];
+#pragma unroll
+  for (int b = 0; b < BT; ++b)
+#pragma unroll
+    for (int k = 0; k < kNC; ++k) acc[b][k] = 0.f;
+  const size_t n4 = F / 4;
+  for (size_t j = (size_t)blockIdx.x * 256 + threadIdx.x; j < n4; j += (size_t)gridDim.x * 256) {
+    uint4 w[kNC];
+    uint2 a[BT];
+#pragma unroll
+    for (int k = 0; k < kNC; ++k) w[k] = ldg_stream16(W + (size_t)k * F + 4 * j);
+#pragma unroll
+    for (int b = 0; b < BT; ++b) a[b] = ldg_stream8(p2 + (size_t)b * F + 4 * j);
+#pragma unroll
+    for (int b = 0; b < BT; ++b) {
+      const float a0 = bf16_lo(a[b].x), a1 = bf16_hi(a[b].x), a2 = bf16_lo(a[b].y), a3 = bf16_hi(a[b].y);
+#pragma unroll
+      for (int k = 0; k < kNC; ++k) {
+        float s = acc[b][k];
+        s = fmaf(a0, __uint_as_float(w[k].x), s);
+        s = fmaf(a1, __uint_as_float(w[k].y), s);
+        s = fmaf(a2, __uint_as_float(w[k].z), s);
+        s = fmaf(a3, __uint_as_float(w[k].w), s);
+        acc[b][k] = s;
+      }
+    }
+  }
+  __shared__ float s_red[8][BT * kNC];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+#pragma unroll
+  for (int b = 0; b < BT; ++b)
+#pragma unroll
+    for (int k = 0; k < kNC; ++k) {
+      float v = warp_sum(acc[b][k]);
+      if (lane == 0) s_red[warp][b * kNC + k] = v;
+    }
+  __syncthreads();
+  if (threadIdx.x < BT * kNC) {
+    float v = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) v += s_red[w][threadIdx.x];
+    partials[(size_t)blockIdx.x * BT * kNC + threadIdx.x] = v;
+  }
+}
+
+__global__ void fc_reduce_kernel(const float* __restrict__ partials, int nparts, int n,
+                                 const float* __restrict__ bias, float* __restrict__ logits) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  double s = 0.0;
+  for (int p = 0; p < nparts; ++p) s += (double)partials[(size_t)p * n + i];
+  logits[i] = (float)s + bias[i % kNC];
+}
+
+// K9: CrossEntropyLoss(reduction='mean') forward + backward in one block:
+// loss, dlogits = (softmax - onehot) * gscale / B, dbias = sum_b dlogits.
+// gscale carries DDP's 1/world_size pre-division for the bias gradient only;
+// dlogits itself stays unscaled (the bucket all-reduce applies 1/world).
+__global__ void ce_kernel(const float* __restrict__ logits, const long long* __restrict__ labels, int B,
+                          float* __restrict__ loss, float* __restrict__ dlogits, float* __restrict__ dbias,
+                          float gscale) {
+  __shared__ float s_loss;
+  __shared__ float s_db[kNC];
+  if (threadIdx.x == 0) s_loss = 0.f;
+  if (threadIdx.x < kNC) s_db[threadIdx.x] = 0.f;
+  __syncthreads();
+  for (int b = threadIdx.x; b < B; b += blockDim.x) {
+    float l[kNC], m = -INFINITY;
+#pragma unroll
+    for (int k = 0; k < kNC; ++k) { l[k] = logits[b * kNC + k]; m = fmaxf(m, l[k]); }
+    float se = 0.f;
+#pragma unroll
+    for (int k = 0; k < kNC; ++k) { l[k] = expf(l[k] - m); se += l[k]; }
+    const int y = (int)labels[b];
+    const float lse = logf(se) + m;
+    atomicAdd(&s_loss, (lse - logits[b * kNC + y]) / (float)B);
+#pragma unroll
+    for (int k = 0; k < kNC; ++k) {
+      float d = (l[k] / se - (k == y ? 1.f : 0.f)) / (float)B;
+      dlogits[b * kNC + k] = d;
+      atomicAdd(&s_db[k], d);
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) *loss = s_loss;
+  if (threadIdx.x < kNC) dbias[threadIdx.x] = s_db[threadIdx.x] * gscale;
+}
+
+// ------------------------------------------------------------------ fc bwd ---
+// K10 (+K14): one streaming pass over the 18M axis produces
+//   dW[k][j] = gscale * sum_b dl[b][k] * p2[b][j]   (written straight into the
+//              gradient bucket: in DDP that buffer is the symmetric-memory
+//              bucket the all-reduce kernel reads)
+//   dp2[b][j] = sum_k dl[b][k] * W[k][j]            (bf16)
+// and, on the single-GPU path (lr != 0), applies SGD in place (W -= lr * dW)
+// so the 720 MB gradient is never written or re-read.
+template <int BT>
+__global__ void __launch_bounds__(256)
+fc_bwd_kernel(const float* __restrict__ dl, const __nv_bfloat16* __restrict__ p2, float* W,
+              float* dW, __nv_bfloat16* __restrict__ dp2, size_t F, float lr, int accumulate, float gscale) {
+  __shared__ float s_dl[BT * kNC];
+  if (threadIdx.x < BT * kNC) s_dl[threadIdx.x] = dl[threadIdx.x];
+  __syncthreads();
+  float d[BT][kNC];
+#pragma unroll
+  for (int b = 0; b < BT; ++b)
+#pragma unroll
+    for (int k = 0; k < kNC; ++k) d[b][k] = s_dl[b * kNC + k];
+  const size_t n4 = F / 4;
+  for (size_t j = (size_t)blockIdx.x * 256 + threadIdx.x; j < n4; j += (size_t)gridDim.x * 256) {
+    float4 w[kNC];
+    uint2 a[BT];
+#pragma unroll
+    for (int k = 0; k < kNC; ++k) w[k] = *reinterpret_cast<const float4*>(W + (size_t)k * F + 4 * j);
+#pragma unroll
+    for (int b = 0; b < BT; ++b) a[b] = ldg_stream8(p2 + (size_t)b * F + 4 * j);
+    float av[BT][4];
+#pragma unroll
+    for (int b = 0; b < BT; ++b) {
+      av[b][0] = bf16_lo(a[b].x); av[b][1] = bf16_hi(a[b].x);
+      av[b][2] = bf16_lo(a[b].y); av[b][3] = bf16_hi(a[b].y);
+    }
+    // dp2
+#pragma unroll
+    for (int b = 0; b < BT; ++b) {
+      float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int k = 0; k < kNC; ++k) {
+        s.x = fmaf(d[b][k], w[k].x, s.x); s.y = fmaf(d[b][k], w[k].y, s.y);
+        s.z = fmaf(d[b][k], w[k].z, s.z); s.w = fmaf(d[b][k], w[k].w, s.w);
+      }
+      *reinterpret_cast<uint2*>(dp2 + (size_t)b * F + 4 * j) =
+          make_uint2(pack_bf16x2(s.x, s.y), pack_bf16x2(s.z, s.w));
+    }
+    // dW (+ optional in-place SGD)
+#pragma unroll
+    for (int k = 0; k < kNC; ++k) {
+      float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int b = 0; b < BT; ++b) {
+        g.x = fmaf(d[b][k], av[b][0], g.x); g.y = fmaf(d[b][k], av[b][1], g.y);
+        g.z = fmaf(d[b][k], av[b][2], g.z); g.w = fmaf(d[b][k], av[b][3], g.w);
+      }
+      if (dW) {
+        float4* gp = reinterpret_cast<float4*>(dW + (size_t)k * F + 4 * j);
+        float4 o = make_float4(g.x * gscale, g.y * gscale, g.z * gscale, g.w * gscale);
+        if (accumulate) { float4 prev = *gp; o.x += prev.x; o.y += prev.y; o.z += prev.z; o.w += prev.w; }
+        *gp = o;
+      }
+      if (lr != 0.f) {
+        float4 o = make_float4(fmaf(-lr, g.x, w[k].x), fmaf(-lr, g.y, w[k].y),
+                               fmaf(-lr, g.z, w[k].z), fmaf(-lr, g.w, w[k].w));
+        *reinterpret_cast<float4*>(W + (size_t)k * F + 4 * j) = o;
+      }
+    }
+  }
+}
+
+// K14: p -= lr * g (vectorised; n need not be a multiple of 4).
+__global__ void sgd_kernel(float* __restrict__ p, const float* __restrict__ g, size_t n, float lr) {
+  const size_t n4 = n / 4;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
+    float4 pv = reinterpret_cast<float4*>(p)[i];
+    const float4 gv = reinterpret_cast<const float4*>(g)[i];
+    pv.x = fmaf(-lr, gv.x, pv.x); pv.y = fmaf(-lr, gv.y, pv.y);
+    pv.z = fmaf(-lr, gv.z, pv.z); pv.w = fmaf(-lr, gv.w, pv.w);
+    reinterpret_cast<float4*>(p)[i] = pv;
+  }
+  if (blockIdx.x == 0 && threadIdx.x < (n & 3)) {
+    size_t i = n4 * 4 + threadIdx.x;
+    p[i] = fmaf(-lr, g[i], p[i]);
+  }
+}
+
+// fp32 NCHW-flatten <-> internal HWC-flatten permutation of fc.weight, used by
+// checkpoint import/export (state_dict parity) and by the
+// torch-module view of the engine.  dst[k][ (y*Wd + x)*C + c ] = src[k][ (c*Hd + y)*Wd + x ]
+__global__ void fcw_chw_to_hwc_kernel(const float* __restrict__ src, float* __restrict__ dst,
+                                      int C, int Hd, int Wd, int to_hwc) {
+  const size_t F = (size_t)C * Hd * Wd;
+  const size_t total = (size_t)kNC * F;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const size_t k = i / F, j = i % F;        // j indexes the HWC side
+    const int c = (int)(j % C);
+    const size_t pix = j / C;
+    const size_t chw = (size_t)c * Hd * Wd + pix;
+    if (to_hwc) dst[k * F + j] = src[k * F + chw];
+    else dst[k * F + chw] = src[k * F + j];
+  }
+}
+
+// bf16 NHWC <-> fp32 NCHW activations (test / interop helper; not on the hot path)
+__global__ void nhwc_bf16_to_nchw_f32_kernel(const __nv_bfloat16* __restrict__ src, float* __restrict__ dst,
+                                             int B, int C, int H, int W) {
+  const size_t total = (size_t)B * C * H * W;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i % C);
+    size_t pix = i / C;
+    const int x = (int)(pix % W); pix /= W;
+    const int y = (int)(pix % H);
+    const int b = (int)(pix / H);
+    dst[(((size_t)b * C + c) * H + y) * W + x] = __bfloat162float(src[i]);
+  }
+}
+__global__ void nchw_f32_to_nhwc_bf16_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst,
+                                             int B, int C, int H, int W) {
+  const size_t total = (size_t)B * C * H * W;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i % C);
+    size_t pix = i / C;
+    const int x = (int)(pix % W); pix /= W;
+    const int y = (int)(pix % H);
+    const int b = (int)(pix / H);
+    dst[i] = __float2bfloat16_rn(src[(((size_t)b * C + c) * H + y) * W + x]);
+  }
+}
+
+inline int grid_for(size_t work, int block, int max_blocks) {
+  size_t g = (work + block - 1) / block;
+  if (g < 1) g = 1;
+  if (g > (size_t)max_blocks) g = max_blocks;
+  return (int)g;
+}
+
+}  // namespace
+
+// ============================================================ C ABI wrappers =
+// (declarations + reference citations: include/b200dp.h)
+
+B200_API int b200_resize_pil_bilinear(const void* src_u8, int B, int sh, int sw, const void* xtab,
+                                      const void* ytab, void* dst_f32, int H, int W, void* stream) {
+  dim3 grid((W + 255) / 256, H, B);
+  resize_pil_bilinear_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(
+      (const uint8_t*)src_u8, sh, sw, (const int*)xtab, (const int*)ytab, (float*)dst_f32, H, W);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+B200_API int b200_conv1_fwd_grid() { return b200_num_sms() * 4; }
+
+B200_API int b200_conv1_fwd(const void* in_f32, const void* w1, const void* b1, void* x1_bf16,
+                            void* partials, int B, int H, int W, void* stream) {
+  B200_CHECK(H % 4 == 0 && W % 4 == 0, "conv1_fwd: H and W must be multiples of 4 (got %d x %d)", H, W);
+  cudaStream_t s = (cudaStream_t)stream;
+  B200_CUDA(cudaMemcpyToSymbolAsync(c_w1, w1, sizeof(float) * kC1 * kTaps, 0, cudaMemcpyDeviceToDevice, s));
+  B200_CUDA(cudaMemcpyToSymbolAsync(c_b1, b1, sizeof(float) * kC1, 0, cudaMemcpyDeviceToDevice, s));
+  const int tilesX = (W + kT1W - 1) / kT1W, tilesY = (H + kT1H - 1) / kT1H;
+  conv1_fwd_kernel<<<b200_conv1_fwd_grid(), 256, 0, s>>>((const float*)in_f32, (__nv_bfloat16*)x1_bf16,
+                                                         (float*)partials, B, H, W, tilesX, tilesY);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+B200_API int b200_bn_finalize(const void* partials, int nparts, int C, double count, const void* gamma,
+                              const void* beta, void* running_mean, void* running_var, void* nbt,
+                              float momentum, float eps, void* out, void* stream) {
+  B200_CHECK(C <= 32, "bn_finalize: C must be <= 32");
+  bn_finalize_kernel<<<1, 32 * C, 0, (cudaStream_t)stream>>>(
+      (const float*)partials, nparts, C, count, (const float*)gamma, (const float*)beta,
+      (float*)running_mean, (float*)running_var, (long long*)nbt, momentum, eps, (float*)out);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+B200_API int b200_bn_relu_pool(const void* x, const void* bn, void* p, int B, int H, int W, int C, void* stream) {
+  B200_CHECK(H % 2 == 0 && W % 2 == 0, "bn_relu_pool: H and W must be even");
+  const size_t work = (size_t)B * (H / 2) * (W / 2) * (C / 8);
+  const int grid = grid_for(work, 256, b200_num_sms() * 16);
+  cudaStream_t s = (cudaStream_t)stream;
+  if (C == 16) bn_relu_pool_kernel<16><<<grid, 256, 0, s>>>((const __nv_bfloat16*)x, (const float*)bn, (__nv_bfloat16*)p, B, H, W);
+  else if (C == 32) bn_relu_pool_kernel<32><<<grid, 256, 0, s>>>((const __nv_bfloat16*)x, (const float*)bn, (__nv_bfloat16*)p, B, H, W);
+  else return b200_fail(-2, "bn_relu_pool: C must be 16 or 32");
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+B200_API int b200_pool_bn_bwd_grid() { return b200_num_sms() * 8; }
+
+// mode 0: stats -> partials [grid][2C];  mode 1: apply -> dx
+B200_API int b200_pool_bn_bwd(const void* x, const void* dp, const void* bn, const void* red, void* partials,
+                              void* dx, int B, int H, int W, int C, int mode, void* stream) {
+  B200_CHECK(H % 2 == 0 && W % 2 == 0, "pool_bn_bwd: H and W must be even");
+  const int grid = b200_pool_bn_bwd_grid();
+  cudaStream_t s = (cudaStream_t)stream;
+#define B200_PBB(CC, MM)                                                                              \
+  pool_bn_bwd_kernel<CC, MM><<<grid, 256, 0, s>>>((const __nv_bfloat16*)x, (const __nv_bfloat16*)dp,  \
+                                                  (const float*)bn, (const float*)red, (float*)partials, \
+                                                  (__nv_bfloat16*)dx, B, H, W)
+  if (C == 16 && mode == 0) B200_PBB(16, 0);
+  else if (C == 16 && mode == 1) B200_PBB(16, 1);
+  else if (C == 32 && mode == 0) B200_PBB(32, 0);
+  else if (C == 32 && mode == 1) B200_PBB(32, 1);
+  else return b200_fail(-2, "pool_bn_bwd: unsupported C/mode");
+#undef B200_PBB
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+B200_API int b200_bn_bwd_finalize(const void* partials, int nparts, int C, double count, void* red,
+                                  void* dgamma, void* dbeta, float gscale, void* stream) {
+  B200_CHECK(C <= 32, "bn_bwd_finalize: C must be <= 32");
+  bn_bwd_finalize_kernel<<<1, 32 * C, 0, (cudaStream_t)stream>>>((const float*)partials, nparts, C, count,
+                                                                  (float*)red, (float*)dgamma, (float*)dbeta, gscale);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+B200_API int b200_conv1_wgrad_grid() { return b200_num_sms(); }
+
+B200_API int b200_conv1_wgrad(const void* in_f32, const void* x1, const void* dp1, const void* bn,
+                              const void* red, void* partials, void* dw1, int B, int H, int W,
+                              float gscale, void* stream) {
+  B200_CHECK(H % 2 == 0 && W % 2 == 0, "conv1_wgrad: H and W must be even");
+  cudaStream_t s = (cudaStream_t)stream;
+  const int tilesX = (W + kWgT - 1) / kWgT, tilesY = (H + kWgT - 1) / kWgT;
+  const int grid = b200_conv1_wgrad_grid();
+  conv1_wgrad_kernel<<<grid, 256, 0, s>>>((const float*)in_f32, (const __nv_bfloat16*)x1,
+                                          (const __nv_bfloat16*)dp1, (const float*)bn, (const float*)red,
+                                          (float*)partials, B, H, W, tilesX, tilesY);
+  B200_LAUNCH_CHECK();
+  reduce_partials_kernel<<<(400 + 127) / 128, 128, 0, s>>>((const float*)partials, grid, 400, (float*)dw1, gscale);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+B200_API int b200_reduce_partials(const void* partials, int nparts, int len, void* out, float scale, void* stream) {
+  reduce_partials_kernel<<<(len + 127) / 128, 128, 0, (cudaStream_t)stream>>>((const float*)partials, nparts, len,
+                                                                              (float*)out, scale);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+B200_API int b200_fc_grid() { return b200_num_sms() * 4; }
+
+// logits[bt][10] for a batch chunk of bt <= 8 rows.
+B200_API int b200_fc_fwd(const void* p2, const void* W, const void* bias, void* partials, void* logits,
+                         int bt, size_t F, void* stream) {
+  B200_CHECK(bt >= 1 && bt <= 8, "fc_fwd: batch chunk must be 1..8 (got %d)", bt);
+  B200_CHECK(F % 4 == 0, "fc_fwd: F must be a multiple of 4");
+  cudaStream_t s = (cudaStream_t)stream;
+  const int grid = b200_fc_grid();
+  switch (bt) {
+#define B200_FCF(N) case N: fc_fwd_kernel<N><<<grid, 256, 0, s>>>((const __nv_bfloat16*)p2, (const float*)W, (float*)partials, F); break;
+    B200_FCF(1) B200_FCF(2) B200_FCF(3) B200_FCF(4) B200_FCF(5) B200_FCF(6) B200_FCF(7) B200_FCF(8)
+#undef B200_FCF
+  }
+  B200_LAUNCH_CHECK();
+  fc_reduce_kernel<<<1, 128, 0, s>>>((const float*)partials, grid, bt * kNC, (const float*)bias, (float*)logits);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+B200_API int b200_cross_entropy(const void* logits, const void* labels_i64, int B, void* loss, void* dlogits,
+                                void* dbias, float gscale, void* stream) {
+  ce_kernel<<<1, 256, 0, (cudaStream_t)stream>>>((const float*)logits, (const long long*)labels_i64, B,
+                                                  (float*)loss, (float*)dlogits, (float*)dbias, gscale);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+B200_API int b200_fc_bwd(const void* dlogits, const void* p2, void* W, void* dW, void* dp2, int bt, size_t F,
+                         float lr, int accumulate, float gscale, void* stream) {
+  B200_CHECK(bt >= 1 && bt <= 8, "fc_bwd: batch chunk must be 1..8 (got %d)", bt);
+  B200_CHECK(F % 4 == 0, "fc_bwd: F must be a multiple of 4");
+  cudaStream_t s = (cudaStream_t)stream;
+  const int grid = b200_fc_grid();
+  switch (bt) {
+#define B200_FCB(N) case N: fc_bwd_kernel<N><<<grid, 256, 0, s>>>((const float*)dlogits, (const __nv_bfloat16*)p2, (float*)W, (float*)dW, (__nv_bfloat16*)dp2, F, lr, accumulate, gscale); break;
+    B200_FCB(1) B200_FCB(2) B200_FCB(3) B200_FCB(4) B200_FCB(5) B200_FCB(6) B200_FCB(7) B200_FCB(8)
+#undef B200_FCB
+  }
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+B200_API int b200_sgd(void* p, const void* g, size_t n, float lr, void* stream) {
+  const int grid = grid_for(n / 4 + 1, 256, b200_num_sms() * 8);
+  sgd_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((float*)p, (const float*)g, n, lr);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+B200_API int b200_fcw_permute(const void* src, void* dst, int C, int Hd, int Wd, int to_hwc, void* stream) {
+  const size_t total = (size_t)kNC * C * Hd * Wd;
+  const int grid = grid_for(total, 256, b200_num_sms() * 8);
+  fcw_chw_to_hwc_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((const float*)src, (float*)dst, C, Hd, Wd, to_hwc);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+B200_API int b200_nhwc_bf16_to_nchw_f32(const void* src, void* dst, int B, int C, int H, int W, void* stream) {
+  const int grid = grid_for((size_t)B * C * H * W, 256, b200_num_sms() * 8);
+  nhwc_bf16_to_nchw_f32_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)src, (float*)dst, B, C, H, W);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+B200_API int b200_nchw_f32_to_nhwc_bf16(const void* src, void* dst, int B, int C, int H, int W, void* stream) {
+  const int grid = grid_for((size_t)B * C * H * W, 256, b200_num_sms() * 8);
+  nchw_f32_to_nhwc_bf16_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((const float*)src, (__nv_bfloat16*)dst, B, C, H, W);
+  B200_LAUNCH_CHECK();
+  return 0;
+}

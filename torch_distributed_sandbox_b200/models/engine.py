@@ -1,0 +1,338 @@
+"""FusedConvNet - the B200-native training engine for the sandbox CNN.
+
+One object owns every parameter, buffer, activation and scratch tensor of the
+model (nothing is allocated inside a step) and runs the whole training step -
+resize, forward, loss, backward, optimizer - as ~22 hand-written sm_100a kernel
+launches on one stream, instead of the reference's autograd graph of cuDNN /
+ATen / cuBLAS calls (mnist_onegpu.py:63-74, mnist_distributed.py:85-97;
+SURVEY.md 3.5 and 2.5 K1-K15).
+
+Data flow (bf16 NHWC activations, fp32 parameters and statistics):
+
+    u8 28x28 --resize--> x fp32 [B,H,W]
+      --conv1 (FFMA, +BN1 stat partials)--> x1 [B,H,W,16]
+      --BN1+ReLU+pool--> p1 [B,H/2,W/2,16]
+      --conv2 (tcgen05, +BN2 stat partials)--> x2 [B,H/2,W/2,32]
+      --BN2+ReLU+pool--> p2 [B,H/4,W/4,32] == fc input (HWC flatten)
+      --fc (weight streaming) + cross-entropy--> loss, dlogits
+    backward: fc_bwd (dW | fused SGD, dp2) -> pool/ReLU/BN2 bwd (2 passes, arg-max
+      recomputed) -> conv2 wgrad + dgrad (tcgen05) -> BN1 stats -> fused
+      pool/ReLU/BN1-bwd + conv1 wgrad -> SGD.
+
+Gradient buffers are written IN PLACE over the activations they replace
+(dp2 over p2, dx2 over x2, dp1 over p1), so resident memory is ~0.58 GB/image at
+3000x3000 against ~2.4 GB/image retained by the reference: the
+"OOM workaround" headroom of README.md:9-15 on a 180 GB part.
+
+In data-parallel mode a ``comm`` object (parallel/ddp.py::EngineGradSync) is
+attached: fc_bwd then writes the 720 MB fc.weight gradient, pre-divided by the
+world size, straight into the symmetric-memory bucket and the all-reduce kernel
+runs on a side stream while the conv backward continues (K10 -> K16).
+"""
+from __future__ import annotations
+
+from collections import OrderedDict
+from typing import Optional, Sequence
+
+import torch
+import torch.nn.functional as F
+
+from .. import ops
+from ..data.resize import pil_bilinear_table
+from . import reference_net as rn
+
+# (state_dict key, shape) of the parameters kept in the "small" flat buffer, in order.
+SMALL_LAYOUT = (
+    ("layer1.0.weight", (16, 1, 5, 5)), ("layer1.0.bias", (16,)),
+    ("layer1.1.weight", (16,)), ("layer1.1.bias", (16,)),
+    ("layer2.0.weight", (32, 16, 5, 5)), ("layer2.0.bias", (32,)),
+    ("layer2.1.weight", (32,)), ("layer2.1.bias", (32,)),
+    ("fc.bias", (10,)),
+)
+
+
+def _numel(shape) -> int:
+    n = 1
+    for s in shape:
+        n *= s
+    return n
+
+
+SMALL_NUMEL = sum(_numel(s) for _, s in SMALL_LAYOUT)          # 13,354
+SMALL_ALLOC = (SMALL_NUMEL + 3) // 4 * 4
+
+
+class FusedConvNet:
+    """Fused training engine.  ``train_step(images, labels)`` returns the loss (0-dim CUDA tensor)."""
+
+    def __init__(self, image_shape: Sequence[int] = (3000, 3000), batch_size: int = 5,
+                 device: Optional[torch.device] = None, lr: float = 1e-4, seed: int = 0,
+                 init: str = "reference", conv_backend: str = "tc", fuse_fc_sgd: bool = True,
+                 fc_weight_storage: Optional[torch.Tensor] = None,
+                 fc_grad_storage: Optional[torch.Tensor] = None):
+        if not torch.cuda.is_available():
+            raise RuntimeError("FusedConvNet needs a CUDA device (sm_100a); use models.ConvNet on CPU")
+        H, W = (int(v) for v in image_shape)
+        if H % 4 or W % 4:
+            raise ValueError("image height/width must be multiples of 4 (two 2x2 pools)")
+        self.device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
+        self.H, self.W, self.B = H, W, int(batch_size)
+        self.image_shape = (H, W)
+        self.lr = float(lr)
+        self.conv_backend = conv_backend
+        self.fuse_fc_sgd = bool(fuse_fc_sgd)
+        self.F = rn.feature_size((H, W))
+        self.comm = None           # set by parallel.ddp for data-parallel runs
+        self.grad_scale = 1.0      # 1/world_size under DDP (fused into the producing kernels)
+        dev, B = self.device, self.B
+        f32 = dict(device=dev, dtype=torch.float32)
+        bf = dict(device=dev, dtype=torch.bfloat16)
+
+        with torch.cuda.device(dev):
+            # ---- parameters / buffers --------------------------------------
+            self.small = torch.zeros(SMALL_ALLOC, **f32)
+            self.small_grad = torch.zeros(SMALL_ALLOC, **f32)
+            self.params: "OrderedDict[str, torch.Tensor]" = OrderedDict()
+            self.grads: "OrderedDict[str, torch.Tensor]" = OrderedDict()
+            off = 0
+            for name, shape in SMALL_LAYOUT:
+                n = _numel(shape)
+                self.params[name] = self.small[off:off + n].view(shape)
+                self.grads[name] = self.small_grad[off:off + n].view(shape)
+                off += n
+            self.fcw = fc_weight_storage if fc_weight_storage is not None else torch.empty(10, self.F, **f32)
+            assert self.fcw.shape == (10, self.F) and self.fcw.dtype == torch.float32
+            self.fcw_grad = fc_grad_storage      # allocated lazily unless fused SGD covers it
+            self.bn_buf = {
+                1: dict(mean=torch.zeros(16, **f32), var=torch.ones(16, **f32),
+                        nbt=torch.zeros((), device=dev, dtype=torch.int64)),
+                2: dict(mean=torch.zeros(32, **f32), var=torch.ones(32, **f32),
+                        nbt=torch.zeros((), device=dev, dtype=torch.int64)),
+            }
+            # ---- activations (gradients alias them) -------------------------
+            self.x = torch.empty(B, H, W, **f32)
+            self.x1 = torch.empty(B, H, W, 16, **bf)
+            self.p1 = torch.empty(B, H // 2, W // 2, 16, **bf)
+            self.x2 = torch.empty(B, H // 2, W // 2, 32, **bf)
+            self.p2 = torch.empty(B, H // 4, W // 4, 32, **bf)
+            self.dp2, self.dx2, self.dp1 = self.p2, self.x2, self.p1     # in-place gradients
+            # ---- scratch ------------------------------------------------------
+            self.g_c1, self.g_wg1 = ops.conv1_fwd_grid(), ops.conv1_wgrad_grid()
+            self.g_tc, self.g_pbb, self.g_fc = ops.conv_tc_max_grid(), ops.pool_bn_bwd_grid(), ops.fc_grid()
+            self.part_c1 = torch.empty(self.g_c1, 32, **f32)
+            self.part_c2 = torch.empty(self.g_tc, 64, **f32)
+            self.part_bwd = torch.empty(self.g_pbb, 64, **f32)
+            self.part_wg1 = torch.empty(self.g_wg1, 400, **f32)
+            self.part_wg2 = torch.empty(self.g_tc, 32 * 16 * 25, **f32)
+            self.part_fc = torch.empty(self.g_fc, 80, **f32)
+            self.bn1 = torch.zeros(4, 16, **f32)
+            self.bn2 = torch.zeros(4, 32, **f32)
+            self.red1 = torch.zeros(2, 16, **f32)
+            self.red2 = torch.zeros(2, 32, **f32)
+            self.logits = torch.zeros(B, 10, **f32)
+            self.dlogits = torch.zeros(B, 10, **f32)
+            self.loss = torch.zeros((), **f32)
+            self._tabs = {}
+            self._u8 = None
+            self._labels = torch.zeros(B, device=dev, dtype=torch.int64)
+
+        if init == "reference":
+            self.load_state_dict(rn.reference_init((H, W), seed=seed).state_dict())
+        elif init == "random":
+            g = torch.Generator(device="cpu").manual_seed(seed)
+            sd = OrderedDict()
+            for name, shape in SMALL_LAYOUT:
+                fan = _numel(shape[1:]) if len(shape) > 1 else 1
+                if name.endswith("1.weight"):      # BN gamma
+                    sd[name] = 1.0 + 0.1 * torch.randn(shape, generator=g)
+                elif len(shape) == 1:
+                    sd[name] = 0.1 * torch.randn(shape, generator=g)
+                else:
+                    sd[name] = torch.randn(shape, generator=g) / fan ** 0.5
+            sd["fc.weight"] = torch.randn(10, self.F, generator=g) / self.F ** 0.5
+            self.load_state_dict(sd, strict=False)
+        elif init != "empty":
+            raise ValueError(f"unknown init {init!r}")
+
+    # ------------------------------------------------------------ checkpoint --
+    def state_dict(self, prefix: str = "") -> "OrderedDict[str, torch.Tensor]":
+        """torch ``state_dict`` with the reference's 16 keys; ``fc.weight`` is
+        converted from the internal HWC-flatten order back to the reference's CHW order."""
+        out = OrderedDict()
+        with torch.cuda.device(self.device):
+            fcw_chw = torch.empty_like(self.fcw)
+            ops.fcw_permute(self.fcw, fcw_chw, 32, self.H // 4, self.W // 4, to_hwc=False)
+        for k in rn.STATE_KEYS:
+            if k == "fc.weight":
+                v = fcw_chw
+            elif k in self.params:
+                v = self.params[k].clone()
+            else:
+                layer = 1 if k.startswith("layer1") else 2
+                field = {"running_mean": "mean", "running_var": "var", "num_batches_tracked": "nbt"}[k.split(".")[-1]]
+                v = self.bn_buf[layer][field].clone()
+            out[prefix + k] = v
+        return out
+
+    def load_state_dict(self, sd, strict: bool = True) -> None:
+        """Accepts a reference/torch ``state_dict`` (optionally with DDP's ``module.`` prefix)."""
+        sd = {(k[7:] if k.startswith("module.") else k): v for k, v in sd.items()}
+        missing = [k for k in rn.STATE_KEYS if k not in sd]
+        if strict and missing:
+            raise KeyError(f"state_dict is missing {missing}")
+        with torch.cuda.device(self.device), torch.no_grad():
+            for k, v in sd.items():
+                if k == "fc.weight":
+                    if tuple(v.shape) != (10, self.F):
+                        raise ValueError(f"fc.weight shape {tuple(v.shape)} != {(10, self.F)}")
+                    src = v.to(self.device, torch.float32).contiguous()
+                    ops.fcw_permute(src, self.fcw, 32, self.H // 4, self.W // 4, to_hwc=True)
+                    torch.cuda.current_stream().synchronize()
+                elif k in self.params:
+                    self.params[k].copy_(v.to(self.device, torch.float32))
+                elif k in rn.STATE_KEYS:
+                    layer = 1 if k.startswith("layer1") else 2
+                    field = {"running_mean": "mean", "running_var": "var", "num_batches_tracked": "nbt"}[k.split(".")[-1]]
+                    self.bn_buf[layer][field].copy_(v.to(self.device))
+                elif strict:
+                    raise KeyError(f"unexpected key {k}")
+
+    def named_gradients(self) -> "OrderedDict[str, torch.Tensor]":
+        """Gradients of the last backward in the reference's layouts (tests / generic DDP)."""
+        out = OrderedDict((k, v.clone()) for k, v in self.grads.items())
+        if self.fcw_grad is not None:
+            g = torch.empty_like(self.fcw_grad)
+            ops.fcw_permute(self.fcw_grad, g, 32, self.H // 4, self.W // 4, to_hwc=False)
+            out["fc.weight"] = g
+        return out
+
+    # ------------------------------------------------------------------ input --
+    def set_input(self, images: torch.Tensor) -> None:
+        """uint8 [B,h,w] raw digits (resized on the GPU, K2) or float [B,1,H,W] / [B,H,W]."""
+        if images.dtype == torch.uint8:
+            if images.dim() == 4:
+                images = images[:, 0]
+            assert images.shape[0] == self.B, f"batch {images.shape[0]} != engine batch {self.B}"
+            sh, sw = int(images.shape[-2]), int(images.shape[-1])
+            key = (sh, sw)
+            if key not in self._tabs:
+                self._tabs[key] = (torch.from_numpy(pil_bilinear_table(sw, self.W)).to(self.device),
+                                   torch.from_numpy(pil_bilinear_table(sh, self.H)).to(self.device))
+            if self._u8 is None or self._u8.shape != images.shape:
+                self._u8 = torch.empty(images.shape, device=self.device, dtype=torch.uint8)
+            self._u8.copy_(images, non_blocking=True)
+            xt, yt = self._tabs[key]
+            ops.resize_pil_bilinear(self._u8, xt, yt, self.x)
+        else:
+            if images.dim() == 4:
+                images = images[:, 0]
+            assert tuple(images.shape) == (self.B, self.H, self.W), f"bad input shape {tuple(images.shape)}"
+            self.x.copy_(images, non_blocking=True)
+
+    # ---------------------------------------------------------------- forward --
+    def forward(self, images: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """Train-mode forward (batch statistics, running stats updated). Returns logits [B,10]."""
+        if images is not None:
+            self.set_input(images)
+        P, B, H, W = self.params, self.B, self.H, self.W
+        ops.conv1_fwd(self.x, P["layer1.0.weight"], P["layer1.0.bias"], self.x1, self.part_c1)
+        ops.bn_finalize(self.part_c1, self.g_c1, 16, B * H * W, P["layer1.1.weight"], P["layer1.1.bias"],
+                        self.bn_buf[1]["mean"], self.bn_buf[1]["var"], self.bn_buf[1]["nbt"], self.bn1)
+        ops.bn_relu_pool(self.x1, self.bn1, self.p1)
+        if self.conv_backend == "tc":
+            nparts = ops.conv2_fwd_tc(self.p1, P["layer2.0.weight"], P["layer2.0.bias"], self.x2, self.part_c2)
+        else:
+            nparts = self._conv2_fwd_torch()
+        ops.bn_finalize(self.part_c2, nparts, 32, B * (H // 2) * (W // 2), P["layer2.1.weight"],
+                        P["layer2.1.bias"], self.bn_buf[2]["mean"], self.bn_buf[2]["var"], self.bn_buf[2]["nbt"],
+                        self.bn2)
+        ops.bn_relu_pool(self.x2, self.bn2, self.p2)
+        p2 = self.p2.view(B, self.F)
+        for b0 in range(0, B, 8):
+            b1 = min(B, b0 + 8)
+            ops.fc_fwd(p2[b0:b1], self.fcw, P["fc.bias"], self.part_fc, self.logits[b0:b1])
+        return self.logits
+
+    # --------------------------------------------------------------- backward --
+    def loss_backward(self, labels: torch.Tensor) -> torch.Tensor:
+        """Cross-entropy (mean) + full backward.  Leaves gradients in ``self.grads`` /
+        ``self.fcw_grad``; with ``fuse_fc_sgd`` and no comm, fc.weight is updated in place here."""
+        P, G, B, H, W = self.params, self.grads, self.B, self.H, self.W
+        gs = self.grad_scale
+        self._labels.copy_(labels, non_blocking=True)
+        ops.cross_entropy(self.logits, self._labels, self.loss, self.dlogits, G["fc.bias"], gs)
+        fused = self.fuse_fc_sgd and self.comm is None and B <= 8
+        if not fused and self.fcw_grad is None:
+            self.fcw_grad = torch.empty_like(self.fcw)
+        p2 = self.p2.view(B, self.F)
+        dp2 = self.dp2.view(B, self.F)
+        for b0 in range(0, B, 8):
+            b1 = min(B, b0 + 8)
+            ops.fc_bwd(self.dlogits[b0:b1], p2[b0:b1], self.fcw, None if fused else self.fcw_grad, dp2[b0:b1],
+                       lr=self.lr if fused else 0.0, accumulate=b0 > 0, gscale=gs)
+        self._fc_fused_done = fused
+        if self.comm is not None:
+            self.comm.fc_grad_ready(self)            # async all-reduce of the 720 MB bucket
+        # ---- layer 2
+        H2, W2 = H // 2, W // 2
+        ops.pool_bn_bwd(self.x2, self.dp2, self.bn2, self.red2, self.part_bwd, None, mode=0)
+        ops.bn_bwd_finalize(self.part_bwd, self.g_pbb, 32, B * H2 * W2, self.red2, G["layer2.1.weight"],
+                            G["layer2.1.bias"], gs)
+        ops.pool_bn_bwd(self.x2, self.dp2, self.bn2, self.red2, None, self.dx2, mode=1)
+        if self.conv_backend == "tc":
+            ops.conv2_wgrad_tc(self.p1, self.dx2, self.part_wg2, G["layer2.0.weight"], gs)
+            ops.conv2_dgrad_tc(self.dx2, P["layer2.0.weight"], self.dp1)
+        else:
+            self._conv2_bwd_torch(gs)
+        G["layer2.0.bias"].zero_()      # a bias feeding BatchNorm has an analytically zero gradient
+        # ---- layer 1
+        ops.pool_bn_bwd(self.x1, self.dp1, self.bn1, self.red1, self.part_bwd, None, mode=0)
+        ops.bn_bwd_finalize(self.part_bwd, self.g_pbb, 16, B * H * W, self.red1, G["layer1.1.weight"],
+                            G["layer1.1.bias"], gs)
+        ops.conv1_wgrad(self.x, self.x1, self.dp1, self.bn1, self.red1, self.part_wg1, G["layer1.0.weight"], gs)
+        G["layer1.0.bias"].zero_()
+        return self.loss
+
+    def step(self) -> None:
+        """SGD (lr, no momentum / weight decay: mnist_onegpu.py:49) on every parameter."""
+        if self.comm is not None:
+            self.comm.small_grads_ready(self)        # one-shot all-reduce of the 53 KB bucket
+        ops.sgd(self.small, self.small_grad, self.lr)
+        if not self._fc_fused_done:
+            if self.comm is not None:
+                self.comm.wait_fc_grad(self)
+            ops.sgd(self.fcw, self.fcw_grad, self.lr)
+
+    def train_step(self, images: torch.Tensor, labels: torch.Tensor) -> torch.Tensor:
+        self.forward(images)
+        self.loss_backward(labels)
+        self.step()
+        return self.loss
+
+    __call__ = forward
+
+    # ------------------------------------------------ torch fallbacks (debug) --
+    def _conv2_fwd_torch(self) -> int:
+        P = self.params
+        x = self.p1.permute(0, 3, 1, 2).float()
+        w = P["layer2.0.weight"].to(torch.bfloat16).float()
+        y = F.conv2d(x, w, P["layer2.0.bias"], padding=2)
+        self.x2.copy_(y.permute(0, 2, 3, 1))
+        r = self.x2.float()
+        self.part_c2.zero_()
+        self.part_c2[0, :32] = r.sum(dim=(0, 1, 2))
+        self.part_c2[0, 32:] = (r * r).sum(dim=(0, 1, 2))
+        return 1
+
+    def _conv2_bwd_torch(self, gs: float) -> None:
+        P, G = self.params, self.grads
+        dy = self.dx2.permute(0, 3, 1, 2).float()
+        x = self.p1.permute(0, 3, 1, 2).float()
+        w = P["layer2.0.weight"].to(torch.bfloat16).float()
+        G["layer2.0.weight"].copy_(torch.nn.grad.conv2d_weight(x, w.shape, dy, padding=2) * gs)
+        dxin = torch.nn.grad.conv2d_input(x.shape, w, dy, padding=2)
+        self.dp1.copy_(dxin.permute(0, 2, 3, 1))
+
+    def activation_bytes(self) -> int:
+        ts = (self.x, self.x1, self.p1, self.x2, self.p2)
+        return sum(t.numel() * t.element_size() for t in ts)

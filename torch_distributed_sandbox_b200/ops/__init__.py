@@ -1,0 +1,218 @@
+"""Python front-ends of the hand-written sm_100a kernels (C ABI in ``include/b200dp.h``).
+
+Every function takes torch CUDA tensors, launches on torch's *current* stream and
+returns nothing (outputs are pre-allocated by the caller: the engine owns all
+activation memory so a training step allocates nothing).  ``LAUNCHES`` counts
+kernels launched by this module; ``bench.py`` reports it as ``gpu_launches``.
+
+Layouts: activations are bf16 **NHWC**, weights/grads fp32 in the reference's
+``state_dict`` layouts except ``fc.weight`` which is kept in HWC-flatten order
+internally (``fcw_permute`` converts for checkpoints).
+"""
+from __future__ import annotations
+
+import ctypes
+from ctypes import c_double, c_float, c_int, c_size_t, c_void_p
+
+import torch
+
+from .. import _native
+
+LAUNCHES = 0
+
+
+def _count(n: int) -> None:
+    global LAUNCHES
+    LAUNCHES += n
+
+
+def _p(t) -> c_void_p:
+    return c_void_p(0 if t is None else t.data_ptr())
+
+
+def _stream() -> c_void_p:
+    return c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _lib():
+    lib = _native.cuda()
+    if not getattr(lib, "_b200_ops_bound", False):
+        lib.b200_fc_fwd.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_size_t, c_void_p]
+        lib.b200_fc_bwd.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_size_t,
+                                    c_float, c_int, c_float, c_void_p]
+        lib.b200_sgd.argtypes = [c_void_p, c_void_p, c_size_t, c_float, c_void_p]
+        lib.b200_bn_finalize.argtypes = [c_void_p, c_int, c_int, c_double, c_void_p, c_void_p, c_void_p, c_void_p,
+                                         c_void_p, c_float, c_float, c_void_p, c_void_p]
+        lib.b200_bn_bwd_finalize.argtypes = [c_void_p, c_int, c_int, c_double, c_void_p, c_void_p, c_void_p,
+                                             c_float, c_void_p]
+        lib.b200_conv1_wgrad.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                         c_int, c_int, c_int, c_float, c_void_p]
+        lib.b200_conv2_wgrad_tc.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_float,
+                                            c_void_p]
+        lib.b200_conv2_fwd_tc.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int,
+                                          ctypes.POINTER(c_int), c_void_p]
+        lib.b200_conv2_dgrad_tc.argtypes = [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]
+        lib.b200_cross_entropy.argtypes = [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_float,
+                                           c_void_p]
+        lib.b200_reduce_partials.argtypes = [c_void_p, c_int, c_int, c_void_p, c_float, c_void_p]
+        lib.b200_l2_flush.argtypes = [c_void_p, c_size_t, c_void_p]
+        lib._b200_ops_bound = True
+    return lib
+
+
+def sm_count() -> int:
+    return int(_lib().b200_sm_count())
+
+
+# ---- grid sizes (callers size their partial buffers with these) ------------
+def conv1_fwd_grid() -> int:
+    return int(_lib().b200_conv1_fwd_grid())
+
+
+def conv1_wgrad_grid() -> int:
+    return int(_lib().b200_conv1_wgrad_grid())
+
+
+def conv_tc_max_grid() -> int:
+    return int(_lib().b200_conv_tc_max_grid())
+
+
+def pool_bn_bwd_grid() -> int:
+    return int(_lib().b200_pool_bn_bwd_grid())
+
+
+def fc_grid() -> int:
+    return int(_lib().b200_fc_grid())
+
+
+# ---- kernels ----------------------------------------------------------------
+def resize_pil_bilinear(src_u8, xtab, ytab, dst_f32):
+    """uint8 [B,h,w] -> fp32 [B,H,W]; bit-exact PIL bilinear + ToTensor (K1/K2)."""
+    B, sh, sw = src_u8.shape
+    H, W = dst_f32.shape[-2:]
+    _native.check(_lib().b200_resize_pil_bilinear(_p(src_u8), B, sh, sw, _p(xtab), _p(ytab), _p(dst_f32), H, W,
+                                                  _stream()), "resize_pil_bilinear")
+    _count(1)
+
+
+def conv1_fwd(x_f32, w1, b1, x1_bf16, partials):
+    """K3: conv(1->16, 5x5, pad 2) + BN-stat partials. x [B,H,W] fp32 -> x1 [B,H,W,16] bf16."""
+    B, H, W = x_f32.shape
+    _native.check(_lib().b200_conv1_fwd(_p(x_f32), _p(w1), _p(b1), _p(x1_bf16), _p(partials), B, H, W, _stream()),
+                  "conv1_fwd")
+    _count(1)
+
+
+def bn_finalize(partials, nparts, C, count, gamma, beta, running_mean, running_var, nbt, out, momentum=0.1,
+                eps=1e-5):
+    """K4: batch stats -> [scale|shift|mean|rstd] + running-stat update."""
+    _native.check(_lib().b200_bn_finalize(_p(partials), nparts, C, float(count), _p(gamma), _p(beta),
+                                          _p(running_mean), _p(running_var), _p(nbt), momentum, eps, _p(out),
+                                          _stream()), "bn_finalize")
+    _count(1)
+
+
+def bn_relu_pool(x_bf16, bn, p_bf16):
+    """K5/K7: BN-apply + ReLU + 2x2 max-pool, bf16 NHWC -> bf16 NHWC."""
+    B, H, W, C = x_bf16.shape
+    _native.check(_lib().b200_bn_relu_pool(_p(x_bf16), _p(bn), _p(p_bf16), B, H, W, C, _stream()), "bn_relu_pool")
+    _count(1)
+
+
+def pool_bn_bwd(x_bf16, dp_bf16, bn, red, partials, dx_bf16, mode):
+    """K11/K13: mode 0 = reduction partials, mode 1 = dense dx (may alias x)."""
+    B, H, W, C = x_bf16.shape
+    _native.check(_lib().b200_pool_bn_bwd(_p(x_bf16), _p(dp_bf16), _p(bn), _p(red), _p(partials), _p(dx_bf16), B, H,
+                                          W, C, mode, _stream()), "pool_bn_bwd")
+    _count(1)
+
+
+def bn_bwd_finalize(partials, nparts, C, count, red, dgamma, dbeta, gscale=1.0):
+    _native.check(_lib().b200_bn_bwd_finalize(_p(partials), nparts, C, float(count), _p(red), _p(dgamma),
+                                              _p(dbeta), gscale, _stream()), "bn_bwd_finalize")
+    _count(1)
+
+
+def conv1_wgrad(x_f32, x1_bf16, dp1_bf16, bn, red, partials, dw1, gscale=1.0):
+    """K13: fused pool1/ReLU1/BN1 backward + conv1 weight gradient."""
+    B, H, W = x_f32.shape
+    _native.check(_lib().b200_conv1_wgrad(_p(x_f32), _p(x1_bf16), _p(dp1_bf16), _p(bn), _p(red), _p(partials),
+                                          _p(dw1), B, H, W, gscale, _stream()), "conv1_wgrad")
+    _count(2)
+
+
+def conv2_fwd_tc(p1_bf16, w2, b2, x2_bf16, partials) -> int:
+    """K6 (tcgen05): conv(16->32) + BN-stat partials. Returns the number of partial rows."""
+    B, H, W, _ = p1_bf16.shape
+    n = c_int(0)
+    _native.check(_lib().b200_conv2_fwd_tc(_p(p1_bf16), _p(w2), _p(b2), _p(x2_bf16), _p(partials), B, H, W,
+                                           ctypes.byref(n), _stream()), "conv2_fwd_tc")
+    _count(1)
+    return n.value
+
+
+def conv2_dgrad_tc(dx2_bf16, w2, dp1_bf16):
+    """K12a (tcgen05): data gradient of conv2, [B,H,W,32] -> [B,H,W,16]."""
+    B, H, W, _ = dx2_bf16.shape
+    _native.check(_lib().b200_conv2_dgrad_tc(_p(dx2_bf16), _p(w2), _p(dp1_bf16), B, H, W, _stream()),
+                  "conv2_dgrad_tc")
+    _count(1)
+
+
+def conv2_wgrad_tc(p1_bf16, dx2_bf16, partials, dw2, gscale=1.0):
+    """K12b (tcgen05): weight gradient of conv2 -> [32,16,5,5] fp32."""
+    B, H, W, _ = p1_bf16.shape
+    _native.check(_lib().b200_conv2_wgrad_tc(_p(p1_bf16), _p(dx2_bf16), _p(partials), _p(dw2), B, H, W, gscale,
+                                             _stream()), "conv2_wgrad_tc")
+    _count(2)
+
+
+def fc_fwd(p2_bf16, W, bias, partials, logits):
+    """K8: logits for a batch chunk of <= 8 rows. p2 [bt,F] bf16, W [10,F] fp32."""
+    bt, F = p2_bf16.shape[0], p2_bf16[0].numel()
+    _native.check(_lib().b200_fc_fwd(_p(p2_bf16), _p(W), _p(bias), _p(partials), _p(logits), bt, F, _stream()),
+                  "fc_fwd")
+    _count(2)
+
+
+def cross_entropy(logits, labels, loss, dlogits, dbias, gscale=1.0):
+    """K9: mean CE loss + dlogits + dbias in one block."""
+    _native.check(_lib().b200_cross_entropy(_p(logits), _p(labels), logits.shape[0], _p(loss), _p(dlogits),
+                                            _p(dbias), gscale, _stream()), "cross_entropy")
+    _count(1)
+
+
+def fc_bwd(dlogits, p2_bf16, W, dW, dp2_bf16, lr=0.0, accumulate=False, gscale=1.0):
+    """K10(+K14): dW (optional), dp2 and optional in-place SGD on W, one streaming pass."""
+    bt, F = p2_bf16.shape[0], p2_bf16[0].numel()
+    _native.check(_lib().b200_fc_bwd(_p(dlogits), _p(p2_bf16), _p(W), _p(dW), _p(dp2_bf16), bt, F, lr,
+                                     1 if accumulate else 0, gscale, _stream()), "fc_bwd")
+    _count(1)
+
+
+def sgd(p, g, lr):
+    """K14: p -= lr * g."""
+    _native.check(_lib().b200_sgd(_p(p), _p(g), p.numel(), lr, _stream()), "sgd")
+    _count(1)
+
+
+def fcw_permute(src, dst, C, Hd, Wd, to_hwc: bool):
+    _native.check(_lib().b200_fcw_permute(_p(src), _p(dst), C, Hd, Wd, 1 if to_hwc else 0, _stream()),
+                  "fcw_permute")
+    _count(1)
+
+
+def nhwc_bf16_to_nchw_f32(src, dst):
+    B, H, W, C = src.shape
+    _native.check(_lib().b200_nhwc_bf16_to_nchw_f32(_p(src), _p(dst), B, C, H, W, _stream()), "nhwc->nchw")
+    _count(1)
+
+
+def nchw_f32_to_nhwc_bf16(src, dst):
+    B, C, H, W = src.shape
+    _native.check(_lib().b200_nchw_f32_to_nhwc_bf16(_p(src), _p(dst), B, C, H, W, _stream()), "nchw->nhwc")
+    _count(1)
+
+
+def l2_flush(buf):
+    _native.check(_lib().b200_l2_flush(_p(buf), buf.numel() * buf.element_size(), _stream()), "l2_flush")
