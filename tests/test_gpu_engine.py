@@ -20,7 +20,32 @@ def _no_tf32():
     torch.backends.cuda.matmul.allow_tf32 = False
 
 
-def _run_pair(shape, B, steps, lr, backend, fuse):
+class _Q(torch.autograd.Function):
+    """bf16 storage point: value rounded in forward; gradient rounded in backward iff the
+    engine materialises that gradient in bf16 (dp2, dx2, dp1 - not the conv1 output grad)."""
+
+    @staticmethod
+    def forward(ctx, x, round_grad):
+        ctx.round_grad = round_grad
+        return x.to(torch.bfloat16).float()
+
+    @staticmethod
+    def backward(ctx, g):
+        return (g.to(torch.bfloat16).float() if ctx.round_grad else g), None
+
+
+def _emulated_forward(m, x):
+    """The reference architecture with the engine's bf16 storage points made explicit."""
+    l1, l2 = m.layer1, m.layer2
+    x1 = _Q.apply(l1[0](x), False)
+    p1 = _Q.apply(F.max_pool2d(F.relu(l1[1](x1)), 2), True)
+    w2 = _Q.apply(l2[0].weight, False)
+    x2 = _Q.apply(F.conv2d(p1, w2, l2[0].bias, padding=2), True)
+    p2 = _Q.apply(F.max_pool2d(F.relu(l2[1](x2)), 2), True)
+    return m.fc(p2.flatten(1))
+
+
+def _run_pair(shape, B, steps, lr, backend, fuse, emulate=True):
     from torch_distributed_sandbox_b200.models import reference_init
     from torch_distributed_sandbox_b200.models.engine import FusedConvNet
     ref = reference_init(shape, seed=0).to(DEV)
@@ -33,7 +58,7 @@ def _run_pair(shape, B, steps, lr, backend, fuse):
     for s in range(steps):
         x = torch.rand(B, 1, *shape, device=DEV, generator=g)
         y = torch.randint(0, 10, (B,), device=DEV, generator=g)
-        loss_ref = F.cross_entropy(ref(x), y)
+        loss_ref = F.cross_entropy(_emulated_forward(ref, x) if emulate else ref(x), y)
         opt.zero_grad()
         loss_ref.backward()
         grads_ref = {k: p.grad.clone() for k, p in ref.named_parameters()}
@@ -48,17 +73,18 @@ def _run_pair(shape, B, steps, lr, backend, fuse):
 
 @pytest.mark.parametrize("backend", ["torch", "tc"])
 def test_engine_matches_reference_model(backend):
+    """Against the fp32 model with the engine's bf16 storage points emulated: tight bands."""
     shape, B = (64, 96), 3
     ref, eng, out = _run_pair(shape, B, steps=3, lr=1e-2, backend=backend, fuse=False)
     for s, (loss, loss_ref, grads, grads_ref) in enumerate(out):
         print(f"[engine/{backend}] step {s}: loss {loss:.6f} ref {loss_ref:.6f}")
-        assert abs(loss - loss_ref) < 2e-2 * max(1.0, abs(loss_ref))
+        assert abs(loss - loss_ref) < 2e-3 * max(1.0, abs(loss_ref))
         for k, gref in grads_ref.items():
             if k in ("layer1.0.bias", "layer2.0.bias"):
                 continue    # analytically zero (bias before BatchNorm); torch returns round-off
             e = rel(grads[k], gref)
             print(f"[engine/{backend}]   grad {k}: rel-L2 {e:.3e}")
-            assert e < 6e-2, f"step {s} grad {k}: {e}"
+            assert e < 2e-2, f"step {s} grad {k}: {e}"
     sd, sd_ref = eng.state_dict(), ref.state_dict()
     assert list(sd.keys()) == list(sd_ref.keys())
     for k in sd_ref:
@@ -68,7 +94,47 @@ def test_engine_matches_reference_model(backend):
         else:
             e = rel(sd[k], sd_ref[k])
             print(f"[engine/{backend}]   state {k}: rel-L2 {e:.3e}")
-            assert e < 2e-2, f"state {k}: {e}"
+            assert e < 5e-3, f"state {k}: {e}"
+
+
+def test_engine_tracks_pure_fp32_model():
+    """Against the un-emulated fp32 model (what the reference computes, TF32 off): the loss
+    curve agrees to bf16 precision and the weights stay close after a few SGD steps.  Per-step
+    gradients of the conv layers are NOT compared here: on random data they are noise-like
+    sums in which a handful of pool arg-max flips (bf16 vs fp32 activations) dominate."""
+    shape, B = (64, 96), 4
+    ref, eng, out = _run_pair(shape, B, steps=4, lr=1e-2, backend="tc", fuse=True, emulate=False)
+    for s, (loss, loss_ref, grads, grads_ref) in enumerate(out):
+        print(f"[engine/fp32] step {s}: loss {loss:.6f} ref {loss_ref:.6f}")
+        assert abs(loss - loss_ref) < 1e-2 * max(1.0, abs(loss_ref))
+    sd, sd_ref = eng.state_dict(), ref.state_dict()
+    for k in ("fc.weight", "fc.bias", "layer2.0.weight", "layer1.0.weight", "layer2.1.running_var"):
+        e = rel(sd[k], sd_ref[k])
+        print(f"[engine/fp32]   state {k}: rel-L2 {e:.3e}")
+        assert e < 2e-2, f"state {k}: {e}"
+
+
+def test_autograd_front_end_matches_train_step():
+    """model(images) -> criterion -> backward -> optimizer.step (the reference's loop idiom)
+    produces the same update as the fused train_step."""
+    from torch_distributed_sandbox_b200.models.module import FusedModule, SGD
+    shape, B = (32, 64), 3
+    g = torch.Generator(device=DEV).manual_seed(5)
+    x = torch.rand(B, 1, *shape, device=DEV, generator=g)
+    y = torch.randint(0, 10, (B,), device=DEV, generator=g)
+    m1 = FusedModule(shape, batch_size=B, device=DEV, lr=1e-2)
+    m2 = FusedModule(shape, batch_size=B, device=DEV, lr=1e-2)
+    opt = SGD(m1, lr=1e-2)
+    crit = torch.nn.CrossEntropyLoss()
+    for _ in range(2):
+        loss1 = crit(m1(x), y)
+        opt.zero_grad()
+        loss1.backward()
+        opt.step()
+        loss2 = m2.train_step(x, y)
+        assert abs(float(loss1) - float(loss2)) < 1e-5
+    assert rel(m1.engine.fcw, m2.engine.fcw) < 1e-6 and rel(m1.engine.small, m2.engine.small) < 1e-5
+    assert list(m1.state_dict().keys())[0] == "layer1.0.weight"
 
 
 def test_fused_fc_sgd_equals_unfused():

@@ -223,14 +223,14 @@ def test_conv1_wgrad(ops):
     B, H, W = 2, 40, 72
     g = torch.Generator(device=DEV).manual_seed(9)
     xin = torch.rand(B, H, W, device=DEV, generator=g)
-    w = (torch.randn(16, 1, 5, 5, device=DEV, generator=g) * 0.2).requires_grad_(True)
+    w = torch.randn(16, 1, 5, 5, device=DEV, generator=g) * 0.2
     b = torch.zeros(16, device=DEV)
     gamma = torch.rand(16, device=DEV, generator=g) + 0.5
     beta = torch.randn(16, device=DEV, generator=g) * 0.2
     dpb = nhwc_bf16(torch.randn(B, 16, H // 2, W // 2, device=DEV, generator=g))
     x1 = torch.empty(B, H, W, 16, device=DEV, dtype=torch.bfloat16)
     part = torch.zeros(ops.conv1_fwd_grid(), 32, device=DEV)
-    ops.conv1_fwd(xin, w.detach(), b, x1, part)
+    ops.conv1_fwd(xin, w, b, x1, part)
     bn = torch.zeros(4, 16, device=DEV)
     rm, rv = torch.zeros(16, device=DEV), torch.ones(16, device=DEV)
     ops.bn_finalize(part, ops.conv1_fwd_grid(), 16, B * H * W, gamma, beta, rm, rv, None, bn)
@@ -243,9 +243,13 @@ def test_conv1_wgrad(ops):
     pw = torch.zeros(ops.conv1_wgrad_grid(), 400, device=DEV)
     dw = torch.zeros(16, 1, 5, 5, device=DEV)
     ops.conv1_wgrad(xin, x1, dpb, bn, red, pw, dw)
-    y = F.batch_norm(F.conv2d(xin[:, None], w, b, padding=2), None, None, gamma, beta, training=True)
+    # Oracle on the SAME stored (bf16-rounded) conv output the kernel sees: otherwise the few
+    # windows whose arg-max flips under bf16 rounding dominate the error of a noise-like sum.
+    x1r = to_nchw(x1).requires_grad_(True)
+    y = F.batch_norm(x1r, None, None, gamma, beta, training=True)
     F.max_pool2d(F.relu(y), 2).backward(to_nchw(dpb))
-    report("conv1_wgrad", rel(dw, w.grad), 2e-2)
+    ref = torch.nn.grad.conv2d_weight(xin[:, None], (16, 1, 5, 5), x1r.grad, padding=2)
+    report("conv1_wgrad", rel(dw, ref), 2e-3)
 
 
 def test_sgd_and_permute(ops):

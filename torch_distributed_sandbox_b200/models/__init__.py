@@ -7,4 +7,7 @@ def __getattr__(name):
     if name == "FusedConvNet":
         from .engine import FusedConvNet
         return FusedConvNet
+    if name in ("FusedModule", "SGD"):
+        from . import module
+        return getattr(module, name)
     raise AttributeError(name)

@@ -83,6 +83,8 @@ class FusedConvNet:
         self.fuse_fc_sgd = bool(fuse_fc_sgd)
         self.F = rn.feature_size((H, W))
         self.comm = None           # set by parallel.ddp for data-parallel runs
+        self._fc_fused_done = False
+        self._publish_grads = lambda: None
         self.grad_scale = 1.0      # 1/world_size under DDP (fused into the producing kernels)
         dev, B = self.device, self.B
         f32 = dict(device=dev, dtype=torch.float32)
@@ -257,11 +259,21 @@ class FusedConvNet:
     def loss_backward(self, labels: torch.Tensor) -> torch.Tensor:
         """Cross-entropy (mean) + full backward.  Leaves gradients in ``self.grads`` /
         ``self.fcw_grad``; with ``fuse_fc_sgd`` and no comm, fc.weight is updated in place here."""
+        self._labels.copy_(labels, non_blocking=True)
+        ops.cross_entropy(self.logits, self._labels, self.loss, self.dlogits, self.grads["fc.bias"], self.grad_scale)
+        self._backward(allow_fused_sgd=True)
+        return self.loss
+
+    def backward_from_dlogits(self, dlogits: torch.Tensor) -> None:
+        """Backward for an externally computed loss (autograd front-end, models/module.py)."""
+        self.dlogits.copy_(dlogits)
+        self.grads["fc.bias"].copy_(self.dlogits.sum(0) * self.grad_scale)
+        self._backward(allow_fused_sgd=False)
+
+    def _backward(self, allow_fused_sgd: bool) -> None:
         P, G, B, H, W = self.params, self.grads, self.B, self.H, self.W
         gs = self.grad_scale
-        self._labels.copy_(labels, non_blocking=True)
-        ops.cross_entropy(self.logits, self._labels, self.loss, self.dlogits, G["fc.bias"], gs)
-        fused = self.fuse_fc_sgd and self.comm is None and B <= 8
+        fused = allow_fused_sgd and self.fuse_fc_sgd and self.comm is None and B <= 8
         if not fused and self.fcw_grad is None:
             self.fcw_grad = torch.empty_like(self.fcw)
         p2 = self.p2.view(B, self.F)
@@ -291,7 +303,6 @@ class FusedConvNet:
                             G["layer1.1.bias"], gs)
         ops.conv1_wgrad(self.x, self.x1, self.dp1, self.bn1, self.red1, self.part_wg1, G["layer1.0.weight"], gs)
         G["layer1.0.bias"].zero_()
-        return self.loss
 
     def step(self) -> None:
         """SGD (lr, no momentum / weight decay: mnist_onegpu.py:49) on every parameter."""
