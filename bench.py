@@ -122,7 +122,7 @@ def run_b200dp(a):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
-    step = model.train_step if world == 1 else model.module.train_step
+    step = model.train_step
 
     def dev_step(i):                                          # inputs already on the device
         step(dev_imgs[i % nb], dev_labs[i % nb])

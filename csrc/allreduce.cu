@@ -1,0 +1,347 @@
+// Hand-written sm_100a collectives over symmetric memory (K16 / C1-C6).
+//
+// The reference's gradient exchange is torch DDP calling ncclAllReduce per bucket
+// (mnist_distributed.py:67,96) and its toy is ncclAllReduce on a 0-dim int32
+// (allreduce_toy.py:30-31).  Here the same collectives are kernels of ours that load and
+// store PEER GPU memory directly over NVLink / NVSwitch:
+//
+//   one-shot       every rank reads all peers' buffers and reduces locally   (<= ~256 KB:
+//                  the 53 KB conv/BN bucket, BN buffers, the toy scalar)
+//   two-shot P2P   reduce-scatter by pulling the own shard from every peer, then
+//                  all-gather by pulling the reduced shards                   (fallback)
+//   two-shot NVLS  multimem.ld_reduce on the own shard (the switch adds the n copies),
+//                  multimem.st of the result (the switch replicates it)       (720 MB bucket)
+//
+// fused into the reduction epilogue: the 1/world_size gradient scale and - optionally - the
+// SGD update itself: instead of all-gathering the reduced GRADIENT shard, rank r applies
+// W[shard r] -= lr * g and multicasts the updated WEIGHT shard, so the separate optimizer
+// pass over the 720 MB fc.weight (K14) disappears and all replicas stay bit-identical.
+//
+// Cross-GPU synchronisation: per-CTA flag words in every rank's symmetric flag page,
+// written with st.release.sys by the peer and polled with ld.acquire.sys locally.  Flags
+// carry a monotonically increasing epoch and are never reset; every wait is bounded (a dead
+// peer traps after ~20 s instead of wedging the GPU).  All ranks launch identical grids.
+#include "common.h"
+#include "ptx.cuh"
+#include <cuda_bf16.h>
+#include <cstdint>
+
+namespace {
+
+constexpr int kMaxRanks = 16;
+constexpr int kMaxBlocks = 256;
+
+struct Peers {
+  void* ptr[kMaxRanks];       // this buffer on every rank (VAs valid in this process)
+  uint32_t* flag[kMaxRanks];  // flag page of every rank for this channel
+  void* mc;                   // multicast VA of the buffer (nullptr if none)
+  int rank, world;
+};
+
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ float4 ld_peer16(const void* p) {
+  float4 v;
+  asm volatile("ld.relaxed.sys.global.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ float4 mc_ld_reduce_f32(const void* p) {
+  float4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void mc_st_f32(void* p, float4 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+// 8 bf16 per 16 bytes, accumulated in fp32 inside the switch
+__device__ __forceinline__ uint4 mc_ld_reduce_bf16(const void* p) {
+  uint4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0,%1,%2,%3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void mc_st_b32x4(void* p, uint4 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
+// Barrier across the same-index CTA of every rank.  Slot layout: flag[(block*kMaxRanks)+src].
+__device__ __forceinline__ void sys_barrier(const Peers& P, uint32_t epoch) {
+  __threadfence_system();            // every thread publishes its own prior writes at system scope
+  __syncthreads();
+  const int t = threadIdx.x;
+  if (t < P.world) {
+    st_release_sys(P.flag[t] + (size_t)blockIdx.x * kMaxRanks + P.rank, epoch);
+    const uint32_t* mine = P.flag[P.rank] + (size_t)blockIdx.x * kMaxRanks + t;
+    const uint64_t t0 = b2::globaltimer_ns();
+    uint32_t spins = 0;
+    // epochs are compared with wrap-safe signed distance
+    while ((int32_t)(ld_acquire_sys(mine) - epoch) < 0) {
+      if ((++spins & 0x3FF) == 0 && b2::globaltimer_ns() - t0 > 20000000000ull) {
+        printf("b200dp: rank %d block %d timed out waiting for rank %d (epoch %u)\n", P.rank, blockIdx.x, t, epoch);
+        __trap();
+      }
+    }
+  }
+  __syncthreads();
+}
+
+__global__ void barrier_kernel(Peers P, uint32_t epoch) { sys_barrier(P, epoch); }
+
+// ------------------------------------------------------------------ one-shot ---
+// out (local, any memory) = scale * sum_p in_p   with `in` the symmetric staging buffer.
+template <typename T, typename Acc>
+__global__ void __launch_bounds__(512)
+allreduce_oneshot_kernel(Peers P, T* __restrict__ out, size_t n, float scale, int op, uint32_t epoch) {
+  sys_barrier(P, epoch);             // all inputs are in place
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    Acc acc = (Acc) reinterpret_cast<const volatile T*>(P.ptr[0])[i];
+    for (int p = 1; p < P.world; ++p) {
+      const Acc v = (Acc) reinterpret_cast<const volatile T*>(P.ptr[p])[i];
+      if (op == 0) acc += v;
+      else if (op == 2) acc = v > acc ? v : acc;
+      else if (op == 3) acc = v < acc ? v : acc;
+      else acc *= v;
+    }
+    out[i] = (T)(acc * (Acc)scale);
+  }
+  sys_barrier(P, epoch + 1);         // inputs may be overwritten after this
+}
+template <>
+__global__ void __launch_bounds__(512)
+allreduce_oneshot_kernel<__nv_bfloat16, float>(Peers P, __nv_bfloat16* __restrict__ out, size_t n, float scale, int op,
+                                               uint32_t epoch) {
+  sys_barrier(P, epoch);
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    float acc = 0.f;
+    for (int p = 0; p < P.world; ++p) {
+      const unsigned short raw = reinterpret_cast<const volatile unsigned short*>(P.ptr[p])[i];
+      const float v = __uint_as_float((uint32_t)raw << 16);
+      if (p == 0) acc = v;
+      else if (op == 0) acc += v;
+      else if (op == 2) acc = fmaxf(acc, v);
+      else if (op == 3) acc = fminf(acc, v);
+      else acc *= v;
+    }
+    out[i] = __float2bfloat16_rn(acc * scale);
+  }
+  sys_barrier(P, epoch + 1);
+}
+
+// -------------------------------------------------------------- two-shot P2P ---
+// In place on the symmetric fp32 buffer.  n4 = number of float4; shard r = [lo_r, hi_r).
+// If w != nullptr the SGD update is fused: w is this rank's weight buffer (same layout, also
+// symmetric: wpeers), phase 1 writes W[shard r] -= lr * g, phase 2 gathers WEIGHT shards.
+__global__ void __launch_bounds__(512)
+allreduce_twoshot_f32_kernel(Peers P, Peers Wp, size_t n4, float scale, float lr, uint32_t epoch) {
+  const int r = P.rank, n = P.world;
+  const size_t per = (n4 + n - 1) / n;
+  const size_t lo = per * r, hi = min(n4, lo + per);
+  const bool fused = Wp.ptr[0] != nullptr;
+  sys_barrier(P, epoch);
+  for (size_t i = lo + (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += (size_t)gridDim.x * blockDim.x) {
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 4
+    for (int p = 0; p < n; ++p) {    // fixed rank order: every rank would compute identical bits
+      const float4 v = ld_peer16(reinterpret_cast<const float4*>(P.ptr[p]) + i);
+      acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+    }
+    acc.x *= scale; acc.y *= scale; acc.z *= scale; acc.w *= scale;
+    if (fused) {
+      float4* wp = reinterpret_cast<float4*>(Wp.ptr[r]) + i;
+      float4 w = *wp;
+      w.x = fmaf(-lr, acc.x, w.x); w.y = fmaf(-lr, acc.y, w.y); w.z = fmaf(-lr, acc.z, w.z); w.w = fmaf(-lr, acc.w, w.w);
+      *wp = w;
+    } else {
+      reinterpret_cast<float4*>(P.ptr[r])[i] = acc;
+    }
+  }
+  sys_barrier(P, epoch + 1);         // every shard is reduced (and every read of my shards is done)
+  const Peers& G = fused ? Wp : P;
+  for (int k = 1; k < n; ++k) {
+    const int p = (r + k) % n;       // stagger peers so the n ranks do not all hit one GPU at once
+    const size_t plo = per * p, phi = min(n4, plo + per);
+    for (size_t i = plo + (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < phi; i += (size_t)gridDim.x * blockDim.x)
+      reinterpret_cast<float4*>(G.ptr[r])[i] = ld_peer16(reinterpret_cast<const float4*>(G.ptr[p]) + i);
+  }
+  sys_barrier(P, epoch + 2);         // nobody still reads my reduced shard
+}
+
+// ------------------------------------------------------------- two-shot NVLS ---
+template <int UNROLL>
+__global__ void __launch_bounds__(512)
+allreduce_nvls_f32_kernel(Peers P, Peers Wp, size_t n4, float scale, float lr, uint32_t epoch) {
+  const int r = P.rank, n = P.world;
+  const size_t per = (n4 + n - 1) / n;
+  const size_t lo = per * r, hi = min(n4, lo + per);
+  const bool fused = Wp.ptr[0] != nullptr;
+  const float4* src = reinterpret_cast<const float4*>(P.mc);
+  float4* dst = reinterpret_cast<float4*>(fused ? Wp.mc : P.mc);
+  const float4* wl = reinterpret_cast<const float4*>(Wp.ptr[r]);
+  sys_barrier(P, epoch);
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  size_t i = lo + (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  for (; i + (UNROLL - 1) * stride < hi; i += UNROLL * stride) {
+    float4 v[UNROLL];
+#pragma unroll
+    for (int u = 0; u < UNROLL; ++u) v[u] = mc_ld_reduce_f32(src + i + u * stride);
+#pragma unroll
+    for (int u = 0; u < UNROLL; ++u) {
+      float4 g = make_float4(v[u].x * scale, v[u].y * scale, v[u].z * scale, v[u].w * scale);
+      if (fused) {
+        const float4 w = wl[i + u * stride];
+        g = make_float4(fmaf(-lr, g.x, w.x), fmaf(-lr, g.y, w.y), fmaf(-lr, g.z, w.z), fmaf(-lr, g.w, w.w));
+      }
+      mc_st_f32(dst + i + u * stride, g);
+    }
+  }
+  for (; i < hi; i += stride) {
+    const float4 v = mc_ld_reduce_f32(src + i);
+    float4 g = make_float4(v.x * scale, v.y * scale, v.z * scale, v.w * scale);
+    if (fused) {
+      const float4 w = wl[i];
+      g = make_float4(fmaf(-lr, g.x, w.x), fmaf(-lr, g.y, w.y), fmaf(-lr, g.z, w.z), fmaf(-lr, g.w, w.w));
+    }
+    mc_st_f32(dst + i, g);
+  }
+  sys_barrier(P, epoch + 1);         // all multicast stores have landed everywhere
+}
+
+// bf16 buffer (8 elements per 16 B), fp32 accumulation in the switch; scale applied here.
+__global__ void __launch_bounds__(512)
+allreduce_nvls_bf16_kernel(Peers P, size_t n16, float scale, uint32_t epoch) {
+  const int r = P.rank, n = P.world;
+  const size_t per = (n16 + n - 1) / n;
+  const size_t lo = per * r, hi = min(n16, lo + per);
+  uint4* mc = reinterpret_cast<uint4*>(P.mc);
+  sys_barrier(P, epoch);
+  for (size_t i = lo + (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += (size_t)gridDim.x * blockDim.x) {
+    uint4 v = mc_ld_reduce_bf16(mc + i);
+    if (scale != 1.0f) {
+      v.x = b2::pack_bf16x2(b2::bf16_lo(v.x) * scale, b2::bf16_hi(v.x) * scale);
+      v.y = b2::pack_bf16x2(b2::bf16_lo(v.y) * scale, b2::bf16_hi(v.y) * scale);
+      v.z = b2::pack_bf16x2(b2::bf16_lo(v.z) * scale, b2::bf16_hi(v.z) * scale);
+      v.w = b2::pack_bf16x2(b2::bf16_lo(v.w) * scale, b2::bf16_hi(v.w) * scale);
+    }
+    mc_st_b32x4(mc + i, v);
+  }
+  sys_barrier(P, epoch + 1);
+}
+
+// broadcast: every rank copies `bytes` (multiple of 16) from the root's symmetric buffer
+__global__ void __launch_bounds__(512)
+broadcast_kernel(Peers P, float4* __restrict__ out, size_t n16, int root, uint32_t epoch) {
+  sys_barrier(P, epoch);
+  if (P.rank != root || out != reinterpret_cast<float4*>(P.ptr[root]))
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += (size_t)gridDim.x * blockDim.x)
+      out[i] = ld_peer16(reinterpret_cast<const float4*>(P.ptr[root]) + i);
+  sys_barrier(P, epoch + 1);
+}
+
+// all-gather: out[p*n16 + i] = peer p's buffer[i]
+__global__ void __launch_bounds__(512)
+allgather_kernel(Peers P, float4* __restrict__ out, size_t n16, uint32_t epoch) {
+  sys_barrier(P, epoch);
+  for (int k = 0; k < P.world; ++k) {
+    const int p = (P.rank + k) % P.world;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += (size_t)gridDim.x * blockDim.x)
+      out[(size_t)p * n16 + i] = ld_peer16(reinterpret_cast<const float4*>(P.ptr[p]) + i);
+  }
+  sys_barrier(P, epoch + 1);
+}
+
+Peers make_peers(void* const* ptrs, void* const* flags, void* mc, int rank, int world) {
+  Peers P;
+  for (int i = 0; i < kMaxRanks; ++i) {
+    P.ptr[i] = (ptrs && i < world) ? ptrs[i] : nullptr;
+    P.flag[i] = (flags && i < world) ? (uint32_t*)flags[i] : nullptr;
+  }
+  P.mc = mc; P.rank = rank; P.world = world;
+  return P;
+}
+
+}  // namespace
+
+// Bytes one channel's flag page needs on every rank.
+B200_API size_t b200_ar_flag_bytes() { return (size_t)kMaxBlocks * kMaxRanks * sizeof(uint32_t); }
+B200_API int b200_ar_max_blocks() { return kMaxBlocks; }
+
+// Epoch convention: every call consumes `b200_ar_epochs(kind)` consecutive epochs starting at
+// `epoch` (the Python layer keeps one counter per flag channel, identical on all ranks).
+B200_API int b200_ar_barrier(void* const* flags, int rank, int world, uint32_t epoch, void* stream) {
+  Peers P = make_peers(nullptr, flags, nullptr, rank, world);
+  barrier_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(P, epoch);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+// dtype: 0 f32, 2 i32, 3 i64, 5 bf16, 1 f64.  op: 0 SUM, 2 MAX, 3 MIN, 4 PROD (AVG = SUM with scale).
+B200_API int b200_ar_oneshot(void* const* ptrs, void* const* flags, int rank, int world, void* out, size_t n,
+                             int dtype, int op, float scale, int blocks, uint32_t epoch, void* stream) {
+  B200_CHECK(world <= kMaxRanks && blocks >= 1 && blocks <= kMaxBlocks, "oneshot: bad world/blocks");
+  Peers P = make_peers(ptrs, flags, nullptr, rank, world);
+  cudaStream_t s = (cudaStream_t)stream;
+  switch (dtype) {
+    case 0: allreduce_oneshot_kernel<float, float><<<blocks, 512, 0, s>>>(P, (float*)out, n, scale, op, epoch); break;
+    case 1: allreduce_oneshot_kernel<double, double><<<blocks, 512, 0, s>>>(P, (double*)out, n, scale, op, epoch); break;
+    case 2: allreduce_oneshot_kernel<int, int><<<blocks, 512, 0, s>>>(P, (int*)out, n, scale, op, epoch); break;
+    case 3: allreduce_oneshot_kernel<long long, long long><<<blocks, 512, 0, s>>>(P, (long long*)out, n, scale, op, epoch); break;
+    case 5: allreduce_oneshot_kernel<__nv_bfloat16, float><<<blocks, 512, 0, s>>>(P, (__nv_bfloat16*)out, n, scale, op, epoch); break;
+    default: return b200_fail(-2, "oneshot: unsupported dtype code %d", dtype);
+  }
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+// In-place fp32 SUM over the symmetric buffer (n floats, n % 4 == 0).  algo: 1 = two-shot P2P,
+// 2 = two-shot NVLS (needs mc).  wptrs/wmc != null fuses SGD: W -= lr * (scale * sum g).
+B200_API int b200_ar_large_f32(void* const* ptrs, void* mc, void* const* flags, void* const* wptrs, void* wmc,
+                               int rank, int world, size_t n, float scale, float lr, int algo, int blocks,
+                               uint32_t epoch, void* stream) {
+  B200_CHECK(world <= kMaxRanks && blocks >= 1 && blocks <= kMaxBlocks, "allreduce: bad world/blocks");
+  B200_CHECK(n % 4 == 0, "allreduce: element count must be a multiple of 4");
+  Peers P = make_peers(ptrs, flags, mc, rank, world);
+  Peers Wp = make_peers(wptrs, nullptr, wmc, rank, world);
+  cudaStream_t s = (cudaStream_t)stream;
+  if (algo == 2) {
+    B200_CHECK(mc != nullptr && (!wptrs || wmc), "allreduce: NVLS requested but no multicast mapping");
+    allreduce_nvls_f32_kernel<4><<<blocks, 512, 0, s>>>(P, Wp, n / 4, scale, lr, epoch);
+  } else {
+    allreduce_twoshot_f32_kernel<<<blocks, 512, 0, s>>>(P, Wp, n / 4, scale, lr, epoch);
+  }
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+B200_API int b200_ar_nvls_bf16(void* mc, void* const* flags, int rank, int world, size_t n, float scale, int blocks,
+                               uint32_t epoch, void* stream) {
+  B200_CHECK(mc != nullptr && n % 8 == 0, "nvls_bf16: needs a multicast mapping and n %% 8 == 0");
+  Peers P = make_peers(nullptr, flags, mc, rank, world);
+  allreduce_nvls_bf16_kernel<<<blocks, 512, 0, (cudaStream_t)stream>>>(P, n / 8, scale, epoch);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+B200_API int b200_ar_broadcast(void* const* ptrs, void* const* flags, int rank, int world, void* out, size_t bytes,
+                               int root, int blocks, uint32_t epoch, void* stream) {
+  B200_CHECK(bytes % 16 == 0, "broadcast: byte count must be a multiple of 16");
+  Peers P = make_peers(ptrs, flags, nullptr, rank, world);
+  broadcast_kernel<<<blocks, 512, 0, (cudaStream_t)stream>>>(P, (float4*)out, bytes / 16, root, epoch);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+B200_API int b200_ar_allgather(void* const* ptrs, void* const* flags, int rank, int world, void* out, size_t bytes,
+                               int blocks, uint32_t epoch, void* stream) {
+  B200_CHECK(bytes % 16 == 0, "allgather: byte count must be a multiple of 16");
+  Peers P = make_peers(ptrs, flags, nullptr, rank, world);
+  allgather_kernel<<<blocks, 512, 0, (cudaStream_t)stream>>>(P, (float4*)out, bytes / 16, epoch);
+  B200_LAUNCH_CHECK();
+  return 0;
+}

@@ -1,0 +1,161 @@
+"""Multi-GPU tests of the native backend: our all-reduce /
+broadcast / all-gather / barrier kernels over symmetric memory against closed-form expected
+values (every rank fills its buffer with a known function of its rank), repeated to shake
+out flag/epoch races, and DDP-vs-manual-averaging equivalence for the fused engine.
+Needs >= 2 GPUs; skipped otherwise (the driver's 1-GPU tier skips it cleanly)."""
+import os
+
+import pytest
+import torch
+
+import torch_distributed_sandbox_b200 as b2
+from torch_distributed_sandbox_b200 import distributed as dist
+
+pytestmark = pytest.mark.gpu
+
+
+def _ngpu():
+    return torch.cuda.device_count() if torch.cuda.is_available() else 0
+
+
+needs2 = pytest.mark.skipif(_ngpu() < 2, reason="needs >= 2 GPUs")
+
+
+def _init(rank, world, port):
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", port
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank), timeout=120)
+
+
+def _collectives(rank, world, port):
+    _init(rank, world, port)
+    dev = torch.device("cuda", rank)
+    be = dist._default().backend
+    print(f"[multi] rank {rank}: {be.describe()} topology {be.topology()}", flush=True)
+    tri = world * (world + 1) // 2
+    # the toy: 0-dim int32 SUM (allreduce_toy.py:30-31), repeated (epoch/flag reuse)
+    for it in range(50):
+        t = torch.tensor(rank + 1 + it, dtype=torch.int32, device=dev)
+        dist.all_reduce(t)
+        assert int(t) == tri + it * world, (it, int(t))
+    dist.barrier()
+    # small fp32 (one-shot), AVG / MAX, bf16, int64
+    x = torch.arange(1000, device=dev, dtype=torch.float32) * (rank + 1)
+    dist.all_reduce(x)
+    assert torch.equal(x, torch.arange(1000, device=dev, dtype=torch.float32) * tri)
+    y = torch.full((333,), float(rank), device=dev)
+    dist.all_reduce(y, op=dist.ReduceOp.AVG)
+    assert torch.allclose(y, torch.full((333,), (world - 1) / 2, device=dev))
+    z = torch.tensor([rank, -rank], device=dev, dtype=torch.int64)
+    dist.all_reduce(z, op=dist.ReduceOp.MAX)
+    assert z.tolist() == [world - 1, 0]
+    h = torch.full((4096,), rank + 0.5, device=dev, dtype=torch.bfloat16)
+    dist.all_reduce(h)
+    assert torch.equal(h.float(), torch.full((4096,), sum(r + 0.5 for r in range(world)), device=dev))
+    # large fp32 through the staging buffer (two-shot, chunked; 40 MB > 32 MiB staging)
+    n = 10_000_004
+    base = (torch.arange(n, device=dev, dtype=torch.float32) % 1013) * 0.25
+    big = base * (rank + 1)
+    dist.all_reduce(big)
+    assert torch.equal(big, base * tri)
+    # symmetric bucket, in place: NVLS (if bound) and P2P two-shot, repeated with skewed arrival
+    m = 6_000_000
+    sym = be.alloc_symmetric(m, torch.float32)
+    basem = (torch.arange(m, device=dev, dtype=torch.float32) % 509) * 0.5
+    for algo in (["nvls"] if be.multicast else []) + ["p2p"]:
+        for it in range(6):
+            if it % world == rank:
+                torch.cuda._sleep(20_000_000)            # one late rank per iteration
+            sym.copy_(basem * (rank + 1 + it))
+            be.all_reduce(sym, dist.ReduceOp.SUM, scale=1.0 / world, algo=algo)
+            want = basem * ((tri + it * world) / world)
+            assert torch.allclose(sym, want, rtol=1e-6, atol=1e-6), (algo, it, float((sym - want).abs().max()))
+    # fused SGD epilogue: W -= lr * mean(g)
+    w = be.alloc_symmetric(m, torch.float32)
+    for algo in (["nvls"] if be.multicast else []) + ["p2p"]:
+        w.fill_(1.0)
+        sym.copy_(basem * (rank + 1))
+        torch.cuda.synchronize()
+        dist.barrier()
+        be.all_reduce(sym, dist.ReduceOp.SUM, scale=1.0 / world, sgd=(w, 0.5), algo=algo)
+        want = 1.0 - 0.5 * basem * (tri / world)
+        torch.cuda.synchronize()
+        dist.barrier()
+        assert torch.allclose(w, want, rtol=1e-6, atol=1e-5), (algo, float((w - want).abs().max()))
+    # broadcast (odd size, non-zero root), all_gather
+    b = torch.full((1001,), float(rank), device=dev)
+    dist.broadcast(b, src=world - 1)
+    assert torch.equal(b, torch.full((1001,), float(world - 1), device=dev))
+    outs = [torch.zeros(7, device=dev) for _ in range(world)]
+    dist.all_gather(outs, torch.full((7,), float(rank), device=dev))
+    assert [int(o[0]) for o in outs] == list(range(world))
+    g = dist.new_group(ranks=list(range(world)))
+    assert g is dist.new_group(ranks=list(range(world)))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@needs2
+def test_native_collectives():
+    world = min(_ngpu(), 4)
+    b2.spawn(_collectives, args=(world, b2.find_free_port()), nprocs=world)
+
+
+def _ddp_engine(rank, world, port, out_path):
+    from torch_distributed_sandbox_b200.models.module import FusedModule
+    from torch_distributed_sandbox_b200.models.engine import FusedConvNet
+    from torch_distributed_sandbox_b200.parallel import DistributedDataParallel
+    _init(rank, world, port)
+    dev = torch.device("cuda", rank)
+    shape, B, lr, steps = (64, 96), 3, 1e-2, 3
+    model = FusedModule(shape, batch_size=B, device=dev, lr=lr, seed=rank)       # different init per rank:
+    ddp = DistributedDataParallel(model, device_ids=[rank])                      # ctor must sync to rank 0
+    assert ddp.bucket_sizes()[1] == 53_416 and list(ddp.state_dict().keys())[0] == "module.layer1.0.weight"
+    init_sd = {k: v.clone() for k, v in model.engine.state_dict().items()}
+    g = torch.Generator().manual_seed(1234)
+    xs = torch.rand(steps, world, B, 1, *shape, generator=g)
+    ys = torch.randint(0, 10, (steps, world, B), generator=g)
+    for s in range(steps):
+        ddp.train_step(xs[s, rank].to(dev), ys[s, rank].to(dev))
+    torch.cuda.synchronize()
+    sd = model.engine.state_dict()
+    # every rank must hold bit-identical parameters
+    for k in ("fc.weight", "layer2.0.weight", "layer1.1.running_mean"):
+        mine = sd[k].flatten()[:4096].float().contiguous()
+        allv = [torch.zeros_like(mine) for _ in range(world)]
+        dist.all_gather(allv, mine)
+        for r in range(world):
+            assert torch.equal(allv[r], allv[0]), f"{k} differs between rank 0 and rank {r}"
+    if rank == 0:
+        # manual data parallelism in one process: per-rank gradients from unfused engines, averaged
+        engs = [FusedConvNet(shape, batch_size=B, device=dev, lr=lr, init="empty", fuse_fc_sgd=False)
+                for _ in range(world)]
+        for e in engs:
+            e.load_state_dict(init_sd)
+        for s in range(steps):
+            grads = []
+            for r, e in enumerate(engs):
+                e.forward(xs[s, r].to(dev))
+                e.loss_backward(ys[s, r].to(dev))
+                grads.append((e.small_grad.clone(), e.fcw_grad.clone()))
+            sm = sum(gr[0] for gr in grads) / world
+            fw = sum(gr[1] for gr in grads) / world
+            for e in engs:
+                e.small.add_(sm, alpha=-lr)
+                e.fcw.add_(fw, alpha=-lr)
+        ref = engs[0]
+        e1 = float((model.engine.fcw - ref.fcw).norm() / ref.fcw.norm())
+        e2 = float((model.engine.small - ref.small).norm() / ref.small.norm())
+        print(f"[multi] DDP vs manual averaging: fc.weight {e1:.2e}, small {e2:.2e}", flush=True)
+        assert e1 < 1e-6 and e2 < 1e-5
+        open(out_path, "w").write("ok")
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@needs2
+def test_ddp_engine_matches_manual_gradient_averaging(tmp_path):
+    world = 2
+    out = str(tmp_path / "ok")
+    b2.spawn(_ddp_engine, args=(world, b2.find_free_port(), out), nprocs=world)
+    assert os.path.exists(out)

@@ -1,0 +1,93 @@
+"""Gradient all-reduce bandwidth sweep: our kernels vs NCCL, 1 KB - 1 GB.
+
+Launch with torch.distributed.run (one rank per GPU).  For each size: in-place all-reduce on
+a symmetric bucket (NVLS and P2P two-shot; one-shot for small), CUDA-event timed, max over
+ranks; the same tensor size through ``torch.distributed.all_reduce`` (NCCL).  Prints a table
+and writes JSON lines to gpurun_out/allreduce_sweep_<N>gpu.jsonl.
+busbw = algbw * 2(n-1)/n; roofline fraction is busbw / 770 GB/s (measured peer copy, B200_PROFILING.md).
+"""
+import json
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+import torch.distributed as tdist
+
+from torch_distributed_sandbox_b200 import distributed as dist
+
+
+def timeit(fn, iters, sync):
+    for _ in range(3):
+        fn()
+    sync()
+    s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    s.record()
+    for _ in range(iters):
+        fn()
+    e.record()
+    torch.cuda.synchronize()
+    return s.elapsed_time(e) / iters
+
+
+def main():
+    rank, local, world = int(os.environ["RANK"]), int(os.environ["LOCAL_RANK"]), int(os.environ["WORLD_SIZE"])
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    tdist.init_process_group("nccl", device_id=dev)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    be = dist._default().backend
+    sizes = [1 << k for k in range(10, 31, 2)] + [53_376, 720_000_040 // 16 * 16]
+    maxn = max(sizes) // 4
+    sym = be.alloc_symmetric(maxn, torch.float32)
+    plain = torch.zeros(maxn, device=dev)
+    rows = []
+
+    def sync():
+        torch.cuda.synchronize()
+        dist.barrier()
+
+    def mx(v):
+        t = torch.tensor([v], device=dev)
+        tdist.all_reduce(t, op=tdist.ReduceOp.MAX)
+        return float(t)
+
+    for nbytes in sorted(sizes):
+        n = nbytes // 4 // 4 * 4
+        iters = 200 if nbytes <= (1 << 20) else (30 if nbytes <= (1 << 26) else 8)
+        row = {"bytes": n * 4, "world": world}
+        view = sym[:n]
+        algos = ["oneshot"] if n * 4 <= (256 << 10) else ((["nvls"] if be.multicast else []) + ["p2p"])
+        for algo in algos:
+            blocks_list = [64] if algo == "oneshot" else [32, 64, 128]
+            best = None
+            for blocks in blocks_list:
+                if algo == "oneshot":
+                    f = lambda: be.all_reduce(plain[:n], dist.ReduceOp.SUM)
+                else:
+                    f = lambda: be.all_reduce(view, dist.ReduceOp.SUM, algo=algo, blocks=blocks)
+                ms = mx(timeit(f, iters, sync))
+                if best is None or ms < best[0]:
+                    best = (ms, blocks)
+            row[f"ours_{algo}_ms"], row[f"ours_{algo}_blocks"] = best
+        f = lambda: tdist.all_reduce(plain[:n])
+        row["nccl_ms"] = mx(timeit(f, iters, sync))
+        ours = min(v for k, v in row.items() if k.startswith("ours_") and k.endswith("_ms"))
+        fac = 2 * (world - 1) / world
+        row["ours_busbw_gbs"] = n * 4 / ours / 1e6 * fac
+        row["nccl_busbw_gbs"] = n * 4 / row["nccl_ms"] / 1e6 * fac
+        row["ours_frac_of_770"] = row["ours_busbw_gbs"] / 770.0
+        rows.append(row)
+        if rank == 0:
+            print(json.dumps(row), flush=True)
+    if rank == 0:
+        os.makedirs("gpurun_out", exist_ok=True)
+        with open(f"gpurun_out/allreduce_sweep_{world}gpu.jsonl", "w") as f:
+            for r in rows:
+                f.write(json.dumps(r) + "\n")
+    dist.destroy_process_group()
+    tdist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -85,6 +85,7 @@ class FusedConvNet:
         self.comm = None           # set by parallel.ddp for data-parallel runs
         self._fc_fused_done = False
         self._publish_grads = lambda: None
+        self._on_rebind = lambda: None
         self.grad_scale = 1.0      # 1/world_size under DDP (fused into the producing kernels)
         dev, B = self.device, self.B
         f32 = dict(device=dev, dtype=torch.float32)
@@ -105,12 +106,12 @@ class FusedConvNet:
             self.fcw = fc_weight_storage if fc_weight_storage is not None else torch.empty(10, self.F, **f32)
             assert self.fcw.shape == (10, self.F) and self.fcw.dtype == torch.float32
             self.fcw_grad = fc_grad_storage      # allocated lazily unless fused SGD covers it
-            self.bn_buf = {
-                1: dict(mean=torch.zeros(16, **f32), var=torch.ones(16, **f32),
-                        nbt=torch.zeros((), device=dev, dtype=torch.int64)),
-                2: dict(mean=torch.zeros(32, **f32), var=torch.ones(32, **f32),
-                        nbt=torch.zeros((), device=dev, dtype=torch.int64)),
-            }
+            # BatchNorm buffers live in ONE 512-byte blob so that DDP's per-forward buffer
+            # broadcast (C4) is a single tiny kernel: [rm1 16 | rv1 16 | rm2 32 | rv2 32 | nbt1 | nbt2]
+            self.bn_flat = torch.zeros(128, **f32)
+            self.bn_flat[16:32] = 1.0
+            self.bn_flat[64:96] = 1.0
+            self._bind_bn_views()
             # ---- activations (gradients alias them) -------------------------
             self.x = torch.empty(B, H, W, **f32)
             self.x1 = torch.empty(B, H, W, 16, **bf)
@@ -155,6 +156,29 @@ class FusedConvNet:
             self.load_state_dict(sd, strict=False)
         elif init != "empty":
             raise ValueError(f"unknown init {init!r}")
+
+    def _bind_bn_views(self) -> None:
+        f = self.bn_flat
+        self.bn_buf = {
+            1: dict(mean=f[0:16], var=f[16:32], nbt=f[96:98].view(torch.int64)[0]),
+            2: dict(mean=f[32:64], var=f[64:96], nbt=f[98:100].view(torch.int64)[0]),
+        }
+
+    def rebind_storage(self, fcw: Optional[torch.Tensor] = None, fcw_grad: Optional[torch.Tensor] = None,
+                       bn_flat: Optional[torch.Tensor] = None) -> None:
+        """Move fc.weight / its gradient / the BN buffer blob into caller-provided storage
+        (symmetric memory under DDP); current values are preserved."""
+        if fcw is not None:
+            fcw = fcw.view(10, self.F)
+            fcw.copy_(self.fcw)
+            self.fcw = fcw
+        if fcw_grad is not None:
+            self.fcw_grad = fcw_grad.view(10, self.F)
+        if bn_flat is not None:
+            bn_flat.copy_(self.bn_flat)
+            self.bn_flat = bn_flat
+            self._bind_bn_views()
+        self._on_rebind()
 
     # ------------------------------------------------------------ checkpoint --
     def state_dict(self, prefix: str = "") -> "OrderedDict[str, torch.Tensor]":
@@ -309,9 +333,10 @@ class FusedConvNet:
         if self.comm is not None:
             self.comm.small_grads_ready(self)        # one-shot all-reduce of the 53 KB bucket
         ops.sgd(self.small, self.small_grad, self.lr)
-        if not self._fc_fused_done:
-            if self.comm is not None:
-                self.comm.wait_fc_grad(self)
+        fc_done = self._fc_fused_done
+        if self.comm is not None:
+            fc_done = self.comm.wait_fc_grad(self) or fc_done   # True when SGD ran inside the all-reduce
+        if not fc_done:
             ops.sgd(self.fcw, self.fcw_grad, self.lr)
 
     def train_step(self, images: torch.Tensor, labels: torch.Tensor) -> torch.Tensor:

@@ -48,6 +48,10 @@ class FusedModule(nn.Module):
             self._named[k] = nn.Parameter(v, requires_grad=True)
         self._named["fc.weight"] = nn.Parameter(eng.fcw, requires_grad=True)   # NOTE: HWC-flatten order
         eng._publish_grads = self._publish_grads
+        eng._on_rebind = self._on_rebind
+
+    def _on_rebind(self):
+        self._named["fc.weight"] = nn.Parameter(self.engine.fcw, requires_grad=True)
 
     def _publish_grads(self):
         eng = self.engine

@@ -187,6 +187,14 @@ class DistributedDataParallel(nn.Module):
             self._sync_buffers()
         return self.module(*args, **kwargs)
 
+    def train_step(self, images, labels):
+        """Fused fast path of an engine-backed module (forward + loss + backward + all-reduce +
+        SGD); includes the per-forward buffer broadcast DDP performs."""
+        if self._engine_sync is None:
+            raise AttributeError("train_step is only available when wrapping a FusedModule")
+        self._engine_sync.before_forward()
+        return self.module.train_step(images, labels)
+
     @contextlib.contextmanager
     def no_sync(self):
         old = self.require_backward_grad_sync

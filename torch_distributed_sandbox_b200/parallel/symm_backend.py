@@ -1,0 +1,300 @@
+"""Native GPU backend: collectives as our own sm_100a kernels over symmetric memory.
+
+This is what stands where ``ProcessGroupNCCL`` stands under the reference
+(``init_process_group('nccl')``, mnist_distributed.py:50): every rank maps every peer's
+buffers (CUDA VMM + fd passing, csrc/symm.cu), binds them to an NVLS multicast object when
+the platform allows, and the collectives are kernels that read/write peer memory over
+NVLink (csrc/allreduce.cu).  No NCCL call is made on any path.
+
+Buffers
+  * ``alloc_symmetric(numel, dtype)`` - collective; returns a torch tensor living in
+    symmetric memory.  ``all_reduce`` on (a slice of) such a tensor runs IN PLACE with the
+    two-shot NVLS / P2P kernel: this is how DDP gradient buckets avoid any staging copy.
+  * every other tensor goes through a 32 MiB symmetric staging buffer (one-shot kernel for
+    small messages, chunked two-shot for large ones).
+Flag channels: 0 = collectives issued on the caller's stream, 1 = the DDP side stream, so the
+overlapped bucket all-reduce never shares flag words with a concurrent small collective.
+"""
+from __future__ import annotations
+
+import ctypes
+from ctypes import c_char_p, c_float, c_int, c_size_t, c_uint32, c_void_p
+from typing import Dict, List, Optional, Tuple
+
+import torch
+
+from .. import _native
+
+ONESHOT_MAX_BYTES = 256 << 10
+STAGING_BYTES = 32 << 20
+_DT = {torch.float32: 0, torch.float64: 1, torch.int32: 2, torch.int64: 3, torch.bfloat16: 5}
+
+
+def _lib():
+    lib = _native.cuda()
+    if not getattr(lib, "_b200_symm_bound", False):
+        lib.b200_symm_comm_create.restype = c_void_p
+        lib.b200_symm_comm_create.argtypes = [c_char_p, c_int, c_int, c_int, c_int]
+        lib.b200_symm_comm_destroy.argtypes = [c_void_p]
+        lib.b200_symm_alloc.restype = c_void_p
+        lib.b200_symm_alloc.argtypes = [c_void_p, c_size_t, c_int, ctypes.POINTER(c_void_p), ctypes.POINTER(c_void_p),
+                                        ctypes.POINTER(c_size_t), ctypes.POINTER(c_void_p), c_int]
+        lib.b200_symm_free.argtypes = [c_void_p, c_void_p]
+        lib.b200_symm_topology.argtypes = [c_int, ctypes.POINTER(c_int), ctypes.POINTER(c_int), c_int]
+        lib.b200_ar_flag_bytes.restype = c_size_t
+        PP = ctypes.POINTER(c_void_p)
+        lib.b200_ar_barrier.argtypes = [PP, c_int, c_int, c_uint32, c_void_p]
+        lib.b200_ar_oneshot.argtypes = [PP, PP, c_int, c_int, c_void_p, c_size_t, c_int, c_int, c_float, c_int,
+                                        c_uint32, c_void_p]
+        lib.b200_ar_large_f32.argtypes = [PP, c_void_p, PP, PP, c_void_p, c_int, c_int, c_size_t, c_float, c_float,
+                                          c_int, c_int, c_uint32, c_void_p]
+        lib.b200_ar_nvls_bf16.argtypes = [c_void_p, PP, c_int, c_int, c_size_t, c_float, c_int, c_uint32, c_void_p]
+        lib.b200_ar_broadcast.argtypes = [PP, PP, c_int, c_int, c_void_p, c_size_t, c_int, c_int, c_uint32, c_void_p]
+        lib.b200_ar_allgather.argtypes = [PP, PP, c_int, c_int, c_void_p, c_size_t, c_int, c_uint32, c_void_p]
+        lib._b200_symm_bound = True
+    return lib
+
+
+class _CudaView:
+    """Minimal ``__cuda_array_interface__`` carrier so torch can wrap raw symmetric memory."""
+
+    def __init__(self, ptr: int, nbytes: int, owner):
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 2}
+        self._owner = owner
+
+
+class SymmBuffer:
+    def __init__(self, backend: "SymmBackend", nbytes: int, multicast: bool = True):
+        lib = _lib()
+        world = backend.size
+        ptrs = (c_void_p * 16)()
+        mc, padded, table = c_void_p(0), c_size_t(0), c_void_p(0)
+        self._backend = backend
+        self._h = lib.b200_symm_alloc(backend._comm, nbytes, 1 if multicast else 0, ptrs, ctypes.byref(mc),
+                                      ctypes.byref(padded), ctypes.byref(table), int(backend.timeout * 1000))
+        if not self._h:
+            raise RuntimeError("symmetric allocation failed: " + _native.cuda().b200_last_error().decode())
+        self.ptrs: List[int] = [int(ptrs[i] or 0) for i in range(world)]
+        self.mc: int = int(mc.value or 0)
+        self.nbytes = int(padded.value)
+        self.local = self.ptrs[backend.rank]
+        with torch.cuda.device(backend.device):
+            self.bytes_view = torch.as_tensor(_CudaView(self.local, self.nbytes, self), device=backend.device)
+
+    def tensor(self, numel: int, dtype: torch.dtype, byte_offset: int = 0) -> torch.Tensor:
+        es = torch.empty((), dtype=dtype).element_size()
+        return self.bytes_view[byte_offset: byte_offset + numel * es].view(dtype)
+
+    def ptr_array(self, byte_offset: int = 0):
+        arr = (c_void_p * 16)()
+        for i, p in enumerate(self.ptrs):
+            arr[i] = p + byte_offset
+        return arr
+
+    def free(self):
+        if self._h:
+            _lib().b200_symm_free(self._backend._comm, self._h)
+            self._h = None
+
+
+class SymmBackend:
+    name = "native"
+
+    def __init__(self, store, job: str, gid: int, ranks: Tuple[int, ...], my_global_rank: int,
+                 device: Optional[torch.device], timeout: float):
+        lib = _lib()
+        self.ranks, self.size = tuple(ranks), len(ranks)
+        self.rank = self.ranks.index(my_global_rank)
+        self.device = torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
+        self.timeout = timeout
+        self._buffers: List[SymmBuffer] = []
+        self._comm = None
+        self.epoch = [4, 4]
+        if self.size == 1:
+            self.multicast = False
+            return
+        torch.cuda.set_device(self.device)
+        tag = f"b200dp_{job}_{gid}".encode()
+        self._comm = lib.b200_symm_comm_create(tag, self.rank, self.size, self.device.index, int(timeout * 1000))
+        if not self._comm:
+            raise RuntimeError("symmetric-memory bring-up failed: " + _native.cuda().b200_last_error().decode())
+        fb = int(lib.b200_ar_flag_bytes())
+        self._flags = SymmBuffer(self, 2 * fb, multicast=False)
+        self._flag_arr = [self._flags.ptr_array(0), self._flags.ptr_array(fb)]
+        self._staging = SymmBuffer(self, STAGING_BYTES, multicast=True)
+        self._buffers += [self._flags, self._staging]
+        self.multicast = self._staging.mc != 0
+        self.comm_stream = torch.cuda.Stream(device=self.device, priority=-1)
+
+    # ------------------------------------------------------------- helpers --
+    def describe(self) -> Dict:
+        return {"backend": "native-symmetric", "world": self.size, "nvls_multicast": bool(self.multicast)}
+
+    def topology(self) -> Dict:
+        n = torch.cuda.device_count()
+        p2p, at = (c_int * 64)(), (c_int * 64)()
+        cnt = _lib().b200_symm_topology(self.device.index, p2p, at, 64)
+        return {"devices": cnt, "p2p": [int(p2p[i]) for i in range(min(cnt, n))],
+                "native_atomics": [int(at[i]) for i in range(min(cnt, n))], "multicast": bool(self.multicast)}
+
+    def _next_epoch(self, channel: int) -> int:
+        e = self.epoch[channel]
+        self.epoch[channel] = (e + 4) & 0xFFFFFFFF
+        return e
+
+    @staticmethod
+    def _stream() -> c_void_p:
+        return c_void_p(torch.cuda.current_stream().cuda_stream)
+
+    def alloc_symmetric(self, numel: int, dtype: torch.dtype = torch.float32, multicast: bool = True) -> torch.Tensor:
+        """COLLECTIVE.  A zero-initialised tensor in symmetric (peer-mapped, multicast-bound) memory."""
+        es = torch.empty((), dtype=dtype).element_size()
+        if self.size == 1:
+            return torch.zeros(numel, dtype=dtype, device=self.device)
+        buf = SymmBuffer(self, max(numel * es, 16), multicast=multicast)
+        self._buffers.append(buf)
+        return buf.tensor(numel, dtype)
+
+    def lookup(self, t: torch.Tensor) -> Optional[Tuple[SymmBuffer, int]]:
+        p = t.data_ptr()
+        for b in self._buffers:
+            if b.local <= p < b.local + b.nbytes:
+                return b, p - b.local
+        return None
+
+    def _blocks(self, nbytes: int) -> int:
+        return max(1, min(64, (nbytes + (1 << 16) - 1) >> 16))
+
+    # --------------------------------------------------------- collectives --
+    def all_reduce(self, t: torch.Tensor, op, channel: int = 0, sgd: Optional[Tuple[torch.Tensor, float]] = None,
+                   scale: Optional[float] = None, algo: Optional[str] = None, blocks: Optional[int] = None):
+        """In-place all-reduce.  ``sgd=(weights, lr)`` fuses ``weights -= lr * result`` into the
+        reduction epilogue (both tensors must be symmetric, fp32, same shape)."""
+        op = int(op)
+        if self.size == 1:
+            if sgd is not None:
+                sgd[0].add_(t.view_as(sgd[0]), alpha=-float(sgd[1]) * (scale or 1.0))
+            return None
+        if t.dtype not in _DT:
+            raise RuntimeError(f"all_reduce: dtype {t.dtype} not supported by the native backend")
+        if not t.is_cuda:
+            raise RuntimeError("all_reduce on the native backend needs a CUDA tensor (use backend='gloo' for CPU)")
+        if scale is None:
+            scale = 1.0 / self.size if op == 1 else 1.0
+        if op == 1:
+            if not t.dtype.is_floating_point:
+                raise RuntimeError("ReduceOp.AVG needs a floating-point tensor")
+            op = 0
+        lib, es = _lib(), t.element_size()
+        nbytes = t.numel() * es
+        flat = t.contiguous().view(-1) if not t.is_contiguous() else t.view(-1)
+        sym = self.lookup(flat)
+        large_ok = t.dtype == torch.float32 and op == 0 and nbytes > ONESHOT_MAX_BYTES
+        if large_ok and sym is not None and sym[1] % 16 == 0 and flat.numel() % 4 == 0:
+            buf, off = sym
+            use_nvls = (algo or ("nvls" if buf.mc else "p2p")) == "nvls"
+            w_arr, w_mc, lr = None, None, 0.0
+            if sgd is not None:
+                wsym = self.lookup(sgd[0])
+                if wsym is None or sgd[0].numel() != flat.numel():
+                    raise RuntimeError("fused SGD needs the weights in symmetric memory with the gradient's shape")
+                w_arr, w_mc, lr = wsym[0].ptr_array(wsym[1]), (wsym[0].mc + wsym[1]) if wsym[0].mc else 0, float(sgd[1])
+                use_nvls = use_nvls and bool(w_mc)
+            rc = lib.b200_ar_large_f32(buf.ptr_array(off), (buf.mc + off) if buf.mc else 0, self._flag_arr[channel],
+                                       w_arr, w_mc, self.rank, self.size, flat.numel(), scale, lr,
+                                       2 if use_nvls else 1, blocks or 64, self._next_epoch(channel), self._stream())
+            _native.check(rc, "all_reduce(large)")
+        else:
+            if sgd is not None:
+                raise RuntimeError("fused SGD is only available on symmetric fp32 buckets")
+            # staged path: chunks through the symmetric staging buffer
+            st = self._staging
+            chunk = (STAGING_BYTES if large_ok else min(STAGING_BYTES, ONESHOT_MAX_BYTES * 16)) // es
+            for s in range(0, flat.numel(), chunk):
+                part = flat[s:s + chunk]
+                n = part.numel()
+                stage = st.tensor(n, t.dtype)
+                stage.copy_(part)
+                if large_ok and n % 4 == 0 and n * es > ONESHOT_MAX_BYTES:
+                    use_nvls = (algo or ("nvls" if st.mc else "p2p")) == "nvls"
+                    rc = lib.b200_ar_large_f32(st.ptr_array(0), st.mc or 0, self._flag_arr[channel], None, None,
+                                               self.rank, self.size, n, scale, 0.0, 2 if use_nvls else 1,
+                                               blocks or 64, self._next_epoch(channel), self._stream())
+                    _native.check(rc, "all_reduce(staged large)")
+                    part.copy_(stage)
+                else:
+                    rc = lib.b200_ar_oneshot(st.ptr_array(0), self._flag_arr[channel], self.rank, self.size,
+                                             c_void_p(part.data_ptr()), n, _DT[t.dtype], op, scale,
+                                             self._blocks(n * es), self._next_epoch(channel), self._stream())
+                    _native.check(rc, "all_reduce(one-shot)")
+            if flat.data_ptr() != t.data_ptr():
+                t.copy_(flat.view_as(t))
+        from ..distributed import Work
+        ev = torch.cuda.Event()
+        ev.record()
+        return Work(ev)
+
+    def _padded_io(self, t: torch.Tensor):
+        """(contiguous byte view padded to 16 B, needs_copy_back)"""
+        flat = t.contiguous().view(-1).view(torch.uint8)
+        if flat.numel() % 16 == 0 and flat.data_ptr() % 16 == 0 and t.is_contiguous():
+            return flat, False
+        pad = torch.zeros((flat.numel() + 15) // 16 * 16, dtype=torch.uint8, device=t.device)
+        pad[:flat.numel()].copy_(flat)
+        return pad, True
+
+    def broadcast(self, t: torch.Tensor, src: int, channel: int = 0):
+        if self.size == 1:
+            return None
+        io, copy_back = self._padded_io(t)
+        lib, st = _lib(), self._staging
+        for s in range(0, io.numel(), STAGING_BYTES):
+            part = io[s:s + STAGING_BYTES]
+            if self.rank == src:
+                st.bytes_view[:part.numel()].copy_(part)
+            rc = lib.b200_ar_broadcast(st.ptr_array(0), self._flag_arr[channel], self.rank, self.size,
+                                       c_void_p(part.data_ptr()), part.numel(), src, self._blocks(part.numel()),
+                                       self._next_epoch(channel), self._stream())
+            _native.check(rc, "broadcast")
+        if copy_back:
+            t.copy_(io[:t.numel() * t.element_size()].view(t.dtype).view(t.shape))
+        return None
+
+    def all_gather(self, out: torch.Tensor, t: torch.Tensor, channel: int = 0):
+        if self.size == 1:
+            out.view(-1).copy_(t.view(-1))
+            return None
+        nb = t.numel() * t.element_size()
+        if nb > STAGING_BYTES:
+            raise RuntimeError("all_gather: per-rank tensor exceeds the 32 MiB staging buffer")
+        pad = (nb + 15) // 16 * 16
+        st = self._staging
+        st.bytes_view[:nb].copy_(t.contiguous().view(-1).view(torch.uint8))
+        tmp = torch.empty(self.size * pad, dtype=torch.uint8, device=t.device)
+        rc = _lib().b200_ar_allgather(st.ptr_array(0), self._flag_arr[channel], self.rank, self.size,
+                                      c_void_p(tmp.data_ptr()), pad, self._blocks(pad), self._next_epoch(channel),
+                                      self._stream())
+        _native.check(rc, "all_gather")
+        out.view(-1).view(torch.uint8).copy_(tmp.view(self.size, pad)[:, :nb].reshape(-1))
+        return None
+
+    def barrier(self, channel: int = 0):
+        if self.size == 1:
+            torch.cuda.synchronize(self.device)
+            return
+        rc = _lib().b200_ar_barrier(self._flag_arr[channel], self.rank, self.size, self._next_epoch(channel),
+                                    self._stream())
+        _native.check(rc, "barrier")
+        torch.cuda.current_stream().synchronize()
+
+    def close(self):
+        if self._comm:
+            try:
+                torch.cuda.synchronize(self.device)
+            except Exception:
+                pass
+            for b in reversed(self._buffers):
+                b.free()
+            self._buffers = []
+            _lib().b200_symm_comm_destroy(self._comm)
+            self._comm = None
