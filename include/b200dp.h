@@ -1,0 +1,149 @@
+/* b200dp C ABI - everything the two native libraries export.
+ *
+ *   libb200dp_cuda.so   sm_100a kernels + symmetric-memory runtime   (b200_*)
+ *   libb200dp_host.so   TCP store, shared-memory collectives, DDP bucket planner (b200h_*)
+ *
+ * Conventions: every b200_* entry point returns 0 on success, non-zero on failure, and
+ * b200_last_error() returns the message of the calling thread's last failure.  Pointers are
+ * device pointers unless the name says host; `stream` is a cudaStream_t.  Activations are bf16
+ * NHWC, parameters / gradients / statistics fp32.  No entry point allocates device memory
+ * unless it says so; callers own every buffer, including scratch ("partials").
+ *
+ * Citations "ref:" point at the reference repo (AditMeh/torch-distributed-sandbox) call site
+ * whose behaviour the entry point provides; "K#/C#/D#" are the SURVEY.md inventory rows.
+ */
+#ifndef B200DP_H
+#define B200DP_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ------------------------------------------------------------------ common --- */
+const char* b200_last_error(void);
+int b200_sm_count(void);
+int b200_l2_flush(void* buf, size_t bytes, void* stream);            /* timing hygiene helper */
+
+/* ------------------------------------------------- input pipeline (K1/K2) --- */
+/* ref: transforms.Resize(IMAGE_SHAPE) + ToTensor, mnist_onegpu.py:53 / mnist_distributed.py:71.
+ * uint8 [B,sh,sw] -> fp32 [B,H,W]; bit-exact with Pillow's 8-bit bilinear resample + /255. */
+int b200_resize_pil_bilinear(const void* src_u8, int B, int sh, int sw, const void* xtab_i32, const void* ytab_i32,
+                             void* dst_f32, int H, int W, void* stream);
+
+/* ------------------------------------------------ layer 1 (K3/K4/K5/K13) --- */
+/* ref: nn.Conv2d(1,16,5,1,2) forward, mnist_distributed.py:29.  partials: [b200_conv1_fwd_grid()][32]. */
+int b200_conv1_fwd_grid(void);
+int b200_conv1_fwd(const void* in_f32, const void* w1, const void* b1, void* x1_bf16, void* partials, int B, int H,
+                   int W, void* stream);
+/* ref: nn.BatchNorm2d train-mode statistics + running-stat update, mnist_distributed.py:30,35.
+ * out = [scale | shift | mean | rstd] (4*C floats). */
+int b200_bn_finalize(const void* partials, int nparts, int C, double count, const void* gamma, const void* beta,
+                     void* running_mean, void* running_var, void* num_batches_tracked_i64, float momentum, float eps,
+                     void* out, void* stream);
+/* ref: BatchNorm2d apply + nn.ReLU + nn.MaxPool2d(2,2), mnist_distributed.py:30-32,35-37. C in {16,32}. */
+int b200_bn_relu_pool(const void* x_bf16, const void* bn, void* p_bf16, int B, int H, int W, int C, void* stream);
+/* ref: loss.backward() through MaxPool2d/ReLU/BatchNorm2d, mnist_distributed.py:96.
+ * mode 0: partials [b200_pool_bn_bwd_grid()][2C];  mode 1: dx (may alias x). */
+int b200_pool_bn_bwd_grid(void);
+int b200_pool_bn_bwd(const void* x_bf16, const void* dp_bf16, const void* bn, const void* red, void* partials,
+                     void* dx_bf16, int B, int H, int W, int C, int mode, void* stream);
+int b200_bn_bwd_finalize(const void* partials, int nparts, int C, double count, void* red, void* dgamma, void* dbeta,
+                         float gscale, void* stream);
+/* ref: conv1 weight gradient inside loss.backward().  partials: [b200_conv1_wgrad_grid()][400] scratch. */
+int b200_conv1_wgrad_grid(void);
+int b200_conv1_wgrad(const void* in_f32, const void* x1_bf16, const void* dp1_bf16, const void* bn, const void* red,
+                     void* partials, void* dw1, int B, int H, int W, float gscale, void* stream);
+
+/* ------------------------------------------- layer 2, tcgen05 (K6/K12) --- */
+/* ref: nn.Conv2d(16,32,5,1,2) forward / input gradient / weight gradient (cuDNN in the reference),
+ * mnist_distributed.py:34,96.  partials (fwd): [b200_conv_tc_max_grid()][64];
+ * partials (wgrad): [b200_conv_tc_max_grid()][12800] scratch. */
+int b200_conv_tc_max_grid(void);
+int b200_conv2_fwd_tc(const void* p1_bf16, const void* w2, const void* b2, void* x2_bf16, void* partials, int B, int H,
+                      int W, int* nparts_out, void* stream);
+int b200_conv2_dgrad_tc(const void* dx2_bf16, const void* w2, void* dp1_bf16, int B, int H, int W, void* stream);
+int b200_conv2_wgrad_tc(const void* p1_bf16, const void* dx2_bf16, void* partials, void* dw2, int B, int H, int W,
+                        float gscale, void* stream);
+
+/* --------------------------------------------- head + loss (K8/K9/K10) --- */
+/* ref: nn.LazyLinear(10) forward/backward and nn.CrossEntropyLoss, mnist_distributed.py:38,44,64,91,96.
+ * W is [10][F] in HWC-flatten order; batch chunks of <= 8 rows.  partials: [b200_fc_grid()][80]. */
+int b200_fc_grid(void);
+int b200_fc_fwd(const void* p2_bf16, const void* W, const void* bias, void* partials, void* logits, int bt, size_t F,
+                void* stream);
+int b200_cross_entropy(const void* logits, const void* labels_i64, int B, void* loss, void* dlogits, void* dbias,
+                       float gscale, void* stream);
+int b200_fc_bwd(const void* dlogits, const void* p2_bf16, void* W, void* dW_or_null, void* dp2_bf16, int bt, size_t F,
+                float lr_fused_sgd, int accumulate, float gscale, void* stream);
+
+/* ------------------------------------------------------ optimizer (K14) --- */
+/* ref: torch.optim.SGD(model.parameters(), 1e-4).step(), mnist_distributed.py:65,97. */
+int b200_sgd(void* p, const void* g, size_t n, float lr, void* stream);
+
+/* ----------------------------------------------------- layout helpers --- */
+int b200_reduce_partials(const void* partials, int nparts, int len, void* out, float scale, void* stream);
+int b200_fcw_permute(const void* src, void* dst, int C, int Hd, int Wd, int to_hwc, void* stream);
+int b200_nhwc_bf16_to_nchw_f32(const void* src, void* dst, int B, int C, int H, int W, void* stream);
+int b200_nchw_f32_to_nhwc_bf16(const void* src, void* dst, int B, int C, int H, int W, void* stream);
+
+/* ------------------------------------- symmetric memory (W3) --- */
+/* ref: what ProcessGroupNCCL sets up under dist.init_process_group('nccl'), mnist_distributed.py:50.
+ * All of these are COLLECTIVE over the group and allocate (cold path). */
+void* b200_symm_comm_create(const char* tag, int rank, int world, int device, int timeout_ms);
+void b200_symm_comm_destroy(void* comm);
+int b200_symm_multicast_supported(int device);
+void* b200_symm_alloc(void* comm, size_t bytes, int want_multicast, void** ptrs_out, void** mc_out,
+                      size_t* padded_out, void** dev_table_out, int timeout_ms);
+void b200_symm_free(void* comm, void* alloc);
+int b200_symm_topology(int device, int* p2p_out, int* native_atomics_out, int cap);
+
+/* -------------------------------------------- collectives (K16, C1-C6) --- */
+/* ref: dist.all_reduce / dist.barrier / DDP's bucket all-reduce and broadcasts,
+ * allreduce_toy.py:31,33; mnist_distributed.py:67,96.  ptrs/flags: host arrays of `world` device VAs
+ * (this process's mappings of every rank's buffer / flag page).  Each call consumes up to 4 epochs. */
+size_t b200_ar_flag_bytes(void);
+int b200_ar_max_blocks(void);
+int b200_ar_barrier(void* const* flags, int rank, int world, uint32_t epoch, void* stream);
+int b200_ar_oneshot(void* const* ptrs, void* const* flags, int rank, int world, void* out, size_t n, int dtype, int op,
+                    float scale, int blocks, uint32_t epoch, void* stream);
+int b200_ar_large_f32(void* const* ptrs, void* mc, void* const* flags, void* const* wptrs, void* wmc, int rank,
+                      int world, size_t n, float scale, float lr, int algo, int blocks, uint32_t epoch, void* stream);
+int b200_ar_nvls_bf16(void* mc, void* const* flags, int rank, int world, size_t n, float scale, int blocks,
+                      uint32_t epoch, void* stream);
+int b200_ar_broadcast(void* const* ptrs, void* const* flags, int rank, int world, void* out, size_t bytes, int root,
+                      int blocks, uint32_t epoch, void* stream);
+int b200_ar_allgather(void* const* ptrs, void* const* flags, int rank, int world, void* out, size_t bytes, int blocks,
+                      uint32_t epoch, void* stream);
+
+/* =========================================================== host library === */
+/* ref: the TCPStore behind env:// rendezvous, test_init.py:76-91 (D2). */
+const char* b200h_last_error(void);
+void* b200h_store_server_start(const char* host, int port, int* actual_port);
+void b200h_store_server_stop(void* server);
+void* b200h_store_connect(const char* host, int port, int timeout_ms);
+void b200h_store_close(void* client);
+int b200h_store_set(void* client, const char* key, const void* val, int len);
+int b200h_store_get(void* client, const char* key, void* buf, int cap, int* len_out, int timeout_ms);
+int b200h_store_add(void* client, const char* key, long long delta, long long* result);
+int b200h_store_check(void* client, const char* key);
+int b200h_store_delete(void* client, const char* key);
+long long b200h_store_num_keys(void* client);
+/* ref: the gloo backend of test_init.py:55 (CPU collectives; D3-D6). dtype: 0 f32,1 f64,2 i32,3 i64,4 u8,5 bf16;
+ * op: 0 SUM,1 AVG,2 MAX,3 MIN,4 PROD. */
+const char* b200h_coll_last_error(void);
+void* b200h_coll_open(const char* name, int rank, int world, int is_creator, size_t slot_bytes, int timeout_ms);
+void b200h_coll_close(void* group, int unlink_segment);
+int b200h_coll_barrier(void* group);
+int b200h_coll_allreduce(void* group, void* data, size_t count, int dtype, int op);
+int b200h_coll_broadcast(void* group, void* data, size_t bytes, int root);
+int b200h_coll_allgather(void* group, const void* in, void* out, size_t bytes);
+/* ref: torch Reducer's compute_bucket_assignment_by_size behind DistributedDataParallel, mnist_distributed.py:67 (D7). */
+int b200h_plan_buckets(const int64_t* sizes, const int32_t* keys, int n, const int64_t* limits, int nlimits,
+                       int32_t* bucket_of);
+int64_t b200h_bucket_offsets(const int64_t* numels, int n, int64_t align_elems, int64_t* offsets);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200DP_H */

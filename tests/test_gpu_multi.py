@@ -119,8 +119,9 @@ def _ddp_engine(rank, world, port, out_path):
         ddp.train_step(xs[s, rank].to(dev), ys[s, rank].to(dev))
     torch.cuda.synchronize()
     sd = model.engine.state_dict()
-    # every rank must hold bit-identical parameters
-    for k in ("fc.weight", "layer2.0.weight", "layer1.1.running_mean"):
+    # every rank must hold bit-identical parameters (BatchNorm buffers are rank-local between a
+    # step and the next forward's broadcast, exactly as under torch DDP, so they are not compared)
+    for k in ("fc.weight", "layer2.0.weight", "layer1.0.weight", "fc.bias"):
         mine = sd[k].flatten()[:4096].float().contiguous()
         allv = [torch.zeros_like(mine) for _ in range(world)]
         dist.all_gather(allv, mine)
