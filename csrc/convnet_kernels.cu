@@ -14,6 +14,7 @@
 #include "common.h"
 #include "ptx.cuh"
 #include <cstdint>
+#include <mutex>
 
 using b2::bf16_hi;
 using b2::bf16_lo;
@@ -840,6 +841,72 @@ B200_API int b200_conv1_wgrad(const void* in_f32, const void* x1, const void* dp
                                           (float*)partials, B, H, W, tilesX, tilesY);
   B200_LAUNCH_CHECK();
   reduce_partials_kernel<<<(400 + 127) / 128, 128, 0, s>>>((const float*)partials, grid, 400, (float*)dw1, gscale);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------------
+// Allocation-free variant of the conv1 weight gradient.
+//
+// b200_conv1_wgrad needs [grid][400] floats of scratch for its per-block partial sums and
+// leaves it to the caller to provide them.  Some callers cannot: code running inside a CUDA
+// stream capture or under a memory-pool policy that forbids new allocations, a host
+// application that hands this library a fixed memory budget up front, or a thin C/Fortran
+// driver that only owns its input and output arrays.  For them the scratch lives here, in a
+// file-scope device array that every GPU loading this library carries until the process exits
+// (kNoAllocMaxBlocks * 400 floats = 256,000 bytes per GPU).
+//
+// In host code the array's name is only a host-side stand-in for the symbol; the device
+// address is obtained once per device with cudaGetSymbolAddress (with that device current) and
+// is what the kernel receives.
+constexpr int kNoAllocMaxBlocks = 160;
+static __device__ __align__(256) float g_conv1_wgrad_scratch[kNoAllocMaxBlocks * 400];
+static float* g_conv1_wgrad_scratch_addr[64];   // per device ordinal; filled by the first call on that device
+static std::mutex g_conv1_wgrad_scratch_mu;
+
+B200_API int b200_conv1_wgrad_noalloc_max_blocks() { return kNoAllocMaxBlocks; }
+
+// Same inputs and output as b200_conv1_wgrad, without the `partials` argument.
+//   nblocks  number of thread blocks (= partial rows) to use; 0 picks the device's SM count.
+//            Values above b200_conv1_wgrad_noalloc_max_blocks() are rejected: the built-in
+//            scratch cannot hold them - use b200_conv1_wgrad with your own scratch instead.
+// The first call on each device looks up the scratch address (no allocation, but a driver
+// query): make that first call outside any stream capture.  All calls on a device share the one
+// array, which keeps the previous call's partial sums: nothing in it has to be zero on entry
+// (every one of the nblocks rows is overwritten by its block before the reduction reads it, rows
+// beyond nblocks are never read), but two calls whose kernels overlap on the GPU - different
+// streams, or different host threads - race on it and must be serialised by the caller.
+// Makes no call to cudaMalloc, cudaFree or any other allocating routine.
+B200_API int b200_conv1_wgrad_noalloc(const void* in_f32, const void* x1, const void* dp1, const void* bn,
+                                      const void* red, void* dw1, int B, int H, int W, float gscale, int nblocks,
+                                      void* stream) {
+  B200_CHECK(H % 2 == 0 && W % 2 == 0, "conv1_wgrad_noalloc: H and W must be even");
+  B200_CHECK(nblocks >= 0, "conv1_wgrad_noalloc: nblocks must be >= 0 (got %d)", nblocks);
+  const int grid = nblocks == 0 ? b200_num_sms() : nblocks;
+  B200_CHECK(grid <= kNoAllocMaxBlocks,
+             "conv1_wgrad_noalloc: %d partial rows of 400 floats requested but the built-in scratch holds %d "
+             "(%zu bytes); call b200_conv1_wgrad with caller-provided scratch for larger grids",
+             grid, kNoAllocMaxBlocks, sizeof(float) * 400 * (size_t)kNoAllocMaxBlocks);
+  int dev = -1;
+  B200_CUDA(cudaGetDevice(&dev));
+  B200_CHECK(dev >= 0 && dev < 64, "conv1_wgrad_noalloc: device ordinal %d out of range", dev);
+  float* scratch = nullptr;
+  {
+    std::lock_guard<std::mutex> lk(g_conv1_wgrad_scratch_mu);
+    if (g_conv1_wgrad_scratch_addr[dev] == nullptr) {          // set-up: once per device, that device current
+      float* p = nullptr;
+      B200_CUDA(cudaGetSymbolAddress((void**)&p, g_conv1_wgrad_scratch));
+      B200_CHECK(p != nullptr, "conv1_wgrad_noalloc: cudaGetSymbolAddress returned a null address");
+      g_conv1_wgrad_scratch_addr[dev] = p;
+    }
+    scratch = g_conv1_wgrad_scratch_addr[dev];
+  }
+  cudaStream_t s = (cudaStream_t)stream;
+  const int tilesX = (W + kWgT - 1) / kWgT, tilesY = (H + kWgT - 1) / kWgT;
+  conv1_wgrad_kernel<<<grid, 256, 0, s>>>((const float*)in_f32, (const __nv_bfloat16*)x1, (const __nv_bfloat16*)dp1,
+                                          (const float*)bn, (const float*)red, scratch, B, H, W, tilesX, tilesY);
+  B200_LAUNCH_CHECK();
+  reduce_partials_kernel<<<(400 + 127) / 128, 128, 0, s>>>(scratch, grid, 400, (float*)dw1, gscale);
   B200_LAUNCH_CHECK();
   return 0;
 }

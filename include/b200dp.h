@@ -55,6 +55,19 @@ int b200_conv1_wgrad_grid(void);
 int b200_conv1_wgrad(const void* in_f32, const void* x1_bf16, const void* dp1_bf16, const void* bn, const void* red,
                      void* partials, void* dw1, int B, int H, int W, float gscale, void* stream);
 
+/* Allocation-free variant of b200_conv1_wgrad.  No counterpart in the reference: it exists for callers
+ * that cannot obtain device scratch themselves (inside a stream capture or a no-new-allocations memory
+ * policy, a fixed up-front memory budget, a thin driver that owns only its inputs and outputs).  The
+ * per-block partial sums go to a 256,000-byte device array built into the library (one per GPU, held
+ * until exit) instead of a caller buffer.  nblocks = thread blocks / partial rows (0: the SM count);
+ * more than b200_conv1_wgrad_noalloc_max_blocks() (160) is rejected.  The first call on each device
+ * resolves the array's address - make it outside stream capture.  All calls on a device share the
+ * array: serialise calls that could overlap on the GPU.  Never calls cudaMalloc/cudaFree. */
+int b200_conv1_wgrad_noalloc_max_blocks(void);
+int b200_conv1_wgrad_noalloc(const void* in_f32, const void* x1_bf16, const void* dp1_bf16, const void* bn,
+                             const void* red, void* dw1, int B, int H, int W, float gscale, int nblocks,
+                             void* stream);
+
 /* ------------------------------------------- layer 2, tcgen05 (K6/K12) --- */
 /* ref: nn.Conv2d(16,32,5,1,2) forward / input gradient / weight gradient (cuDNN in the reference),
  * mnist_distributed.py:34,96.  partials (fwd): [b200_conv_tc_max_grid()][64];
