@@ -414,6 +414,467 @@ conv5x5_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tm_act, const __grid
   if (warp == 1) { __syncwarp(); tmem_dealloc<kWgTmemCols>(tmem_base); }
 }
 
+// ======================================================= v2: row-stationary ===
+// Same operands, different loop nest.  v1 issues one M=128,N=COUT MMA per filter tap and
+// output row (25 per row): every one of them re-reads its 4 KB A tile from shared memory for
+// only 16 (N=32) cycles of math, so the kernel is bound by smem operand bandwidth and by the
+// per-instruction cost, not by the tensor pipe.  v2 keeps the INPUT row stationary instead:
+// for input row r and horizontal tap dx, ONE MMA with N = 5*COUT multiplies the row (shifted
+// by dx) with the weights of all five vertical taps at once; column block jj = 4-dy of the
+// result belongs to output row r-2+jj.  The accumulators of consecutive output rows sit in
+// consecutive TMEM column blocks of a 16-deep ring, so that single MMA accumulates straight
+// into five different output rows.  5 (x CIN/16) fat MMAs per row instead of 25 thin ones,
+// each input row is needed only while its own MMAs run, and the epilogue is unchanged.
+template <int CIN, int COUT>
+struct RsCfg {
+  static constexpr int kPlanes = CIN / 8;
+  static constexpr int kSlotBytes = kPlanes * kPlaneBytes;
+  static constexpr int kSlots = 8;
+  static constexpr int kKSteps = CIN / 16;
+  static constexpr int kNB = 5 * COUT;                       // B rows per (dx, kk): n = jj*COUT + co
+  static constexpr int kWChunkBytes = kNB * 16;              // one 8-channel k-chunk of all n rows
+  static constexpr int kWStepBytes = 2 * kWChunkBytes;       // one (dx, kk) B tile
+  static constexpr int kWBytes = 5 * kKSteps * kWStepBytes;  // == 25*CIN*COUT*2
+  static constexpr int kTStages = 16;
+  static constexpr int kTmemCols = kTStages * COUT;          // 512 (COUT=32) / 256 (COUT=16)
+  static constexpr int kSmemBytes = kWBytes + kSlots * kSlotBytes + 2048 + 128;
+  static_assert(kWBytes % 128 == 0 && kSlotBytes % 128 == 0, "alignment");
+  static_assert(kTmemCols <= 512 && (kTmemCols & (kTmemCols - 1)) == 0, "TMEM columns");
+};
+
+// Operand feed: LDGSTS=false uses TMA (one 5-D tensor-map request per plane and row; measured
+// ~4-7 cycles per 16-byte box row, i.e. 1-3 k cycles per image row: the bottleneck of v2);
+// LDGSTS=true has the whole producer warp issue 16-byte cp.async copies (zero-fill = padding),
+// 9-25 warp instructions per row, software-pipelined kCpDepth rows deep with wait_group,
+// then fence.proxy.async + one mbarrier arrive per row.
+constexpr int kCpDepth = 3;
+
+template <int C>
+__device__ __forceinline__ void cp_row(uint8_t* dst, const __nv_bfloat16* __restrict__ src, int b, int y, int x_first,
+                                       int npix, int plane_bytes, int H, int W, int lane) {
+  // dst: [C/8 planes][npix][16 B];  src pixel (b, y, x_first + p), channels plane*8..+7
+  const bool row_ok = (y >= 0) && (y < H);
+  const __nv_bfloat16* row = src + ((size_t)b * H + (row_ok ? y : 0)) * (size_t)W * C;
+  const int total = (C / 8) * npix;
+  for (int i = lane; i < total; i += 32) {
+    const int pl = i / npix, p = i - pl * npix;
+    const int x = x_first + p;
+    const bool ok = row_ok && x >= 0 && x < W;
+    cp_async16(dst + pl * plane_bytes + p * 16, row + (size_t)(ok ? x : 0) * C + pl * 8, ok ? 16u : 0u);
+  }
+}
+
+template <int CIN, int COUT, bool TRANSPOSED, bool STATS, bool LDGSTS>
+__global__ void __launch_bounds__(kThreads, 1)
+conv5x5_rs_kernel(const __grid_constant__ CUtensorMap tm_act, const __nv_bfloat16* __restrict__ act,
+                  const float* __restrict__ w,
+                  const float* __restrict__ bias, __nv_bfloat16* __restrict__ out,
+                  float* __restrict__ partials, ConvGeom g) {
+  using Cfg = RsCfg<CIN, COUT>;
+  constexpr int RT = Cfg::kTStages;
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((128u - (smem_u32(smem_raw) & 127u)) & 127u);
+  uint8_t* s_w = smem;
+  uint8_t* s_slots = smem + Cfg::kWBytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_slots + Cfg::kSlots * Cfg::kSlotBytes);
+  uint64_t* full = bars;
+  uint64_t* empty = bars + Cfg::kSlots;
+  uint64_t* tfull = empty + Cfg::kSlots;       // [RT]
+  uint64_t* tempty = tfull + RT;               // [RT]
+  uint32_t* s_tmem = reinterpret_cast<uint32_t*>(tempty + RT);
+  float* s_bias = reinterpret_cast<float*>(s_tmem + 4);
+  float* s_stat = s_bias + COUT;               // [4][2*COUT]
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  // weights: byte(dx, kk, c, n=(jj,co), e) = ((((dx*KSTEPS + kk)*2 + c)*kNB + n)*8 + e)*2, dy = 4 - jj
+  for (int i = threadIdx.x; i < kTaps * CIN * COUT; i += kThreads) {
+    const int e = i & 7;
+    int r = i >> 3;
+    const int n = r % Cfg::kNB; r /= Cfg::kNB;
+    const int c = r & 1; r >>= 1;
+    const int kk = r % Cfg::kKSteps;
+    const int dx = r / Cfg::kKSteps;
+    const int jj = n / COUT, co = n % COUT;
+    const int tap = (4 - jj) * 5 + dx;
+    const int k = kk * 16 + c * 8 + e;
+    const float v = TRANSPOSED ? w[((size_t)k * COUT + co) * kTaps + (kTaps - 1 - tap)]
+                               : w[((size_t)co * CIN + k) * kTaps + tap];
+    reinterpret_cast<__nv_bfloat16*>(s_w)[i] = __float2bfloat16_rn(v);
+  }
+  if (threadIdx.x < COUT) s_bias[threadIdx.x] = bias ? bias[threadIdx.x] : 0.f;
+  fence_proxy_async_smem();
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < Cfg::kSlots; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+    for (int i = 0; i < RT; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], 128); }
+    mbar_fence_init();
+    tma_prefetch_desc(&tm_act);
+  }
+  if (warp == 1) tmem_alloc<Cfg::kTmemCols>(s_tmem);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *s_tmem;
+
+  if (warp == 0) {
+    if (LDGSTS) {
+      // whole warp: cp.async feed, kCpDepth rows in flight
+      uint32_t gcount = 0;          // rows issued
+      uint32_t gdone = 0;           // rows published
+      for (int item = blockIdx.x; item < g.nitems; item += gridDim.x) {
+        const int seg = item % g.nseg;
+        const int strip = (item / g.nseg) % g.nstrips;
+        const int b = item / (g.nseg * g.nstrips);
+        const int y0 = seg * g.rseg;
+        const int rows = min(g.rseg, g.H - y0);
+        const int x0 = strip * kBM;
+        for (int i = 0; i < rows + 4; ++i, ++gcount) {
+          const uint32_t slot = gcount % Cfg::kSlots, use = gcount / Cfg::kSlots;
+          mbar_wait(&empty[slot], (use & 1) ^ 1);
+          cp_row<CIN>(s_slots + slot * Cfg::kSlotBytes, act, b, y0 - 2 + i, x0 - 2, kPW, kPlaneBytes, g.H, g.W, lane);
+          cp_async_commit();
+          if (gcount >= (uint32_t)kCpDepth) {
+            cp_async_wait<kCpDepth>();
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&full[gdone % Cfg::kSlots]);
+            ++gdone;
+          }
+        }
+      }
+      cp_async_wait<0>();
+      fence_proxy_async_smem();
+      __syncwarp();
+      for (; gdone < gcount; ++gdone)
+        if (lane == 0) mbar_arrive(&full[gdone % Cfg::kSlots]);
+    } else if (lane == 0) {
+      uint32_t gcount = 0;
+      for (int item = blockIdx.x; item < g.nitems; item += gridDim.x) {
+        const int seg = item % g.nseg;
+        const int strip = (item / g.nseg) % g.nstrips;
+        const int b = item / (g.nseg * g.nstrips);
+        const int y0 = seg * g.rseg;
+        const int rows = min(g.rseg, g.H - y0);
+        const int x0 = strip * kBM;
+        for (int i = 0; i < rows + 4; ++i, ++gcount) {
+          const uint32_t slot = gcount % Cfg::kSlots, use = gcount / Cfg::kSlots;
+          mbar_wait(&empty[slot], (use & 1) ^ 1);
+          mbar_expect_tx(&full[slot], Cfg::kSlotBytes);
+          uint8_t* dst = s_slots + slot * Cfg::kSlotBytes;
+#pragma unroll
+          for (int p = 0; p < Cfg::kPlanes; ++p)
+            tma_load_5d(dst + p * kPlaneBytes, &tm_act, &full[slot], 0, p, x0 - 2, y0 - 2 + i, b);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc0 = umma_idesc_bf16(kBM, 0, 0, 0);          // N filled in per MMA
+      const uint32_t slots_addr = smem_u32(s_slots);
+      const uint64_t a_tmpl = smem_desc_noswz(0, kPlaneBytes, 128);
+      const uint64_t b_tmpl = smem_desc_noswz(smem_u32(s_w), Cfg::kWChunkBytes, 128);
+      uint32_t gcount = 0, qbase = 0;
+      for (int item = blockIdx.x; item < g.nitems; item += gridDim.x) {
+        const int seg = item % g.nseg;
+        const int y0 = seg * g.rseg;
+        const int rows = min(g.rseg, g.H - y0);
+        for (int i = 0; i < rows + 4; ++i, ++gcount) {
+          const int jj_lo = max(0, 4 - i), jj_hi = min(4, rows + 3 - i);   // output row j = i-4+jj in [0, rows)
+          if (i < rows) {                                                  // a new accumulator comes into play
+            const uint32_t qn = qbase + i;
+            mbar_wait(&tempty[qn % RT], ((qn / RT) & 1) ^ 1);
+          }
+          const uint32_t slot = gcount % Cfg::kSlots;
+          mbar_wait(&full[slot], (gcount / Cfg::kSlots) & 1);
+          tc_fence_after();
+          const uint32_t row_addr = slots_addr + slot * Cfg::kSlotBytes;
+          const uint32_t q_lo = qbase + (uint32_t)(i - 4 + jj_lo);         // counter of the first target row
+#pragma unroll
+          for (int dx = 0; dx < 5; ++dx) {
+#pragma unroll
+            for (int kk = 0; kk < Cfg::kKSteps; ++kk) {
+              const uint32_t a_addr = row_addr + (2 * kk) * kPlaneBytes + dx * 16;
+              const uint64_t a_desc = a_tmpl | (uint64_t)((a_addr >> 4) & 0x3FFF);
+              const uint64_t b_step = b_tmpl + (uint64_t)(((dx * Cfg::kKSteps + kk) * Cfg::kWStepBytes) >> 4);
+              const bool first = (dx == 0 && kk == 0 && i < rows);         // block jj=4 starts output row i
+              // range of accumulating blocks [jj_lo, acc_hi]; on `first` block 4 is issued separately
+              const int acc_hi = first ? min(jj_hi, 3) : jj_hi;
+              int jj = jj_lo;
+              while (jj <= acc_hi) {
+                const uint32_t s0 = (q_lo + (uint32_t)(jj - jj_lo)) % RT;
+                const int nblk = min(acc_hi - jj + 1, (int)(RT - s0));
+                umma_bf16(tmem_base + s0 * COUT, a_desc, b_step + (uint64_t)((jj * COUT * 16) >> 4),
+                          idesc0 | ((uint32_t)((nblk * COUT) >> 3) << 17), 1u);
+                jj += nblk;
+              }
+              if (first) {
+                const uint32_t s0 = (qbase + (uint32_t)i) % RT;
+                umma_bf16(tmem_base + s0 * COUT, a_desc, b_step + (uint64_t)((4 * COUT * 16) >> 4),
+                          idesc0 | ((uint32_t)(COUT >> 3) << 17), 0u);
+              }
+            }
+          }
+          umma_commit(&empty[slot]);                                       // this input row is consumed
+          if (i >= 4) umma_commit(&tfull[(qbase + (uint32_t)(i - 4)) % RT]);  // output row i-4 is complete
+        }
+        qbase += rows;
+      }
+    }
+  } else {
+    const int quarter = warp & 3;
+    const int m = quarter * 32 + lane;
+    float ssum[STATS ? COUT : 1], ssq[STATS ? COUT : 1];
+    if (STATS) {
+#pragma unroll
+      for (int c = 0; c < COUT; ++c) { ssum[c] = 0.f; ssq[c] = 0.f; }
+    }
+    uint32_t q = 0;
+    for (int item = blockIdx.x; item < g.nitems; item += gridDim.x) {
+      const int seg = item % g.nseg;
+      const int strip = (item / g.nseg) % g.nstrips;
+      const int b = item / (g.nseg * g.nstrips);
+      const int y0 = seg * g.rseg;
+      const int rows = min(g.rseg, g.H - y0);
+      const int x = strip * kBM + m;
+      const bool valid = x < g.W;
+      for (int j = 0; j < rows; ++j, ++q) {
+        const uint32_t stage = q % RT, use = q / RT;
+        mbar_wait(&tfull[stage], use & 1);
+        tc_fence_after();
+        const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + stage * COUT;
+        uint32_t v[COUT];
+#pragma unroll
+        for (int c0 = 0; c0 < COUT; c0 += 16) tmem_ld16(taddr + c0, *reinterpret_cast<uint32_t(*)[16]>(&v[c0]));
+        tmem_ld_wait();
+        tc_fence_before();
+        mbar_arrive(&tempty[stage]);
+        uint32_t pk[COUT / 2];
+#pragma unroll
+        for (int c = 0; c < COUT; c += 2) {
+          pk[c / 2] = pack_bf16x2(__uint_as_float(v[c]) + s_bias[c], __uint_as_float(v[c + 1]) + s_bias[c + 1]);
+          if (STATS && valid) {
+            const float r0 = bf16_lo(pk[c / 2]), r1 = bf16_hi(pk[c / 2]);
+            ssum[c] += r0; ssq[c] = fmaf(r0, r0, ssq[c]);
+            ssum[c + 1] += r1; ssq[c + 1] = fmaf(r1, r1, ssq[c + 1]);
+          }
+        }
+        if (valid) {
+          uint4* o = reinterpret_cast<uint4*>(out + (((size_t)b * g.H + (y0 + j)) * g.W + x) * COUT);
+#pragma unroll
+          for (int i = 0; i < COUT / 8; ++i) o[i] = make_uint4(pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
+        }
+      }
+    }
+    if (STATS) {
+#pragma unroll
+      for (int c = 0; c < COUT; ++c) {
+        const float a = warp_sum(ssum[c]), s2 = warp_sum(ssq[c]);
+        if (lane == 0) { s_stat[quarter * 2 * COUT + c] = a; s_stat[quarter * 2 * COUT + COUT + c] = s2; }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  if (STATS && threadIdx.x < 2 * COUT) {
+    float a = 0.f;
+#pragma unroll
+    for (int w4 = 0; w4 < 4; ++w4) a += s_stat[w4 * 2 * COUT + threadIdx.x];
+    partials[(size_t)blockIdx.x * 2 * COUT + threadIdx.x] = a;
+  }
+  if (warp == 1) { __syncwarp(); tmem_dealloc<Cfg::kTmemCols>(tmem_base); }
+}
+
+// wgrad, row-stationary: the act (p1) row is the stationary operand; the five dx2 rows it
+// pairs with (y = r-2 .. r+2) are five CONSECUTIVE slots of the dx2 ring, i.e. 20 consecutive
+// 8-channel planes, i.e. one MN-major B operand with N = 160.  D[pl][(dx,ci8)][(jj,co)], dy = 4-jj.
+constexpr int kWg2SlotsA = 4, kWg2SlotsB = 12;
+constexpr int kWg2SmemBytes = kWg2SlotsA * kWgSlotABytes + kWg2SlotsB * kWgSlotBBytes + 1024 + 128;
+
+template <bool LDGSTS>
+__global__ void __launch_bounds__(kThreads, 1)
+conv5x5_wgrad_rs_kernel(const __grid_constant__ CUtensorMap tm_act, const __grid_constant__ CUtensorMap tm_dxo,
+                        const __nv_bfloat16* __restrict__ act, const __nv_bfloat16* __restrict__ dxo,
+                        float* __restrict__ partials, ConvGeom g) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((128u - (smem_u32(smem_raw) & 127u)) & 127u);
+  uint8_t* s_a = smem;
+  uint8_t* s_b = smem + kWg2SlotsA * kWgSlotABytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_b + kWg2SlotsB * kWgSlotBBytes);
+  uint64_t* fullA = bars;
+  uint64_t* emptyA = fullA + kWg2SlotsA;
+  uint64_t* fullB = emptyA + kWg2SlotsA;
+  uint64_t* emptyB = fullB + kWg2SlotsB;
+  uint64_t* done = emptyB + kWg2SlotsB;
+  uint32_t* s_tmem = reinterpret_cast<uint32_t*>(done + 1);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < kWg2SlotsA; ++i) { mbar_init(&fullA[i], 1); mbar_init(&emptyA[i], 1); }
+    for (int i = 0; i < kWg2SlotsB; ++i) { mbar_init(&fullB[i], 1); mbar_init(&emptyB[i], 1); }
+    mbar_init(done, 1);
+    mbar_fence_init();
+    tma_prefetch_desc(&tm_act);
+    tma_prefetch_desc(&tm_dxo);
+  }
+  if (warp == 1) tmem_alloc<kWgTmemCols>(s_tmem);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *s_tmem;
+
+  if (warp == 0) {
+    if (LDGSTS) {
+      uint32_t ga = 0, gb = 0, ga_done = 0, gb_done = 0, it = 0, has_a = 0;   // has_a: bit k = iteration (it-1-k) carried an act row
+      for (int item = blockIdx.x; item < g.nitems; item += gridDim.x) {
+        const int seg = item % g.nseg;
+        const int strip = (item / g.nseg) % g.nstrips;
+        const int b = item / (g.nseg * g.nstrips);
+        const int r0 = seg * g.rseg;
+        const int rows = min(g.rseg, g.H - r0);
+        const int x0 = strip * kBM;
+        for (int i = 0; i < rows + 4; ++i, ++it) {
+          {
+            const uint32_t slot = gb % kWg2SlotsB, use = gb / kWg2SlotsB;
+            mbar_wait(&emptyB[slot], (use & 1) ^ 1);
+            cp_row<32>(s_b + slot * kWgSlotBBytes, dxo, b, r0 - 2 + i, x0, kBM, kWgPlaneBBytes, g.H, g.W, lane);
+            ++gb;
+          }
+          has_a <<= 1;
+          if (i >= 4) {
+            const uint32_t slot = ga % kWg2SlotsA, use = ga / kWg2SlotsA;
+            mbar_wait(&emptyA[slot], (use & 1) ^ 1);
+            cp_row<16>(s_a + slot * kWgSlotABytes, act, b, r0 + i - 4, x0 - 2, kPW, kPlaneBytes, g.H, g.W, lane);
+            ++ga;
+            has_a |= 1u;
+          }
+          cp_async_commit();
+          if (it >= (uint32_t)kCpDepth) {
+            cp_async_wait<kCpDepth>();
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&fullB[gb_done % kWg2SlotsB]);
+            ++gb_done;
+            if ((has_a >> kCpDepth) & 1u) {
+              if (lane == 0) mbar_arrive(&fullA[ga_done % kWg2SlotsA]);
+              ++ga_done;
+            }
+          }
+        }
+      }
+      cp_async_wait<0>();
+      fence_proxy_async_smem();
+      __syncwarp();
+      for (; gb_done < gb; ++gb_done)
+        if (lane == 0) mbar_arrive(&fullB[gb_done % kWg2SlotsB]);
+      for (; ga_done < ga; ++ga_done)
+        if (lane == 0) mbar_arrive(&fullA[ga_done % kWg2SlotsA]);
+    } else if (lane == 0) {
+      uint32_t ga = 0, gb = 0;
+      for (int item = blockIdx.x; item < g.nitems; item += gridDim.x) {
+        const int seg = item % g.nseg;
+        const int strip = (item / g.nseg) % g.nstrips;
+        const int b = item / (g.nseg * g.nstrips);
+        const int r0 = seg * g.rseg;
+        const int rows = min(g.rseg, g.H - r0);
+        const int x0 = strip * kBM;
+        for (int i = 0; i < rows + 4; ++i) {
+          {   // dx2 row r0-2+i (zero-filled outside the image)
+            const uint32_t slot = gb % kWg2SlotsB, use = gb / kWg2SlotsB;
+            mbar_wait(&emptyB[slot], (use & 1) ^ 1);
+            mbar_expect_tx(&fullB[slot], kWgSlotBBytes);
+            uint8_t* dst = s_b + slot * kWgSlotBBytes;
+#pragma unroll
+            for (int p = 0; p < 4; ++p)
+              tma_load_5d(dst + p * kWgPlaneBBytes, &tm_dxo, &fullB[slot], 0, p, x0, r0 - 2 + i, b);
+            ++gb;
+          }
+          if (i >= 4) {   // act row r0+i-4: all five dx2 rows it needs are now in flight
+            const uint32_t slot = ga % kWg2SlotsA, use = ga / kWg2SlotsA;
+            mbar_wait(&emptyA[slot], (use & 1) ^ 1);
+            mbar_expect_tx(&fullA[slot], kWgSlotABytes);
+            uint8_t* dst = s_a + slot * kWgSlotABytes;
+            tma_load_5d(dst, &tm_act, &fullA[slot], 0, 0, x0 - 2, r0 + i - 4, b);
+            tma_load_5d(dst + kPlaneBytes, &tm_act, &fullA[slot], 0, 1, x0 - 2, r0 + i - 4, b);
+            ++ga;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc0 = umma_idesc_bf16(64, 0, 1, 1);
+      const uint64_t a_tmpl = smem_desc_noswz(0, 128, 16);
+      const uint64_t b_tmpl = smem_desc_noswz(0, 128, kWgPlaneBBytes);
+      const uint32_t a_base = smem_u32(s_a), b_base = smem_u32(s_b);
+      uint32_t ga = 0, gbase = 0;
+      uint32_t first = 1;
+      for (int item = blockIdx.x; item < g.nitems; item += gridDim.x) {
+        const int seg = item % g.nseg;
+        const int r0 = seg * g.rseg;
+        const int rows = min(g.rseg, g.H - r0);
+        for (int i = 0; i < rows; ++i, ++ga) {
+          for (int k = (i == 0 ? 0 : 4); k < 5; ++k) {          // dx2 local rows i..i+4 have landed
+            const uint32_t gc = gbase + i + k;
+            mbar_wait(&fullB[gc % kWg2SlotsB], (gc / kWg2SlotsB) & 1);
+          }
+          const uint32_t slotA = ga % kWg2SlotsA;
+          mbar_wait(&fullA[slotA], (ga / kWg2SlotsA) & 1);
+          tc_fence_after();
+          const uint32_t s0 = (gbase + i) % kWg2SlotsB;          // ring slot of the window's first row
+          const int n1 = min(5, (int)(kWg2SlotsB - s0));
+          const uint32_t arow = a_base + slotA * kWgSlotABytes;
+#pragma unroll 1
+          for (int kb = 0; kb < kBM / 16; ++kb) {
+            const uint64_t b1 = b_tmpl | (uint64_t)(((b_base + s0 * kWgSlotBBytes + kb * 256) >> 4) & 0x3FFF);
+            const uint64_t b2 = b_tmpl | (uint64_t)(((b_base + kb * 256) >> 4) & 0x3FFF);
+#pragma unroll
+            for (int pl = 0; pl < 2; ++pl) {
+              const uint64_t a_desc = a_tmpl | (uint64_t)(((arow + pl * kPlaneBytes + kb * 256) >> 4) & 0x3FFF);
+              umma_bf16(tmem_base + pl * 160, a_desc, b1, idesc0 | ((uint32_t)((n1 * 32) >> 3) << 17), first ? 0u : 1u);
+              if (n1 < 5)
+                umma_bf16(tmem_base + pl * 160 + n1 * 32, a_desc, b2,
+                          idesc0 | ((uint32_t)(((5 - n1) * 32) >> 3) << 17), first ? 0u : 1u);
+            }
+            first = 0;
+          }
+          umma_commit(&emptyA[slotA]);
+          umma_commit(&emptyB[(gbase + i) % kWg2SlotsB]);
+        }
+        for (int k = 0; k < 4; ++k) umma_commit(&emptyB[(gbase + rows + k) % kWg2SlotsB]);
+        gbase += rows + 4;
+      }
+      umma_commit(done);
+    }
+  } else {
+    const int quarter = warp & 3;
+    float* dst = partials + (size_t)blockIdx.x * (32 * 16 * kTaps);
+    mbar_wait(done, 0);
+    tc_fence_after();
+    const int r = quarter * 16 + (lane & 15);
+    const int dxs = r >> 3, e = r & 7;
+    const bool row_valid = (lane < 16) && (dxs < 5);
+#pragma unroll 1
+    for (int acc = 0; acc < 10; ++acc) {
+      const int pl = acc / 5, jj = acc % 5, dy = 4 - jj;
+      uint32_t v[32];
+      const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + pl * 160 + jj * 32;
+      tmem_ld16(taddr, *reinterpret_cast<uint32_t(*)[16]>(&v[0]));
+      tmem_ld16(taddr + 16, *reinterpret_cast<uint32_t(*)[16]>(&v[16]));
+      tmem_ld_wait();
+      if (row_valid) {
+        const int ci = pl * 8 + e;
+#pragma unroll
+        for (int co = 0; co < 32; ++co)
+          dst[((size_t)co * 16 + ci) * kTaps + dy * 5 + dxs] = __uint_as_float(v[co]);
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  if (warp == 1) { __syncwarp(); tmem_dealloc<kWgTmemCols>(tmem_base); }
+}
+
 // ------------------------------------------------------------- host side ----
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
@@ -468,9 +929,40 @@ ConvGeom make_geom(int B, int H, int W, int nsm, int halo_rows) {
   return g;
 }
 
+// 1 = tap-stationary + TMA, 2 = row-stationary + TMA, 3 = row-stationary + cp.async feed (default)
+int g_conv_tc_version = 3;
+
+template <int CIN, int COUT, bool TRANSPOSED, bool STATS, bool LDGSTS>
+int launch_conv_rs(const void* act, const void* w, const void* bias, void* out, void* partials, int B, int H, int W,
+                   cudaStream_t s, int* grid_out) {
+  using Cfg = RsCfg<CIN, COUT>;
+  auto kern = conv5x5_rs_kernel<CIN, COUT, TRANSPOSED, STATS, LDGSTS>;
+  static std::once_flag once;
+  static cudaError_t attr_err = cudaSuccess;
+  std::call_once(once, [&] {
+    attr_err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes);
+  });
+  B200_CUDA(attr_err);
+  CUtensorMap tm;
+  int rc = make_act_tmap(&tm, act, B, H, W, CIN, kPW);
+  if (rc) return rc;
+  const int nsm = b200_num_sms();
+  ConvGeom g = make_geom(B, H, W, nsm, 4);
+  const int grid = g.nitems < nsm ? g.nitems : nsm;
+  kern<<<grid, kThreads, Cfg::kSmemBytes, s>>>(tm, (const __nv_bfloat16*)act, (const float*)w, (const float*)bias,
+                                                (__nv_bfloat16*)out, (float*)partials, g);
+  B200_LAUNCH_CHECK();
+  if (grid_out) *grid_out = grid;
+  return 0;
+}
+
 template <int CIN, int COUT, bool TRANSPOSED, bool STATS>
 int launch_conv(const void* act, const void* w, const void* bias, void* out, void* partials, int B, int H, int W,
                 cudaStream_t s, int* grid_out) {
+  if (g_conv_tc_version == 3)
+    return launch_conv_rs<CIN, COUT, TRANSPOSED, STATS, true>(act, w, bias, out, partials, B, H, W, s, grid_out);
+  if (g_conv_tc_version == 2)
+    return launch_conv_rs<CIN, COUT, TRANSPOSED, STATS, false>(act, w, bias, out, partials, B, H, W, s, grid_out);
   using Cfg = ConvCfg<CIN, COUT>;
   auto kern = conv5x5_tc_kernel<CIN, COUT, TRANSPOSED, STATS>;
   static std::once_flag once;
@@ -497,6 +989,12 @@ int launch_conv(const void* act, const void* w, const void* bias, void* out, voi
 // Number of partial-stat rows conv2_fwd writes (= its grid size); callers size
 // the partials buffer with b200_conv_tc_max_grid() x 2*COUT floats.
 B200_API int b200_conv_tc_max_grid() { return b200_num_sms(); }
+B200_API int b200_conv_tc_set_version(int v) {
+  if (v < 1 || v > 3) return b200_fail(-2, "conv_tc version must be 1, 2 or 3");
+  g_conv_tc_version = v;
+  return 0;
+}
+B200_API int b200_conv_tc_get_version() { return g_conv_tc_version; }
 
 // *nparts_out receives the number of valid partial-stat rows (= grid size).
 B200_API int b200_conv2_fwd_tc(const void* p1_bf16, const void* w2, const void* b2, void* x2_bf16,
@@ -519,6 +1017,10 @@ B200_API int b200_conv2_wgrad_tc(const void* p1_bf16, const void* dx2_bf16, void
   static cudaError_t attr_err = cudaSuccess;
   std::call_once(once, [&] {
     attr_err = cudaFuncSetAttribute(conv5x5_wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kWgSmemBytes);
+    if (attr_err == cudaSuccess)
+      attr_err = cudaFuncSetAttribute(conv5x5_wgrad_rs_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kWg2SmemBytes);
+    if (attr_err == cudaSuccess)
+      attr_err = cudaFuncSetAttribute(conv5x5_wgrad_rs_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kWg2SmemBytes);
   });
   B200_CUDA(attr_err);
   CUtensorMap tma, tmb;
@@ -529,7 +1031,14 @@ B200_API int b200_conv2_wgrad_tc(const void* p1_bf16, const void* dx2_bf16, void
   const int nsm = b200_num_sms();
   ConvGeom g = make_geom(B, H, W, nsm, 4);
   const int grid = g.nitems < nsm ? g.nitems : nsm;
-  conv5x5_wgrad_tc_kernel<<<grid, kThreads, kWgSmemBytes, s>>>(tma, tmb, (float*)partials, g);
+  if (g_conv_tc_version == 3)
+    conv5x5_wgrad_rs_kernel<true><<<grid, kThreads, kWg2SmemBytes, s>>>(tma, tmb, (const __nv_bfloat16*)p1_bf16,
+                                                                        (const __nv_bfloat16*)dx2_bf16, (float*)partials, g);
+  else if (g_conv_tc_version == 2)
+    conv5x5_wgrad_rs_kernel<false><<<grid, kThreads, kWg2SmemBytes, s>>>(tma, tmb, (const __nv_bfloat16*)p1_bf16,
+                                                                         (const __nv_bfloat16*)dx2_bf16, (float*)partials, g);
+  else
+    conv5x5_wgrad_tc_kernel<<<grid, kThreads, kWgSmemBytes, s>>>(tma, tmb, (float*)partials, g);
   B200_LAUNCH_CHECK();
   return b200_reduce_partials(partials, grid, 32 * 16 * kTaps, dw2, gscale, stream);
 }

@@ -106,8 +106,15 @@ def test_bn_relu_pool(ops, C):
     report(f"bn_relu_pool C={C}", rel(to_nchw(p), ref), 4e-3)
 
 
-@pytest.mark.parametrize("shape", [(2, 24, 200), (1, 50, 128), (3, 17, 300)])
-def test_conv2_fwd_tc(ops, shape):
+@pytest.fixture(params=[3, 2, 1], ids=["rowstat_cpasync", "rowstat_tma", "tapstat_tma"])
+def tc_version(ops, request):
+    ops.conv_tc_set_version(request.param)
+    yield request.param
+    ops.conv_tc_set_version(3)
+
+
+@pytest.mark.parametrize("shape", [(2, 24, 200), (1, 50, 128), (3, 17, 300), (1, 3, 40), (2, 133, 260)])
+def test_conv2_fwd_tc(ops, shape, tc_version):
     B, H, W = shape
     g = torch.Generator(device=DEV).manual_seed(4)
     x = torch.randn(B, 16, H, W, device=DEV, generator=g)
@@ -126,8 +133,8 @@ def test_conv2_fwd_tc(ops, shape):
     report("conv2_fwd_tc sumsq", rel(s[32:], (r ** 2).sum((0, 1, 2))), 1e-4)
 
 
-@pytest.mark.parametrize("shape", [(2, 24, 200), (1, 50, 128)])
-def test_conv2_dgrad_tc(ops, shape):
+@pytest.mark.parametrize("shape", [(2, 24, 200), (1, 50, 128), (1, 2, 24), (2, 133, 260)])
+def test_conv2_dgrad_tc(ops, shape, tc_version):
     B, H, W = shape
     g = torch.Generator(device=DEV).manual_seed(5)
     dy = torch.randn(B, 32, H, W, device=DEV, generator=g)
@@ -140,8 +147,8 @@ def test_conv2_dgrad_tc(ops, shape):
     report(f"conv2_dgrad_tc {shape}", rel(to_nchw(out), ref), 5e-3)
 
 
-@pytest.mark.parametrize("shape", [(2, 24, 200), (1, 50, 128), (3, 17, 300)])
-def test_conv2_wgrad_tc(ops, shape):
+@pytest.mark.parametrize("shape", [(2, 24, 200), (1, 50, 128), (3, 17, 300), (1, 2, 24), (2, 133, 260)])
+def test_conv2_wgrad_tc(ops, shape, tc_version):
     B, H, W = shape
     g = torch.Generator(device=DEV).manual_seed(6)
     x = torch.randn(B, 16, H, W, device=DEV, generator=g)

@@ -22,6 +22,9 @@ def main():
         out.flush()
 
     backend = sys.argv[1] if len(sys.argv) > 1 else "tc"
+    if backend in ("tc1", "tc2", "tc3"):
+        ops.conv_tc_set_version(int(backend[2]))
+        backend = "tc"
     B = int(sys.argv[2]) if len(sys.argv) > 2 else 5
     t0 = time.time()
     eng = FusedConvNet((3000, 3000), batch_size=B, lr=1e-4, conv_backend=backend)

@@ -85,6 +85,15 @@ def fc_grid() -> int:
     return int(_lib().b200_fc_grid())
 
 
+def conv_tc_set_version(v: int) -> None:
+    """tcgen05 conv variant: 1 = tap-stationary + TMA, 2 = row-stationary + TMA, 3 = row-stationary + cp.async (default)."""
+    _native.check(_lib().b200_conv_tc_set_version(int(v)), "conv_tc_set_version")
+
+
+def conv_tc_get_version() -> int:
+    return int(_lib().b200_conv_tc_get_version())
+
+
 # ---- kernels ----------------------------------------------------------------
 def resize_pil_bilinear(src_u8, xtab, ytab, dst_f32):
     """uint8 [B,h,w] -> fp32 [B,H,W]; bit-exact PIL bilinear + ToTensor (K1/K2)."""
