@@ -567,57 +567,63 @@ conv5x5_rs_kernel(const __grid_constant__ CUtensorMap tm_act, const __nv_bfloat1
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      constexpr uint32_t idesc0 = umma_idesc_bf16(kBM, 0, 0, 0);          // N filled in per MMA
-      const uint32_t slots_addr = smem_u32(s_slots);
-      const uint64_t a_tmpl = smem_desc_noswz(0, kPlaneBytes, 128);
-      const uint64_t b_tmpl = smem_desc_noswz(smem_u32(s_w), Cfg::kWChunkBytes, 128);
-      uint32_t gcount = 0, qbase = 0;
-      for (int item = blockIdx.x; item < g.nitems; item += gridDim.x) {
-        const int seg = item % g.nseg;
-        const int y0 = seg * g.rseg;
-        const int rows = min(g.rseg, g.H - y0);
-        for (int i = 0; i < rows + 4; ++i, ++gcount) {
-          const int jj_lo = max(0, 4 - i), jj_hi = min(4, rows + 3 - i);   // output row j = i-4+jj in [0, rows)
-          if (i < rows) {                                                  // a new accumulator comes into play
-            const uint32_t qn = qbase + i;
-            mbar_wait(&tempty[qn % RT], ((qn / RT) & 1) ^ 1);
-          }
-          const uint32_t slot = gcount % Cfg::kSlots;
-          mbar_wait(&full[slot], (gcount / Cfg::kSlots) & 1);
-          tc_fence_after();
-          const uint32_t row_addr = slots_addr + slot * Cfg::kSlotBytes;
-          const uint32_t q_lo = qbase + (uint32_t)(i - 4 + jj_lo);         // counter of the first target row
+    // ===== MMA issue.  The WHOLE warp runs this loop (warp-uniform control flow, descriptors in
+    // uniform registers); only the tcgen05 instructions are predicated on one elected lane.
+    // (Running the loop under `if (lane == 0)` made ptxas serialise every UTCHMMA operand through
+    // ELECT / R2UR / BRA.U.ANY: ~285 SASS instructions per row on one lane - the bottleneck ncu showed.)
+    constexpr uint32_t idesc0 = umma_idesc_bf16(kBM, 0, 0, 0);            // N filled in per MMA
+    const uint32_t slots_addr = smem_u32(s_slots);
+    const uint64_t a_tmpl = smem_desc_noswz(0, kPlaneBytes, 128);          // LBO lives in the LOW word (bits 16..29)
+    const uint32_t a_hi = (uint32_t)(a_tmpl >> 32), a_lo0 = (uint32_t)a_tmpl;
+    const uint64_t b_tmpl = smem_desc_noswz(smem_u32(s_w), Cfg::kWChunkBytes, 128);
+    const uint32_t b_hi = (uint32_t)(b_tmpl >> 32), b_lo0 = (uint32_t)b_tmpl;
+    uint32_t gcount = 0, qbase = 0;
+    for (int item = blockIdx.x; item < g.nitems; item += gridDim.x) {
+      const int seg = item % g.nseg;
+      const int y0 = seg * g.rseg;
+      const int rows = min(g.rseg, g.H - y0);
+      for (int i = 0; i < rows + 4; ++i, ++gcount) {
+        const int jj_lo = max(0, 4 - i), jj_hi = min(4, rows + 3 - i);     // output row j = i-4+jj in [0, rows)
+        const bool starts_row = i < rows;                                  // block jj=4 opens output row i
+        if (starts_row) {
+          const uint32_t qn = qbase + i;
+          mbar_wait(&tempty[qn % RT], ((qn / RT) & 1) ^ 1);
+        }
+        const uint32_t slot = gcount % Cfg::kSlots;
+        mbar_wait(&full[slot], (gcount / Cfg::kSlots) & 1);
+        tc_fence_after();
+        // accumulating blocks [jj_lo, acc_hi] as (at most) two column ranges of the 16-slot TMEM ring
+        const int acc_hi_first = starts_row ? min(jj_hi, 3) : jj_hi;       // on dx=0/kk=0, block 4 overwrites
+        const uint32_t s0 = (qbase + (uint32_t)(i - 4 + jj_lo)) % RT;
+        const uint32_t a_lo_row = a_lo0 + ((slots_addr + slot * Cfg::kSlotBytes) >> 4);
+        if (elect_one()) {
 #pragma unroll
           for (int dx = 0; dx < 5; ++dx) {
 #pragma unroll
             for (int kk = 0; kk < Cfg::kKSteps; ++kk) {
-              const uint32_t a_addr = row_addr + (2 * kk) * kPlaneBytes + dx * 16;
-              const uint64_t a_desc = a_tmpl | (uint64_t)((a_addr >> 4) & 0x3FFF);
-              const uint64_t b_step = b_tmpl + (uint64_t)(((dx * Cfg::kKSteps + kk) * Cfg::kWStepBytes) >> 4);
-              const bool first = (dx == 0 && kk == 0 && i < rows);         // block jj=4 starts output row i
-              // range of accumulating blocks [jj_lo, acc_hi]; on `first` block 4 is issued separately
-              const int acc_hi = first ? min(jj_hi, 3) : jj_hi;
-              int jj = jj_lo;
-              while (jj <= acc_hi) {
-                const uint32_t s0 = (q_lo + (uint32_t)(jj - jj_lo)) % RT;
-                const int nblk = min(acc_hi - jj + 1, (int)(RT - s0));
-                umma_bf16(tmem_base + s0 * COUT, a_desc, b_step + (uint64_t)((jj * COUT * 16) >> 4),
-                          idesc0 | ((uint32_t)((nblk * COUT) >> 3) << 17), 1u);
-                jj += nblk;
-              }
-              if (first) {
-                const uint32_t s0 = (qbase + (uint32_t)i) % RT;
-                umma_bf16(tmem_base + s0 * COUT, a_desc, b_step + (uint64_t)((4 * COUT * 16) >> 4),
-                          idesc0 | ((uint32_t)(COUT >> 3) << 17), 0u);
-              }
+              const uint64_t a_desc = ((uint64_t)a_hi << 32) | (uint64_t)(a_lo_row + ((2 * kk) * kPlaneBytes >> 4) + dx);
+              const uint32_t b_lo = b_lo0 + (((dx * Cfg::kKSteps + kk) * Cfg::kWStepBytes) >> 4);
+              const bool first = (dx == 0 && kk == 0);
+              const int acc_hi = first ? acc_hi_first : jj_hi;
+              const int nacc = acc_hi - jj_lo + 1;                          // may be <= 0
+              const int n1 = min(nacc, (int)(RT - s0));
+              if (n1 > 0)
+                umma_bf16(tmem_base + s0 * COUT, a_desc, ((uint64_t)b_hi << 32) | (uint64_t)(b_lo + jj_lo * COUT),
+                          idesc0 | ((uint32_t)((n1 * COUT) >> 3) << 17), 1u);
+              if (nacc > n1)
+                umma_bf16(tmem_base, a_desc, ((uint64_t)b_hi << 32) | (uint64_t)(b_lo + (jj_lo + n1) * COUT),
+                          idesc0 | ((uint32_t)(((nacc - n1) * COUT) >> 3) << 17), 1u);
+              if (first && starts_row)
+                umma_bf16(tmem_base + ((qbase + (uint32_t)i) % RT) * COUT, a_desc,
+                          ((uint64_t)b_hi << 32) | (uint64_t)(b_lo + 4 * COUT), idesc0 | ((uint32_t)(COUT >> 3) << 17), 0u);
             }
           }
-          umma_commit(&empty[slot]);                                       // this input row is consumed
+          umma_commit(&empty[slot]);                                        // this input row is consumed
           if (i >= 4) umma_commit(&tfull[(qbase + (uint32_t)(i - 4)) % RT]);  // output row i-4 is complete
         }
-        qbase += rows;
+        __syncwarp();
       }
+      qbase += rows;
     }
   } else {
     const int quarter = warp & 3;
@@ -801,50 +807,57 @@ conv5x5_wgrad_rs_kernel(const __grid_constant__ CUtensorMap tm_act, const __grid
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      constexpr uint32_t idesc0 = umma_idesc_bf16(64, 0, 1, 1);
-      const uint64_t a_tmpl = smem_desc_noswz(0, 128, 16);
-      const uint64_t b_tmpl = smem_desc_noswz(0, 128, kWgPlaneBBytes);
-      const uint32_t a_base = smem_u32(s_a), b_base = smem_u32(s_b);
-      uint32_t ga = 0, gbase = 0;
-      uint32_t first = 1;
-      for (int item = blockIdx.x; item < g.nitems; item += gridDim.x) {
-        const int seg = item % g.nseg;
-        const int r0 = seg * g.rseg;
-        const int rows = min(g.rseg, g.H - r0);
-        for (int i = 0; i < rows; ++i, ++ga) {
-          for (int k = (i == 0 ? 0 : 4); k < 5; ++k) {          // dx2 local rows i..i+4 have landed
-            const uint32_t gc = gbase + i + k;
-            mbar_wait(&fullB[gc % kWg2SlotsB], (gc / kWg2SlotsB) & 1);
-          }
-          const uint32_t slotA = ga % kWg2SlotsA;
-          mbar_wait(&fullA[slotA], (ga / kWg2SlotsA) & 1);
-          tc_fence_after();
-          const uint32_t s0 = (gbase + i) % kWg2SlotsB;          // ring slot of the window's first row
-          const int n1 = min(5, (int)(kWg2SlotsB - s0));
-          const uint32_t arow = a_base + slotA * kWgSlotABytes;
-#pragma unroll 1
+    // warp-uniform loop, tcgen05 instructions on one elected lane (see conv5x5_rs_kernel)
+    constexpr uint32_t idesc0 = umma_idesc_bf16(64, 0, 1, 1);
+    const uint64_t a_tmpl = smem_desc_noswz(0, 128, 16), b_tmpl = smem_desc_noswz(0, 128, kWgPlaneBBytes);
+    const uint32_t a_hi = (uint32_t)(a_tmpl >> 32), b_hi = (uint32_t)(b_tmpl >> 32);
+    const uint32_t a_base = (uint32_t)a_tmpl + (smem_u32(s_a) >> 4), b_base = (uint32_t)b_tmpl + (smem_u32(s_b) >> 4);
+    uint32_t ga = 0, gbase = 0;
+    uint32_t first = 1;
+    for (int item = blockIdx.x; item < g.nitems; item += gridDim.x) {
+      const int seg = item % g.nseg;
+      const int r0 = seg * g.rseg;
+      const int rows = min(g.rseg, g.H - r0);
+      for (int i = 0; i < rows; ++i, ++ga) {
+        for (int k = (i == 0 ? 0 : 4); k < 5; ++k) {          // dx2 local rows i..i+4 have landed
+          const uint32_t gc = gbase + i + k;
+          mbar_wait(&fullB[gc % kWg2SlotsB], (gc / kWg2SlotsB) & 1);
+        }
+        const uint32_t slotA = ga % kWg2SlotsA;
+        mbar_wait(&fullA[slotA], (ga / kWg2SlotsA) & 1);
+        tc_fence_after();
+        const uint32_t s0 = (gbase + i) % kWg2SlotsB;          // ring slot of the window's first row
+        const int n1 = min(5, (int)(kWg2SlotsB - s0));
+        const uint32_t arow = a_base + slotA * (kWgSlotABytes >> 4);
+        const uint32_t brow1 = b_base + s0 * (kWgSlotBBytes >> 4);
+        const uint32_t acc0 = first ? 0u : 1u;
+        if (elect_one()) {
+#pragma unroll
           for (int kb = 0; kb < kBM / 16; ++kb) {
-            const uint64_t b1 = b_tmpl | (uint64_t)(((b_base + s0 * kWgSlotBBytes + kb * 256) >> 4) & 0x3FFF);
-            const uint64_t b2 = b_tmpl | (uint64_t)(((b_base + kb * 256) >> 4) & 0x3FFF);
+            const uint32_t acc = kb == 0 ? acc0 : 1u;
+            const uint64_t b1 = ((uint64_t)b_hi << 32) | (uint64_t)(brow1 + kb * 16);
+            const uint64_t b2 = ((uint64_t)b_hi << 32) | (uint64_t)(b_base + kb * 16);
 #pragma unroll
             for (int pl = 0; pl < 2; ++pl) {
-              const uint64_t a_desc = a_tmpl | (uint64_t)(((arow + pl * kPlaneBytes + kb * 256) >> 4) & 0x3FFF);
-              umma_bf16(tmem_base + pl * 160, a_desc, b1, idesc0 | ((uint32_t)((n1 * 32) >> 3) << 17), first ? 0u : 1u);
+              const uint64_t a_desc = ((uint64_t)a_hi << 32) | (uint64_t)(arow + pl * (kPlaneBytes >> 4) + kb * 16);
+              umma_bf16(tmem_base + pl * 160, a_desc, b1, idesc0 | ((uint32_t)((n1 * 32) >> 3) << 17), acc);
               if (n1 < 5)
-                umma_bf16(tmem_base + pl * 160 + n1 * 32, a_desc, b2,
-                          idesc0 | ((uint32_t)(((5 - n1) * 32) >> 3) << 17), first ? 0u : 1u);
+                umma_bf16(tmem_base + pl * 160 + n1 * 32, a_desc, b2, idesc0 | ((uint32_t)(((5 - n1) * 32) >> 3) << 17), acc);
             }
-            first = 0;
           }
           umma_commit(&emptyA[slotA]);
           umma_commit(&emptyB[(gbase + i) % kWg2SlotsB]);
         }
-        for (int k = 0; k < 4; ++k) umma_commit(&emptyB[(gbase + rows + k) % kWg2SlotsB]);
-        gbase += rows + 4;
+        __syncwarp();
+        first = 0;
       }
-      umma_commit(done);
+      if (elect_one())
+        for (int k = 0; k < 4; ++k) umma_commit(&emptyB[(gbase + rows + k) % kWg2SlotsB]);
+      __syncwarp();
+      gbase += rows + 4;
     }
+    if (elect_one()) umma_commit(done);
+    __syncwarp();
   } else {
     const int quarter = warp & 3;
     float* dst = partials + (size_t)blockIdx.x * (32 * 16 * kTaps);
