@@ -1,0 +1,534 @@
+// tcgen05 kernels for conv1 (Conv2d(1, 16, 5, 1, 2), mnist_distributed.py:29) - the layer with
+// Cin = 1 that "has no tensor-core shape".  It has one if the GEMM is built differently.
+//
+// K13, weight gradient  dW1[c][dy][dx] = sum_{b,y,x} g[b,y,x,c] * in[b, y+dy-2, x+dx-2]
+// where g, the gradient of the conv1 output, is the pool1/ReLU1/BN1 backward of dp1 and is
+// never written to HBM.  The reduction runs over PIXELS, so pixels are the K dimension:
+//
+//   A (M=128, MN-major)  m = (image row r in 0..7, channel c in 0..15), k = pixel x
+//        = g for 8 consecutive image rows; producer warps compute it on CUDA cores from
+//        (x1, dp1, BN stats) and store it as bf16 straight in the UMMA layout;
+//   B (N=96,  MN-major)  n = (input row r' in 0..11, horizontal tap dxs in 0..7), k = pixel x
+//        = the input rows y0-2 .. y0+9 "expanded" so that E[r'][x][dxs] = in[y0-2+r'][x+dxs-2]
+//        (a 1-channel row becomes 8 shifted copies: 16 bytes per pixel, cheap);
+//   D[(r,c)][(r',dxs)] accumulates over every pixel of every work item of the CTA in ONE
+//   128x96 fp32 TMEM tile; dW1[c][dy][dxs] = sum_r D[(r,c)][(r+dy, dxs)] is extracted once.
+//
+// One tcgen05.mma (M=128, N=96, K=16) contracts 16 pixels x 8 rows; 26 % of its MACs are
+// useful, and it still replaces 16*8*16*25 = 51,200 FFMAs with a 56-cycle instruction.  The
+// kernel is then bounded by producing g (reading x1 once, 1.44 GB at batch 5) - which is
+// what the FFMA version (2.5 ms, csrc/convnet_kernels.cu) could not get near.
+#include "common.h"
+#include "ptx.cuh"
+#include <cstdint>
+#include <mutex>
+
+namespace {
+
+using namespace b2;
+
+constexpr int kC1 = 16;
+constexpr int kXW = 128;                    // pixels per strip
+constexpr int kRows = 8;                    // image rows per work item (M = 8 rows x 16 channels)
+constexpr int kChunkBytes = kXW * 16;       // one MN-chunk (8 elements) over the strip: 2048 B
+constexpr int kABytes = 2 * kRows * kChunkBytes;     // 32 KB
+constexpr int kERows = kRows + 4;           // 12 input rows
+constexpr int kEBytes = kERows * kChunkBytes;        // 24 KB
+constexpr int kStageBytes = kABytes + kEBytes;       // 56 KB
+constexpr int kStages = 2;
+constexpr int kInW = kXW + 8;               // staged fp32 input row: x0-2 .. x0+133
+constexpr int kProducerWarps = 8;
+constexpr int kProducers = 32 * kProducerWarps;      // 256 = one 2x2 window each
+constexpr int kWgThreads = 32 + kProducers;          // warp 0 = MMA issue
+constexpr int kNCols = kERows * 8;          // 96 accumulator columns
+constexpr int kTmemCols = 128;
+constexpr int kSmemBytes = kStages * kStageBytes + kStages * kERows * kInW * 4 + 1024 + 128;
+
+__device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+__device__ __forceinline__ uint4 ldg16(const void* p) {
+  uint4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+  return r;
+}
+
+struct WgGeom {
+  int B, H, W;
+  int nstrips, ngroups, nitems;
+};
+
+__global__ void __launch_bounds__(kWgThreads, 1)
+conv1_wgrad_tc_kernel(const float* __restrict__ in, const __nv_bfloat16* __restrict__ x1,
+                      const __nv_bfloat16* __restrict__ dp1, const float* __restrict__ bn,
+                      const float* __restrict__ red, float* __restrict__ partials, WgGeom g) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((128u - (smem_u32(smem_raw) & 127u)) & 127u);
+  uint8_t* s_stage = smem;                                                    // [kStages][A | E]
+  float* s_in = reinterpret_cast<float*>(smem + kStages * kStageBytes);       // [kStages][12][136]
+  float4* s_const = reinterpret_cast<float4*>(s_in + kStages * kERows * kInW);  // [16] (sc, sh, ca, cb), 16-B aligned
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_const + kC1);
+  uint64_t* full = bars;                 // [kStages] producers -> MMA (count = producer warps)
+  uint64_t* empty = bars + kStages;      // [kStages] MMA -> producers
+  uint64_t* done = empty + kStages;
+  uint32_t* s_tmem = reinterpret_cast<uint32_t*>(done + 1);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < kStages; ++i) { mbar_init(&full[i], kProducerWarps); mbar_init(&empty[i], 1); }
+    mbar_init(done, 1);
+    mbar_fence_init();
+  }
+  if (warp == 0) tmem_alloc<kTmemCols>(s_tmem);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *s_tmem;
+  const int Ho = g.H / 2, Wo = g.W / 2;
+
+  if (warp == 0) {
+    // ================= MMA issue (warp-uniform, one elected lane issues) =================
+    constexpr uint32_t idesc = umma_idesc_bf16(128, kNCols, 1, 1);
+    const uint64_t tmpl = smem_desc_noswz(0, 128, kChunkBytes);      // MN-major: LBO = 8 pixels, SBO = next chunk
+    const uint32_t hi = (uint32_t)(tmpl >> 32), lo0 = (uint32_t)tmpl;
+    uint32_t n = 0;
+    for (int item = blockIdx.x; item < g.nitems; item += gridDim.x, ++n) {
+      const uint32_t s = n % kStages;
+      mbar_wait(&full[s], (n / kStages) & 1);
+      tc_fence_after();
+      const uint32_t a_lo = lo0 + (smem_u32(s_stage + s * kStageBytes) >> 4);
+      const uint32_t b_lo = a_lo + (kABytes >> 4);
+      const uint32_t acc0 = n == 0 ? 0u : 1u;
+      if (elect_one()) {
+#pragma unroll
+        for (int kb = 0; kb < kXW / 16; ++kb)
+          umma_bf16(tmem_base, ((uint64_t)hi << 32) | (uint64_t)(a_lo + kb * 16),
+                    ((uint64_t)hi << 32) | (uint64_t)(b_lo + kb * 16), idesc, kb == 0 ? acc0 : 1u);
+        umma_commit(&empty[s]);
+      }
+      __syncwarp();
+    }
+    if (elect_one()) umma_commit(done);
+    __syncwarp();
+  } else {
+    // ================= producers: 256 threads, one 2x2 window (x 16 channels) each =================
+    // Software-pipelined: the global loads of item n+1 (its window of x1 / dp1 and its share of the
+    // input rows) are issued into registers before item n is processed, so the ~1-2 us HBM latency
+    // overlaps the CUDA-core work instead of being exposed twice per item.
+    const int pt = threadIdx.x - 32;                 // 0..255
+    const int wr = pt >> 6, wc = pt & 63;            // window row 0..3, window col 0..63
+    for (int c = pt; c < kC1; c += kProducers) {     // per-channel constants: g = ca + cb*x + [argmax&relu] sc*dp
+      const float s_ = bn[c], mu = bn[2 * kC1 + c], rs = bn[3 * kC1 + c];
+      const float mdy = red[c], mdyx = red[kC1 + c];
+      s_const[c] = make_float4(s_, bn[kC1 + c], s_ * (rs * mdyx * mu - mdy), -s_ * rs * mdyx);
+    }
+    named_bar_sync(1, kProducers);
+    constexpr int kInPer = (kERows * kInW + kProducers - 1) / kProducers;   // 7 staged floats per thread
+
+    struct Regs { uint4 xr[4][2], gr[2]; float pin[kInPer]; bool wvalid; };
+    Regs nx;                                          // next item's data, in flight
+    nx.wvalid = false;
+    auto issue_loads = [&](int item) {
+      uint4 (&xr)[4][2] = nx.xr; uint4 (&gr)[2] = nx.gr; float (&pin)[kInPer] = nx.pin; bool& wvalid = nx.wvalid;
+      const int strip = item % g.nstrips;
+      const int grp = (item / g.nstrips) % g.ngroups;
+      const int b = item / (g.nstrips * g.ngroups);
+      const int y0 = grp * kRows, x0 = strip * kXW;
+#pragma unroll
+      for (int j = 0; j < kInPer; ++j) {
+        const int i = pt + j * kProducers;
+        const int rr = i / kInW, cc = i - rr * kInW;
+        const int gy = y0 - 2 + rr, gx = x0 - 2 + cc;
+        pin[j] = (i < kERows * kInW && gy >= 0 && gy < g.H && gx >= 0 && gx < g.W)
+                     ? __ldg(in + ((size_t)b * g.H + gy) * g.W + gx) : 0.f;
+      }
+      const int gy = y0 + 2 * wr, gx = x0 + 2 * wc;
+      wvalid = gy < g.H && gx < g.W;
+      if (wvalid) {
+        const __nv_bfloat16* xb = x1 + (((size_t)b * g.H + gy) * g.W + gx) * kC1;
+        xr[0][0] = ldg16(xb); xr[0][1] = ldg16(xb + 8);
+        xr[1][0] = ldg16(xb + kC1); xr[1][1] = ldg16(xb + kC1 + 8);
+        xr[2][0] = ldg16(xb + (size_t)g.W * kC1); xr[2][1] = ldg16(xb + (size_t)g.W * kC1 + 8);
+        xr[3][0] = ldg16(xb + (size_t)g.W * kC1 + kC1); xr[3][1] = ldg16(xb + (size_t)g.W * kC1 + kC1 + 8);
+        const __nv_bfloat16* gb = dp1 + (((size_t)b * Ho + (gy >> 1)) * Wo + (gx >> 1)) * kC1;
+        gr[0] = ldg16(gb); gr[1] = ldg16(gb + 8);
+      }
+    };
+    if ((int)blockIdx.x < g.nitems) issue_loads(blockIdx.x);
+    uint32_t n = 0;
+    for (int item = blockIdx.x; item < g.nitems; item += gridDim.x, ++n) {
+      const uint32_t s = n % kStages;
+      uint8_t* sA = s_stage + s * kStageBytes;
+      uint8_t* sE = sA + kABytes;
+      float* sI = s_in + s * kERows * kInW;
+      const Regs cur = nx;                            // (0) take this item's data, put the next item's loads in flight
+      if (item + (int)gridDim.x < g.nitems) issue_loads(item + gridDim.x);
+      const uint4 (&xr)[4][2] = cur.xr; const uint4 (&gr)[2] = cur.gr; const float (&pin)[kInPer] = cur.pin;
+      const bool wvalid = cur.wvalid;
+      mbar_wait(&empty[s], ((n / kStages) & 1) ^ 1);
+      // (1) staged input rows: registers -> smem
+#pragma unroll
+      for (int j = 0; j < kInPer; ++j) {
+        const int i = pt + j * kProducers;
+        if (i < kERows * kInW) sI[i] = pin[j];
+      }
+      // (2) g for this thread's window (from the prefetched registers) -> A[(2r+pl)][k][e]
+      {
+        uint32_t o[4][kC1 / 2];
+#pragma unroll
+        for (int c = 0; c < kC1; c += 2) {
+          float res[2][4];
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            const int ch = c + h;
+            const float4 k4 = s_const[ch];           // (sc, sh, ca, cb)
+            float xv[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              const uint32_t w = (&xr[i][ch >> 3].x)[(ch & 7) >> 1];
+              xv[i] = h ? bf16_hi(w) : bf16_lo(w);
+            }
+            int am = 0;
+            float best = fmaf(xv[0], k4.x, k4.y);
+#pragma unroll
+            for (int i = 1; i < 4; ++i) {
+              const float y = fmaf(xv[i], k4.x, k4.y);
+              if (y > best) { best = y; am = i; }
+            }
+            const uint32_t gw = (&gr[ch >> 3].x)[(ch & 7) >> 1];
+            float gv = h ? bf16_hi(gw) : bf16_lo(gw);
+            gv = best > 0.f ? gv * k4.x : 0.f;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) res[h][i] = fmaf(k4.w, xv[i], k4.z) + ((am == i) ? gv : 0.f);
+          }
+#pragma unroll
+          for (int i = 0; i < 4; ++i) o[i][c / 2] = wvalid ? pack_bf16x2(res[0][i], res[1][i]) : 0u;
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int r = 2 * wr + (i >> 1), k = 2 * wc + (i & 1);
+          uint8_t* dst = sA + (2 * r) * kChunkBytes + k * 16;
+          *reinterpret_cast<uint4*>(dst) = make_uint4(o[i][0], o[i][1], o[i][2], o[i][3]);
+          *reinterpret_cast<uint4*>(dst + kChunkBytes) = make_uint4(o[i][4], o[i][5], o[i][6], o[i][7]);
+        }
+      }
+      named_bar_sync(1, kProducers);                 // staged input complete
+      // (4) expanded input E[r'][k][dxs]: 12 x 128 pieces of 16 B, 6 per thread
+      {
+        const int k = pt & 127;
+#pragma unroll
+        for (int rr = pt >> 7; rr < kERows; rr += 2) {
+          const float* src = sI + rr * kInW + k;     // in[.., x0 + k - 2 + dxs]
+          uint4 o;
+          o.x = pack_bf16x2(src[0], src[1]); o.y = pack_bf16x2(src[2], src[3]);
+          o.z = pack_bf16x2(src[4], src[5]); o.w = pack_bf16x2(src[6], src[7]);
+          *reinterpret_cast<uint4*>(sE + rr * kChunkBytes + k * 16) = o;
+        }
+      }
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&full[s]);
+    }
+  }
+  // ================= extraction: dW1[c][dy][dxs] = sum_r D[(r,c)][(r+dy)*8 + dxs] =================
+  float* s_T = reinterpret_cast<float*>(s_stage);    // [128][97] floats, aliases the (now idle) stages
+  constexpr int kTP = kNCols + 1;
+  if (warp >= 1 && warp <= 4) {
+    mbar_wait(done, 0);
+    tc_fence_after();
+    const int q = warp & 3, m = q * 32 + lane;
+#pragma unroll 1
+    for (int c0 = 0; c0 < kNCols; c0 += 16) {
+      uint32_t v[16];
+      tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + c0, v);
+      tmem_ld_wait();
+#pragma unroll
+      for (int j = 0; j < 16; ++j) s_T[m * kTP + c0 + j] = __uint_as_float(v[j]);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  for (int t = threadIdx.x; t < kC1 * 25; t += kWgThreads) {
+    const int c = t / 25, tap = t % 25, dy = tap / 5, dxs = tap % 5;
+    const int pl = c >> 3, e = c & 7;
+    float a = 0.f;
+#pragma unroll
+    for (int r = 0; r < kRows; ++r) a += s_T[((2 * r + pl) * 8 + e) * kTP + (r + dy) * 8 + dxs];
+    partials[(size_t)blockIdx.x * 400 + t] = a;
+  }
+  if (warp == 0) { __syncwarp(); tmem_dealloc<kTmemCols>(tmem_base); }
+}
+
+}  // namespace
+
+// Same contract as b200_conv1_wgrad (partials: [b200_conv1_wgrad_grid()][400] scratch).
+B200_API int b200_conv1_wgrad_tc(const void* in_f32, const void* x1, const void* dp1, const void* bn, const void* red,
+                                 void* partials, void* dw1, int B, int H, int W, float gscale, void* stream) {
+  B200_CHECK(H % 2 == 0 && W % 2 == 0, "conv1_wgrad_tc: H and W must be even");
+  cudaStream_t s = (cudaStream_t)stream;
+  static std::once_flag once;
+  static cudaError_t attr_err = cudaSuccess;
+  std::call_once(once, [&] {
+    attr_err = cudaFuncSetAttribute(conv1_wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
+  });
+  B200_CUDA(attr_err);
+  WgGeom g;
+  g.B = B; g.H = H; g.W = W;
+  g.nstrips = (W + kXW - 1) / kXW;
+  g.ngroups = (H + kRows - 1) / kRows;
+  g.nitems = B * g.nstrips * g.ngroups;
+  const int nsm = b200_num_sms();
+  const int grid = g.nitems < nsm ? g.nitems : nsm;
+  conv1_wgrad_tc_kernel<<<grid, kWgThreads, kSmemBytes, s>>>((const float*)in_f32, (const __nv_bfloat16*)x1,
+                                                             (const __nv_bfloat16*)dp1, (const float*)bn,
+                                                             (const float*)red, (float*)partials, g);
+  B200_LAUNCH_CHECK();
+  return b200_reduce_partials(partials, grid, 400, dw1, gscale, stream);
+}
+
+// =====================================================================================
+// K3 (+K4 statistics), conv1 forward as a Toeplitz GEMM on tcgen05.
+//
+//   out[y, x0+xo, c] = sum_{dy} sum_{k} in[y+dy-2, x0-2+k] * T_dy[k][(xo, c)],
+//   T_dy[k][(xo,c)] = w[c][dy][k - xo]  (0 <= k - xo <= 4, else 0),   k = 0..15, xo = 0..7
+//
+// i.e. for 8 output columns at a time, M = 128 image ROWS, N = 8 columns x 16 channels = 128,
+// K = 16 input columns, five MMAs (one per dy; A = the same input planes shifted down by dy
+// rows).  31 % of the MACs are useful; a 64-cycle MMA still replaces 409,600 FFMAs.
+// The input tile is written by producer warps as bf16 "column planes" (8 pixels = 16 B per
+// row, rows 16 B apart) so that it is directly the no-swizzle K-major A operand.
+// Accuracy: inputs and weights are split into bf16 hi + lo parts and three MMAs
+// (hi*hi + hi*lo + lo*hi) are accumulated in fp32, which restores ~16 mantissa bits - the
+// result matches the fp32 FFMA kernel to output rounding.  The kernel is bounded by writing
+// its 16-channel bf16 output (1.44 GB at batch 5).
+namespace {
+
+constexpr int kFwRows = 128;                 // M: image rows per item
+constexpr int kFwSegPx = 64;                 // output pixels per item along x (8 x-blocks of 8)
+constexpr int kFwBlocks = kFwSegPx / 8;
+constexpr int kFwPlanes = kFwBlocks + 1;     // input planes of 8 pixels
+constexpr int kFwPlaneRows = 136;            // 132 needed, padded so a plane is 17 * 128 B
+constexpr int kFwPlaneBytes = kFwPlaneRows * 16;
+constexpr int kFwXBytes = kFwPlanes * kFwPlaneBytes;          // one of hi / lo
+constexpr int kFwStageBytes = 2 * kFwXBytes;                  // hi + lo
+constexpr int kFwStages = 2;
+constexpr int kFwWBytes = 5 * 2 * 128 * 16;                   // Toeplitz weights, one of hi / lo
+constexpr int kFwProdWarps = 4, kFwEpiWarps = 8;
+constexpr int kFwThreads = 32 * (1 + kFwProdWarps + kFwEpiWarps);   // 416
+constexpr int kFwTStages = 4;
+constexpr int kFwSmemBytes = kFwStages * kFwStageBytes + 2 * kFwWBytes + 2048 + 128;
+
+struct FwGeom {
+  int B, H, W;
+  int nys, nxs, nitems;
+};
+
+__global__ void __launch_bounds__(kFwThreads, 1)
+conv1_fwd_tc_kernel(const float* __restrict__ in, const float* __restrict__ w1, const float* __restrict__ b1,
+                    __nv_bfloat16* __restrict__ x1, float* __restrict__ partials, FwGeom g) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((128u - (smem_u32(smem_raw) & 127u)) & 127u);
+  uint8_t* s_x = smem;                                   // [kFwStages][hi | lo][planes][rows][16 B]
+  uint8_t* s_w = smem + kFwStages * kFwStageBytes;       // [hi | lo][dy][chunk][n][16 B]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_w + 2 * kFwWBytes);
+  uint64_t* xfull = bars;                   // [2]
+  uint64_t* xempty = xfull + kFwStages;     // [2]
+  uint64_t* tfull = xempty + kFwStages;     // [4]
+  uint64_t* tempty = tfull + kFwTStages;    // [4]
+  uint32_t* s_tmem = reinterpret_cast<uint32_t*>(tempty + kFwTStages);
+  float* s_bias = reinterpret_cast<float*>(s_tmem + 4);  // [16]
+  float* s_stat = s_bias + 16;                            // [8 warps][32]
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  // Toeplitz weight tiles (hi / lo)
+  for (int i = threadIdx.x; i < 5 * 2 * 128 * 8; i += kFwThreads) {
+    const int e = i & 7;
+    int r = i >> 3;
+    const int n = r & 127; r >>= 7;
+    const int c = r & 1;
+    const int dy = r >> 1;
+    const int k = c * 8 + e, xo = n >> 4, ch = n & 15, dx = k - xo;
+    const float v = (dx >= 0 && dx <= 4) ? w1[ch * 25 + dy * 5 + dx] : 0.f;
+    const __nv_bfloat16 hi = __float2bfloat16_rn(v);
+    reinterpret_cast<__nv_bfloat16*>(s_w)[i] = hi;
+    reinterpret_cast<__nv_bfloat16*>(s_w + kFwWBytes)[i] = __float2bfloat16_rn(v - __bfloat162float(hi));
+  }
+  if (threadIdx.x < 16) s_bias[threadIdx.x] = b1[threadIdx.x];
+  fence_proxy_async_smem();
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < kFwStages; ++i) { mbar_init(&xfull[i], kFwProdWarps); mbar_init(&xempty[i], 1); }
+    for (int i = 0; i < kFwTStages; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], 128); }
+    mbar_fence_init();
+  }
+  if (warp == 0) tmem_alloc<512>(s_tmem);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *s_tmem;
+
+  if (warp == 0) {
+    // ================= MMA issue =================
+    constexpr uint32_t idesc = umma_idesc_bf16(128, 128, 0, 0);
+    const uint64_t a_tmpl = smem_desc_noswz(0, kFwPlaneBytes, 128);      // K-major: next k-chunk = next plane
+    const uint64_t b_tmpl = smem_desc_noswz(0, 128 * 16, 128);
+    const uint32_t a_hi32 = (uint32_t)(a_tmpl >> 32), a_lo0 = (uint32_t)a_tmpl;
+    const uint32_t b_hi32 = (uint32_t)(b_tmpl >> 32);
+    const uint32_t w_hi_lo = (uint32_t)b_tmpl + (smem_u32(s_w) >> 4), w_lo_lo = w_hi_lo + (kFwWBytes >> 4);
+    uint32_t n = 0, q = 0;
+    for (int item = blockIdx.x; item < g.nitems; item += gridDim.x, ++n) {
+      const uint32_t s = n % kFwStages;
+      mbar_wait(&xfull[s], (n / kFwStages) & 1);
+      const uint32_t xh = a_lo0 + (smem_u32(s_x + s * kFwStageBytes) >> 4), xl = xh + (kFwXBytes >> 4);
+      for (int j = 0; j < kFwBlocks; ++j, ++q) {
+        const uint32_t ts = q % kFwTStages;
+        mbar_wait(&tempty[ts], ((q / kFwTStages) & 1) ^ 1);
+        tc_fence_after();
+        const uint32_t d = tmem_base + ts * 128;
+        const uint32_t pj = (uint32_t)j * (kFwPlaneBytes >> 4);
+        if (elect_one()) {
+#pragma unroll
+          for (int dy = 0; dy < 5; ++dy) {
+            const uint64_t ah = ((uint64_t)a_hi32 << 32) | (uint64_t)(xh + pj + dy);
+            const uint64_t al = ((uint64_t)a_hi32 << 32) | (uint64_t)(xl + pj + dy);
+            const uint64_t bh = ((uint64_t)b_hi32 << 32) | (uint64_t)(w_hi_lo + dy * (4096 >> 4));
+            const uint64_t bl = ((uint64_t)b_hi32 << 32) | (uint64_t)(w_lo_lo + dy * (4096 >> 4));
+            umma_bf16(d, ah, bh, idesc, dy == 0 ? 0u : 1u);
+            umma_bf16(d, ah, bl, idesc, 1u);
+            umma_bf16(d, al, bh, idesc, 1u);
+          }
+          umma_commit(&tfull[ts]);
+          if (j == kFwBlocks - 1) umma_commit(&xempty[s]);
+        }
+        __syncwarp();
+      }
+    }
+  } else if (warp <= kFwProdWarps) {
+    // ================= producers: fp32 input tile -> bf16 hi/lo column planes =================
+    const int pt = threadIdx.x - 32;                    // 0..127
+    constexpr int kTileW = kFwPlanes * 8;               // 72 input columns
+    constexpr int kTileH = kFwRows + 4;                 // 132 input rows
+    uint32_t n = 0;
+    for (int item = blockIdx.x; item < g.nitems; item += gridDim.x, ++n) {
+      const int xs = item % g.nxs;
+      const int ys = (item / g.nxs) % g.nys;
+      const int b = item / (g.nxs * g.nys);
+      const int y0 = ys * kFwRows, x0 = xs * kFwSegPx;
+      const uint32_t s = n % kFwStages;
+      uint8_t* xh = s_x + s * kFwStageBytes;
+      uint8_t* xl = xh + kFwXBytes;
+      mbar_wait(&xempty[s], ((n / kFwStages) & 1) ^ 1);
+      const float* src = in + (size_t)b * g.H * g.W;
+#pragma unroll 8
+      for (int i = pt; i < kTileH * kTileW; i += 32 * kFwProdWarps) {
+        const int rho = i / kTileW, sx = i - rho * kTileW;
+        const int gy = y0 - 2 + rho, gx = x0 - 2 + sx;
+        float v = 0.f;
+        if (gy >= 0 && gy < g.H && gx >= 0 && gx < g.W) v = __ldg(src + (size_t)gy * g.W + gx);
+        const __nv_bfloat16 hi = __float2bfloat16_rn(v);
+        const __nv_bfloat16 lo = __float2bfloat16_rn(v - __bfloat162float(hi));
+        const int off = (sx >> 3) * kFwPlaneBytes + rho * 16 + (sx & 7) * 2;
+        *reinterpret_cast<__nv_bfloat16*>(xh + off) = hi;
+        *reinterpret_cast<__nv_bfloat16*>(xl + off) = lo;
+      }
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&xfull[s]);
+    }
+  } else {
+    // ================= epilogue: 8 warps, two groups alternating tiles =================
+    const int ew = warp - (1 + kFwProdWarps);           // 0..7
+    const int quarter = warp & 3, grp = ew >> 2;
+    const int m = quarter * 32 + lane;
+    float ssum[16], ssq[16];
+#pragma unroll
+    for (int c = 0; c < 16; ++c) { ssum[c] = 0.f; ssq[c] = 0.f; }
+    uint32_t q = 0;
+    for (int item = blockIdx.x; item < g.nitems; item += gridDim.x) {
+      const int xs = item % g.nxs;
+      const int ys = (item / g.nxs) % g.nys;
+      const int b = item / (g.nxs * g.nys);
+      const int y = ys * kFwRows + m;
+      const bool row_ok = y < g.H;
+      for (int j = 0; j < kFwBlocks; ++j, ++q) {
+        if ((int)(q & 1) != grp) continue;
+        const uint32_t ts = q % kFwTStages;
+        mbar_wait(&tfull[ts], (q / kFwTStages) & 1);
+        tc_fence_after();
+        const int xb = xs * kFwSegPx + j * 8;
+        __nv_bfloat16* orow = x1 + (((size_t)b * g.H + (row_ok ? y : 0)) * g.W + xb) * 16;
+#pragma unroll
+        for (int c0 = 0; c0 < 128; c0 += 32) {              // 2 pixels x 16 channels per chunk
+          uint32_t v[32];
+          const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + ts * 128 + c0;
+          tmem_ld16(taddr, *reinterpret_cast<uint32_t(*)[16]>(&v[0]));
+          tmem_ld16(taddr + 16, *reinterpret_cast<uint32_t(*)[16]>(&v[16]));
+          tmem_ld_wait();
+          if (c0 == 96) { tc_fence_before(); mbar_arrive(&tempty[ts]); }
+          const bool ok = row_ok && (xb + (c0 >> 4)) < g.W;     // W % 2 == 0: both pixels or neither
+          uint32_t pk[16];
+#pragma unroll
+          for (int e = 0; e < 32; e += 2) {
+            pk[e >> 1] = pack_bf16x2(__uint_as_float(v[e]) + s_bias[e & 15], __uint_as_float(v[e + 1]) + s_bias[(e + 1) & 15]);
+            // statistics of the ROUNDED values: BN backward relies on mean/var being exactly those of the
+            // stored tensor (sum dx = 0, sum dx*xhat = 0); unrounded stats leave a coherent residual
+            const float f0 = bf16_lo(pk[e >> 1]), f1 = bf16_hi(pk[e >> 1]);
+            if (ok) {
+              ssum[e & 15] += f0; ssq[e & 15] = fmaf(f0, f0, ssq[e & 15]);
+              ssum[(e + 1) & 15] += f1; ssq[(e + 1) & 15] = fmaf(f1, f1, ssq[(e + 1) & 15]);
+            }
+          }
+          if (ok) {
+            uint4* o = reinterpret_cast<uint4*>(orow + (c0 >> 4) * 16);
+            o[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+            o[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+            o[2] = make_uint4(pk[8], pk[9], pk[10], pk[11]);
+            o[3] = make_uint4(pk[12], pk[13], pk[14], pk[15]);
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int c = 0; c < 16; ++c) {
+      const float a = warp_sum(ssum[c]), s2 = warp_sum(ssq[c]);
+      if (lane == 0) { s_stat[ew * 32 + c] = a; s_stat[ew * 32 + 16 + c] = s2; }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  if (threadIdx.x < 32) {
+    float a = 0.f;
+#pragma unroll
+    for (int w8 = 0; w8 < kFwEpiWarps; ++w8) a += s_stat[w8 * 32 + threadIdx.x];
+    partials[(size_t)blockIdx.x * 32 + threadIdx.x] = a;
+  }
+  if (warp == 0) { __syncwarp(); tmem_dealloc<512>(tmem_base); }
+}
+
+}  // namespace
+
+// Same contract as b200_conv1_fwd; partials must hold [b200_sm_count()][32]; *nparts_out = rows written.
+B200_API int b200_conv1_fwd_tc(const void* in_f32, const void* w1, const void* b1, void* x1_bf16, void* partials, int B,
+                               int H, int W, int* nparts_out, void* stream) {
+  B200_CHECK(H % 2 == 0 && W % 2 == 0, "conv1_fwd_tc: H and W must be even");
+  cudaStream_t s = (cudaStream_t)stream;
+  static std::once_flag once;
+  static cudaError_t attr_err = cudaSuccess;
+  std::call_once(once, [&] {
+    attr_err = cudaFuncSetAttribute(conv1_fwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kFwSmemBytes);
+  });
+  B200_CUDA(attr_err);
+  FwGeom g;
+  g.B = B; g.H = H; g.W = W;
+  g.nys = (H + kFwRows - 1) / kFwRows;
+  g.nxs = (W + kFwSegPx - 1) / kFwSegPx;
+  g.nitems = B * g.nys * g.nxs;
+  const int nsm = b200_num_sms();
+  const int grid = g.nitems < nsm ? g.nitems : nsm;
+  conv1_fwd_tc_kernel<<<grid, kFwThreads, kFwSmemBytes, s>>>((const float*)in_f32, (const float*)w1, (const float*)b1,
+                                                             (__nv_bfloat16*)x1_bf16, (float*)partials, g);
+  B200_LAUNCH_CHECK();
+  if (nparts_out) *nparts_out = grid;
+  return 0;
+}

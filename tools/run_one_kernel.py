@@ -28,7 +28,10 @@ fn = {
     "conv2_fwd": lambda: ops.conv2_fwd_tc(eng.p1, P["layer2.0.weight"], P["layer2.0.bias"], eng.x2, eng.part_c2),
     "conv2_dgrad": lambda: ops.conv2_dgrad_tc(eng.x2, P["layer2.0.weight"], torch.empty_like(eng.p1)),
     "conv2_wgrad": lambda: ops.conv2_wgrad_tc(eng.p1, eng.x2, eng.part_wg2, eng.grads["layer2.0.weight"]),
+    "conv1_fwd_tc": lambda: ops.conv1_fwd_tc(eng.x, P["layer1.0.weight"], P["layer1.0.bias"], eng.x1, eng.part_c1),
     "conv1_fwd": lambda: ops.conv1_fwd(eng.x, P["layer1.0.weight"], P["layer1.0.bias"], eng.x1, eng.part_c1),
+    "conv1_wgrad_tc": lambda: ops.conv1_wgrad_tc(eng.x, eng.x1, eng.p1, eng.bn1, eng.red1, eng.part_wg1,
+                                                 eng.grads["layer1.0.weight"]),
     "conv1_wgrad": lambda: ops.conv1_wgrad(eng.x, eng.x1, eng.p1, eng.bn1, eng.red1, eng.part_wg1,
                                            eng.grads["layer1.0.weight"]),
     "step": lambda: eng.train_step(imgs, labels),

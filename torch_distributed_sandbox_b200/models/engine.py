@@ -31,6 +31,7 @@ runs on a side stream while the conv backward continues (K10 -> K16).
 """
 from __future__ import annotations
 
+import os
 from collections import OrderedDict
 from typing import Optional, Sequence
 
@@ -80,6 +81,7 @@ class FusedConvNet:
         self.image_shape = (H, W)
         self.lr = float(lr)
         self.conv_backend = conv_backend
+        self.conv1_backend = os.environ.get("B200DP_CONV1", "tc")      # "tc" (tcgen05) | "ffma"
         self.fuse_fc_sgd = bool(fuse_fc_sgd)
         self.F = rn.feature_size((H, W))
         self.comm = None           # set by parallel.ddp for data-parallel runs
@@ -261,8 +263,12 @@ class FusedConvNet:
         if images is not None:
             self.set_input(images)
         P, B, H, W = self.params, self.B, self.H, self.W
-        ops.conv1_fwd(self.x, P["layer1.0.weight"], P["layer1.0.bias"], self.x1, self.part_c1)
-        ops.bn_finalize(self.part_c1, self.g_c1, 16, B * H * W, P["layer1.1.weight"], P["layer1.1.bias"],
+        if self.conv1_backend == "tc":
+            n1 = ops.conv1_fwd_tc(self.x, P["layer1.0.weight"], P["layer1.0.bias"], self.x1, self.part_c1)
+        else:
+            ops.conv1_fwd(self.x, P["layer1.0.weight"], P["layer1.0.bias"], self.x1, self.part_c1)
+            n1 = self.g_c1
+        ops.bn_finalize(self.part_c1, n1, 16, B * H * W, P["layer1.1.weight"], P["layer1.1.bias"],
                         self.bn_buf[1]["mean"], self.bn_buf[1]["var"], self.bn_buf[1]["nbt"], self.bn1)
         ops.bn_relu_pool(self.x1, self.bn1, self.p1)
         if self.conv_backend == "tc":
@@ -325,7 +331,8 @@ class FusedConvNet:
         ops.pool_bn_bwd(self.x1, self.dp1, self.bn1, self.red1, self.part_bwd, None, mode=0)
         ops.bn_bwd_finalize(self.part_bwd, self.g_pbb, 16, B * H * W, self.red1, G["layer1.1.weight"],
                             G["layer1.1.bias"], gs)
-        ops.conv1_wgrad(self.x, self.x1, self.dp1, self.bn1, self.red1, self.part_wg1, G["layer1.0.weight"], gs)
+        wg1 = ops.conv1_wgrad_tc if self.conv1_backend == "tc" else ops.conv1_wgrad
+        wg1(self.x, self.x1, self.dp1, self.bn1, self.red1, self.part_wg1, G["layer1.0.weight"], gs)
         G["layer1.0.bias"].zero_()
 
     def step(self) -> None:

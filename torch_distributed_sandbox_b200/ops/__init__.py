@@ -47,6 +47,9 @@ def _lib():
                                              c_float, c_void_p]
         lib.b200_conv1_wgrad.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                          c_int, c_int, c_int, c_float, c_void_p]
+        lib.b200_conv1_wgrad_tc.argtypes = lib.b200_conv1_wgrad.argtypes
+        lib.b200_conv1_fwd_tc.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int,
+                                          ctypes.POINTER(c_int), c_void_p]
         lib.b200_conv2_wgrad_tc.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_float,
                                             c_void_p]
         lib.b200_conv2_fwd_tc.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int,
@@ -112,6 +115,17 @@ def conv1_fwd(x_f32, w1, b1, x1_bf16, partials):
     _count(1)
 
 
+def conv1_fwd_tc(x_f32, w1, b1, x1_bf16, partials) -> int:
+    """K3 on tcgen05 (Toeplitz GEMM over 8 output columns, bf16 hi/lo split, fp32 accumulate).
+    Returns the number of BN-stat partial rows written (partials: [sm_count()][32])."""
+    B, H, W = x_f32.shape
+    n = c_int(0)
+    _native.check(_lib().b200_conv1_fwd_tc(_p(x_f32), _p(w1), _p(b1), _p(x1_bf16), _p(partials), B, H, W,
+                                           ctypes.byref(n), _stream()), "conv1_fwd_tc")
+    _count(1)
+    return n.value
+
+
 def bn_finalize(partials, nparts, C, count, gamma, beta, running_mean, running_var, nbt, out, momentum=0.1,
                 eps=1e-5):
     """K4: batch stats -> [scale|shift|mean|rstd] + running-stat update."""
@@ -147,6 +161,15 @@ def conv1_wgrad(x_f32, x1_bf16, dp1_bf16, bn, red, partials, dw1, gscale=1.0):
     B, H, W = x_f32.shape
     _native.check(_lib().b200_conv1_wgrad(_p(x_f32), _p(x1_bf16), _p(dp1_bf16), _p(bn), _p(red), _p(partials),
                                           _p(dw1), B, H, W, gscale, _stream()), "conv1_wgrad")
+    _count(2)
+
+
+def conv1_wgrad_tc(x_f32, x1_bf16, dp1_bf16, bn, red, partials, dw1, gscale=1.0):
+    """K13 on tcgen05: same contract as conv1_wgrad; pixels are the GEMM K dimension, the conv1-output
+    gradient is produced into shared memory by CUDA-core warps and never touches HBM."""
+    B, H, W = x_f32.shape
+    _native.check(_lib().b200_conv1_wgrad_tc(_p(x_f32), _p(x1_bf16), _p(dp1_bf16), _p(bn), _p(red), _p(partials),
+                                             _p(dw1), B, H, W, gscale, _stream()), "conv1_wgrad_tc")
     _count(2)
 
 
