@@ -311,7 +311,7 @@ B200_API int b200_ar_large_f32(void* const* ptrs, void* mc, void* const* flags, 
   cudaStream_t s = (cudaStream_t)stream;
   if (algo == 2) {
     B200_CHECK(mc != nullptr && (!wptrs || wmc), "allreduce: NVLS requested but no multicast mapping");
-    allreduce_nvls_f32_kernel<4><<<blocks, 512, 0, s>>>(P, Wp, n / 4, scale, lr, epoch);
+    allreduce_nvls_f32_kernel<8><<<blocks, 512, 0, s>>>(P, Wp, n / 4, scale, lr, epoch);   // 8 x 16 B in flight per thread
   } else {
     allreduce_twoshot_f32_kernel<<<blocks, 512, 0, s>>>(P, Wp, n / 4, scale, lr, epoch);
   }

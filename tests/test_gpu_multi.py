@@ -97,7 +97,7 @@ def _collectives(rank, world, port):
 
 @needs2
 def test_native_collectives():
-    world = min(_ngpu(), 4)
+    world = min(_ngpu(), 8)
     b2.spawn(_collectives, args=(world, b2.find_free_port()), nprocs=world)
 
 

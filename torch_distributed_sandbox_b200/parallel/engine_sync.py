@@ -32,9 +32,10 @@ class EngineGradSync:
         self.broadcast_buffers = broadcast_buffers
         self.fuse_sgd = os.environ.get("B200DP_FUSE_AR_SGD", "1") == "1"
         self.algo = os.environ.get("B200DP_AR_ALGO") or None         # "nvls" | "p2p" | None (auto)
-        self.blocks = int(os.environ.get("B200DP_AR_BLOCKS", "64"))
+        self.blocks = int(os.environ.get("B200DP_AR_BLOCKS", "32"))     # CTAs of the overlapped bucket all-reduce (tuned at N=2)
         self._fc_event = None
         self._steps = 0
+        self._debug_skip_fc = os.environ.get("B200DP_DEBUG_SKIP_FC_ALLREDUCE", "0") == "1"   # timing experiments only
         be = self.backend
         if self.world > 1 and getattr(be, "name", "") != "native":
             raise RuntimeError("the fused engine needs the native (symmetric-memory) backend for world_size > 1")
@@ -79,7 +80,7 @@ class EngineGradSync:
 
     def fc_grad_ready(self, engine) -> None:
         """Called right after the fc backward kernel is enqueued (main stream)."""
-        if self.world == 1:
+        if self.world == 1 or self._debug_skip_fc:
             return
         main = torch.cuda.current_stream()
         ready = torch.cuda.Event()
