@@ -43,12 +43,16 @@ def env_rank():
         int(os.environ.get("WORLD_SIZE", "1"))
 
 
-def timed_loop(step_fn, K, W, sync_all, max_over_ranks, local_rank, sample_clocks=True):
-    """W warm-up + K timed calls of step_fn(i); returns (ms_per_step max over ranks, clocks)."""
+def timed_loop(step_fn, K, W, sync_all, max_over_ranks, local_rank, sample_clocks=True, drain=None):
+    """W warm-up + K timed calls of step_fn(i); returns (ms_per_step max over ranks, clocks).
+    ``drain`` makes the launching stream wait for any work a step left on side streams (the
+    overlapped gradient all-reduce), so the timed region contains ALL the work of its K steps."""
     import torch
     from torch_distributed_sandbox_b200.utils.clocks import ClockSampler
     for i in range(W):
         step_fn(i)
+    if drain:
+        drain()
     sync_all()
     start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     sampler = ClockSampler(_physical_gpu_index(local_rank)) if sample_clocks else None
@@ -58,6 +62,8 @@ def timed_loop(step_fn, K, W, sync_all, max_over_ranks, local_rank, sample_clock
     start.record()
     for i in range(K):
         step_fn(W + i)
+    if drain:
+        drain()
     end.record()
     torch.cuda.synchronize()
     ms = start.elapsed_time(end) / K
@@ -135,10 +141,10 @@ def run_b200dp(a):
         torch.cuda.current_stream().synchronize()
 
     launches0 = ops.LAUNCHES
-    ms, clocks = timed_loop(dev_step, a.steps, a.warmup, sync_all, max_over_ranks, local_rank)
+    ms, clocks = timed_loop(dev_step, a.steps, a.warmup, sync_all, max_over_ranks, local_rank, drain=eng._sync_fc)
     launches = (ops.LAUNCHES - launches0) * a.steps // (a.steps + a.warmup)
     ms_e2e, _ = timed_loop(e2e_step, a.steps, max(3, a.warmup // 2), sync_all, max_over_ranks, local_rank,
-                           sample_clocks=False)
+                           sample_clocks=False, drain=eng._sync_fc)
     loss_val = float(loss_host)
     peak = torch.cuda.max_memory_allocated(dev) / 2 ** 30
     if world > 1:

@@ -134,6 +134,33 @@ allreduce_oneshot_kernel<__nv_bfloat16, float>(Peers P, __nv_bfloat16* __restric
   sys_barrier(P, epoch + 1);
 }
 
+// fp32, 16 bytes per thread, every peer's load in flight before the first add; optional fused SGD
+// (param -= lr * scale * sum) for the small DDP bucket.  `in` is symmetric, out/param are local.
+template <int MAXW>
+__global__ void __launch_bounds__(512)
+allreduce_oneshot_f32x4_kernel(Peers P, float4* __restrict__ out, float4* __restrict__ param, size_t n4, float scale,
+                               float lr, uint32_t epoch) {
+  sys_barrier(P, epoch);
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
+    float4 v[MAXW];
+#pragma unroll
+    for (int p = 0; p < MAXW; ++p)
+      if (p < P.world) v[p] = ld_peer16(reinterpret_cast<const float4*>(P.ptr[p]) + i);
+    float4 acc = v[0];
+#pragma unroll
+    for (int p = 1; p < MAXW; ++p)
+      if (p < P.world) { acc.x += v[p].x; acc.y += v[p].y; acc.z += v[p].z; acc.w += v[p].w; }
+    acc.x *= scale; acc.y *= scale; acc.z *= scale; acc.w *= scale;
+    if (out) out[i] = acc;
+    if (param) {
+      float4 w = param[i];
+      w.x = fmaf(-lr, acc.x, w.x); w.y = fmaf(-lr, acc.y, w.y); w.z = fmaf(-lr, acc.z, w.z); w.w = fmaf(-lr, acc.w, w.w);
+      param[i] = w;
+    }
+  }
+  sys_barrier(P, epoch + 1);
+}
+
 // -------------------------------------------------------------- two-shot P2P ---
 // In place on the symmetric fp32 buffer.  n4 = number of float4; shard r = [lo_r, hi_r).
 // If w != nullptr the SGD update is fused: w is this rank's weight buffer (same layout, also
@@ -174,8 +201,11 @@ allreduce_twoshot_f32_kernel(Peers P, Peers Wp, size_t n4, float scale, float lr
 }
 
 // ------------------------------------------------------------- two-shot NVLS ---
+// Register budget matters here: this kernel runs UNDER the backward/forward compute kernels.  At <= 32
+// registers a 512-thread CTA takes 16 K of the SM's 64 K registers and co-resides with every persistent
+// compute CTA of the step; at 46 it could not share an SM with conv1_*_tc and delayed those kernels.
 template <int UNROLL>
-__global__ void __launch_bounds__(512)
+__global__ void __launch_bounds__(512, 4)
 allreduce_nvls_f32_kernel(Peers P, Peers Wp, size_t n4, float scale, float lr, uint32_t epoch) {
   const int r = P.rank, n = P.world;
   const size_t per = (n4 + n - 1) / n;
@@ -299,6 +329,21 @@ B200_API int b200_ar_oneshot(void* const* ptrs, void* const* flags, int rank, in
   return 0;
 }
 
+// Small fp32 SUM straight from a symmetric input (no staging copy): out (local, may be null) = scale*sum,
+// and/or param -= lr * scale * sum.  n % 4 == 0.
+B200_API int b200_ar_oneshot_f32x4(void* const* ptrs, void* const* flags, int rank, int world, void* out, void* param,
+                                   size_t n, float scale, float lr, int blocks, uint32_t epoch, void* stream) {
+  B200_CHECK(world <= kMaxRanks && blocks >= 1 && blocks <= kMaxBlocks && n % 4 == 0, "oneshot_f32x4: bad arguments");
+  Peers P = make_peers(ptrs, flags, nullptr, rank, world);
+  cudaStream_t s = (cudaStream_t)stream;
+  if (world <= 8)
+    allreduce_oneshot_f32x4_kernel<8><<<blocks, 512, 0, s>>>(P, (float4*)out, (float4*)param, n / 4, scale, lr, epoch);
+  else
+    allreduce_oneshot_f32x4_kernel<16><<<blocks, 512, 0, s>>>(P, (float4*)out, (float4*)param, n / 4, scale, lr, epoch);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
 // In-place fp32 SUM over the symmetric buffer (n floats, n % 4 == 0).  algo: 1 = two-shot P2P,
 // 2 = two-shot NVLS (needs mc).  wptrs/wmc != null fuses SGD: W -= lr * (scale * sum g).
 B200_API int b200_ar_large_f32(void* const* ptrs, void* mc, void* const* flags, void* const* wptrs, void* wmc,
@@ -311,7 +356,7 @@ B200_API int b200_ar_large_f32(void* const* ptrs, void* mc, void* const* flags, 
   cudaStream_t s = (cudaStream_t)stream;
   if (algo == 2) {
     B200_CHECK(mc != nullptr && (!wptrs || wmc), "allreduce: NVLS requested but no multicast mapping");
-    allreduce_nvls_f32_kernel<8><<<blocks, 512, 0, s>>>(P, Wp, n / 4, scale, lr, epoch);   // 8 x 16 B in flight per thread
+    allreduce_nvls_f32_kernel<4><<<blocks, 512, 0, s>>>(P, Wp, n / 4, scale, lr, epoch);
   } else {
     allreduce_twoshot_f32_kernel<<<blocks, 512, 0, s>>>(P, Wp, n / 4, scale, lr, epoch);
   }

@@ -58,7 +58,7 @@ struct WgGeom {
   int nstrips, ngroups, nitems;
 };
 
-__global__ void __launch_bounds__(kWgThreads, 1)
+__global__ void __maxnreg__(160)     // 288 threads x 160 regs = 46 K: leaves room for a comm CTA on the SM
 conv1_wgrad_tc_kernel(const float* __restrict__ in, const __nv_bfloat16* __restrict__ x1,
                       const __nv_bfloat16* __restrict__ dp1, const float* __restrict__ bn,
                       const float* __restrict__ red, float* __restrict__ partials, WgGeom g) {
@@ -324,7 +324,7 @@ struct FwGeom {
   int nys, nxs, nitems;
 };
 
-__global__ void __launch_bounds__(kFwThreads, 1)
+__global__ void __maxnreg__(112)     // 416 threads x 112 regs = 46.6 K: leaves room for a comm CTA on the SM
 conv1_fwd_tc_kernel(const float* __restrict__ in, const float* __restrict__ w1, const float* __restrict__ b1,
                     __nv_bfloat16* __restrict__ x1, float* __restrict__ partials, FwGeom g) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];

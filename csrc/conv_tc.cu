@@ -429,7 +429,7 @@ template <int CIN, int COUT>
 struct RsCfg {
   static constexpr int kPlanes = CIN / 8;
   static constexpr int kSlotBytes = kPlanes * kPlaneBytes;
-  static constexpr int kSlots = 8;
+  static constexpr int kSlots = 10;          // >= kCpDepth + 2
   static constexpr int kKSteps = CIN / 16;
   static constexpr int kNB = 5 * COUT;                       // B rows per (dx, kk): n = jj*COUT + co
   static constexpr int kWChunkBytes = kNB * 16;              // one 8-channel k-chunk of all n rows
@@ -447,7 +447,7 @@ struct RsCfg {
 // LDGSTS=true has the whole producer warp issue 16-byte cp.async copies (zero-fill = padding),
 // 9-25 warp instructions per row, software-pipelined kCpDepth rows deep with wait_group,
 // then fence.proxy.async + one mbarrier arrive per row.
-constexpr int kCpDepth = 3;
+constexpr int kCpDepth = 6;      // rows of cp.async in flight per producer warp (memory-level parallelism)
 
 template <int C>
 __device__ __forceinline__ void cp_row(uint8_t* dst, const __nv_bfloat16* __restrict__ src, int b, int y, int x_first,
@@ -693,7 +693,7 @@ conv5x5_rs_kernel(const __grid_constant__ CUtensorMap tm_act, const __nv_bfloat1
 // wgrad, row-stationary: the act (p1) row is the stationary operand; the five dx2 rows it
 // pairs with (y = r-2 .. r+2) are five CONSECUTIVE slots of the dx2 ring, i.e. 20 consecutive
 // 8-channel planes, i.e. one MN-major B operand with N = 160.  D[pl][(dx,ci8)][(jj,co)], dy = 4-jj.
-constexpr int kWg2SlotsA = 4, kWg2SlotsB = 12;
+constexpr int kWg2SlotsA = 8, kWg2SlotsB = 12;      // A >= kCpDepth + 1, B >= 5 + kCpDepth
 constexpr int kWg2SmemBytes = kWg2SlotsA * kWgSlotABytes + kWg2SlotsB * kWgSlotBBytes + 1024 + 128;
 
 template <bool LDGSTS>

@@ -120,6 +120,8 @@ int b200_ar_max_blocks(void);
 int b200_ar_barrier(void* const* flags, int rank, int world, uint32_t epoch, void* stream);
 int b200_ar_oneshot(void* const* ptrs, void* const* flags, int rank, int world, void* out, size_t n, int dtype, int op,
                     float scale, int blocks, uint32_t epoch, void* stream);
+int b200_ar_oneshot_f32x4(void* const* ptrs, void* const* flags, int rank, int world, void* out, void* param, size_t n,
+                          float scale, float lr, int blocks, uint32_t epoch, void* stream);
 int b200_ar_large_f32(void* const* ptrs, void* mc, void* const* flags, void* const* wptrs, void* wmc, int rank,
                       int world, size_t n, float scale, float lr, int algo, int blocks, uint32_t epoch, void* stream);
 int b200_ar_nvls_bf16(void* mc, void* const* flags, int rank, int world, size_t n, float scale, int blocks,

@@ -86,6 +86,7 @@ class FusedConvNet:
         self.F = rn.feature_size((H, W))
         self.comm = None           # set by parallel.ddp for data-parallel runs
         self._fc_fused_done = False
+        self._fc_pending = False
         self._publish_grads = lambda: None
         self._on_rebind = lambda: None
         self.grad_scale = 1.0      # 1/world_size under DDP (fused into the producing kernels)
@@ -167,7 +168,7 @@ class FusedConvNet:
         }
 
     def rebind_storage(self, fcw: Optional[torch.Tensor] = None, fcw_grad: Optional[torch.Tensor] = None,
-                       bn_flat: Optional[torch.Tensor] = None) -> None:
+                       bn_flat: Optional[torch.Tensor] = None, small_grad: Optional[torch.Tensor] = None) -> None:
         """Move fc.weight / its gradient / the BN buffer blob into caller-provided storage
         (symmetric memory under DDP); current values are preserved."""
         if fcw is not None:
@@ -176,6 +177,13 @@ class FusedConvNet:
             self.fcw = fcw
         if fcw_grad is not None:
             self.fcw_grad = fcw_grad.view(10, self.F)
+        if small_grad is not None:
+            self.small_grad = small_grad
+            off = 0
+            for name, shape in SMALL_LAYOUT:
+                n = _numel(shape)
+                self.grads[name] = self.small_grad[off:off + n].view(shape)
+                off += n
         if bn_flat is not None:
             bn_flat.copy_(self.bn_flat)
             self.bn_flat = bn_flat
@@ -187,6 +195,7 @@ class FusedConvNet:
         """torch ``state_dict`` with the reference's 16 keys; ``fc.weight`` is
         converted from the internal HWC-flatten order back to the reference's CHW order."""
         out = OrderedDict()
+        self._sync_fc()
         with torch.cuda.device(self.device):
             fcw_chw = torch.empty_like(self.fcw)
             ops.fcw_permute(self.fcw, fcw_chw, 32, self.H // 4, self.W // 4, to_hwc=False)
@@ -280,6 +289,7 @@ class FusedConvNet:
                         self.bn2)
         ops.bn_relu_pool(self.x2, self.bn2, self.p2)
         p2 = self.p2.view(B, self.F)
+        self._sync_fc()
         for b0 in range(0, B, 8):
             b1 = min(B, b0 + 8)
             ops.fc_fwd(p2[b0:b1], self.fcw, P["fc.bias"], self.part_fc, self.logits[b0:b1])
@@ -336,15 +346,25 @@ class FusedConvNet:
         G["layer1.0.bias"].zero_()
 
     def step(self) -> None:
-        """SGD (lr, no momentum / weight decay: mnist_onegpu.py:49) on every parameter."""
+        """SGD (lr, no momentum / weight decay: mnist_onegpu.py:49) on every parameter.  Under DDP the
+        small bucket's update is fused into its one-shot all-reduce, and the fc.weight update (fused into
+        the overlapped bucket all-reduce) is only WAITED FOR right before the next fc forward
+        (``_sync_fc``): nothing earlier in the next step reads fc.weight, so the all-reduce also hides
+        under the next forward's conv layers."""
+        small_done = self.comm.small_grads_ready(self) if self.comm is not None else False
+        if not small_done:
+            ops.sgd(self.small, self.small_grad, self.lr)
         if self.comm is not None:
-            self.comm.small_grads_ready(self)        # one-shot all-reduce of the 53 KB bucket
-        ops.sgd(self.small, self.small_grad, self.lr)
-        fc_done = self._fc_fused_done
-        if self.comm is not None:
-            fc_done = self.comm.wait_fc_grad(self) or fc_done   # True when SGD ran inside the all-reduce
-        if not fc_done:
+            self._fc_pending = True
+        elif not self._fc_fused_done:
             ops.sgd(self.fcw, self.fcw_grad, self.lr)
+
+    def _sync_fc(self) -> None:
+        """Make fc.weight current (DDP: wait for the bucket all-reduce; apply SGD if it was not fused)."""
+        if self._fc_pending:
+            self._fc_pending = False
+            if not self.comm.wait_fc_grad(self):
+                ops.sgd(self.fcw, self.fcw_grad, self.lr)
 
     def train_step(self, images: torch.Tensor, labels: torch.Tensor) -> torch.Tensor:
         self.forward(images)

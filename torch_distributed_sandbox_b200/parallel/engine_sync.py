@@ -47,7 +47,8 @@ class EngineGradSync:
                 grad = be.alloc_symmetric(n, torch.float32)
                 wsym = be.alloc_symmetric(n, torch.float32) if self.fuse_sgd else None
                 bn = be.alloc_symmetric(128, torch.float32, multicast=False)
-                engine.rebind_storage(fcw=wsym, fcw_grad=grad, bn_flat=bn)
+                sg = be.alloc_symmetric(engine.small_grad.numel(), torch.float32, multicast=False)
+                engine.rebind_storage(fcw=wsym, fcw_grad=grad, bn_flat=bn, small_grad=sg)
             self.comm_stream = be.comm_stream
         if init_sync:
             self._sync_params()
@@ -76,7 +77,7 @@ class EngineGradSync:
         """C4: BatchNorm running stats follow rank 0 (they are not used by the train-mode
         forward; this keeps checkpoints identical on every rank, like DDP does)."""
         if self.world > 1 and self.broadcast_buffers:
-            dist.broadcast(self.engine.bn_flat, src=self.group.ranks[0], group=self.group)
+            self.backend.broadcast_symmetric_inplace(self.engine.bn_flat, 0)
 
     def fc_grad_ready(self, engine) -> None:
         """Called right after the fc backward kernel is enqueued (main stream)."""
@@ -93,9 +94,12 @@ class EngineGradSync:
             self._fc_event = torch.cuda.Event()
             self._fc_event.record(self.comm_stream)
 
-    def small_grads_ready(self, engine) -> None:
-        if self.world > 1:
-            self.backend.all_reduce(engine.small_grad, dist.ReduceOp.AVG, channel=0)
+    def small_grads_ready(self, engine) -> bool:
+        """One-shot all-reduce of the 53 KB bucket with the SGD update fused in; True = parameters updated."""
+        if self.world == 1:
+            return False
+        self.backend.all_reduce_small_symmetric(engine.small_grad, 1.0 / self.world, sgd=(engine.small, engine.lr))
+        return True
 
     def wait_fc_grad(self, engine) -> bool:
         """Main stream waits for the bucket all-reduce; True when SGD was applied in it."""

@@ -46,6 +46,8 @@ def _lib():
         lib.b200_ar_barrier.argtypes = [PP, c_int, c_int, c_uint32, c_void_p]
         lib.b200_ar_oneshot.argtypes = [PP, PP, c_int, c_int, c_void_p, c_size_t, c_int, c_int, c_float, c_int,
                                         c_uint32, c_void_p]
+        lib.b200_ar_oneshot_f32x4.argtypes = [PP, PP, c_int, c_int, c_void_p, c_void_p, c_size_t, c_float, c_float, c_int,
+                                              c_uint32, c_void_p]
         lib.b200_ar_large_f32.argtypes = [PP, c_void_p, PP, PP, c_void_p, c_int, c_int, c_size_t, c_float, c_float,
                                           c_int, c_int, c_uint32, c_void_p]
         lib.b200_ar_nvls_bf16.argtypes = [c_void_p, PP, c_int, c_int, c_size_t, c_float, c_int, c_uint32, c_void_p]
@@ -233,6 +235,40 @@ class SymmBackend:
         ev = torch.cuda.Event()
         ev.record()
         return Work(ev)
+
+    def all_reduce_small_symmetric(self, t: torch.Tensor, scale: float, out: Optional[torch.Tensor] = None,
+                                   sgd: Optional[Tuple[torch.Tensor, float]] = None, channel: int = 0):
+        """One-shot fp32 all-reduce reading a SYMMETRIC tensor on every rank directly (no staging copy):
+        ``out = scale * sum`` and/or ``sgd[0] -= sgd[1] * scale * sum``; ``t`` itself is left untouched."""
+        n = t.numel()
+        if self.size == 1:
+            if out is not None:
+                out.copy_(t * scale)
+            if sgd is not None:
+                sgd[0].view(-1)[:n].add_(t.view(-1), alpha=-float(sgd[1]) * scale)
+            return
+        sym = self.lookup(t)
+        assert sym is not None and sym[1] % 16 == 0 and n % 4 == 0 and t.dtype == torch.float32
+        buf, off = sym
+        rc = _lib().b200_ar_oneshot_f32x4(buf.ptr_array(off), self._flag_arr[channel], self.rank, self.size,
+                                          c_void_p(out.data_ptr() if out is not None else 0),
+                                          c_void_p(sgd[0].data_ptr() if sgd is not None else 0), n, scale,
+                                          float(sgd[1]) if sgd is not None else 0.0,
+                                          max(1, min(32, (n // 4 + 511) // 512)), self._next_epoch(channel), self._stream())
+        _native.check(rc, "all_reduce(one-shot f32x4)")
+
+    def broadcast_symmetric_inplace(self, t: torch.Tensor, src: int, channel: int = 0):
+        """Every rank overwrites its copy of the symmetric tensor ``t`` with rank ``src``'s (one tiny kernel)."""
+        if self.size == 1:
+            return
+        sym = self.lookup(t)
+        nb = t.numel() * t.element_size()
+        assert sym is not None and sym[1] % 16 == 0 and nb % 16 == 0
+        buf, off = sym
+        rc = _lib().b200_ar_broadcast(buf.ptr_array(off), self._flag_arr[channel], self.rank, self.size,
+                                      c_void_p(t.data_ptr()), nb, src, self._blocks(nb), self._next_epoch(channel),
+                                      self._stream())
+        _native.check(rc, "broadcast(symmetric)")
 
     def _padded_io(self, t: torch.Tensor):
         """(contiguous byte view padded to 16 B, needs_copy_back)"""
