@@ -317,7 +317,10 @@ constexpr int kFwWBytes = 5 * 2 * 128 * 16;                   // Toeplitz weight
 constexpr int kFwProdWarps = 4, kFwEpiWarps = 8;
 constexpr int kFwThreads = 32 * (1 + kFwProdWarps + kFwEpiWarps);   // 416
 constexpr int kFwTStages = 4;
-constexpr int kFwSmemBytes = kFwStages * kFwStageBytes + 2 * kFwWBytes + 2048 + 128;
+constexpr int kFwTileW = kFwPlanes * 8;      // 72 input columns
+constexpr int kFwTileH = kFwRows + 4;        // 132 input rows
+constexpr int kFwRawBytes = kFwTileH * kFwTileW * 4;          // fp32 staging of one input tile (38 KB)
+constexpr int kFwSmemBytes = kFwStages * kFwStageBytes + 2 * kFwWBytes + 2 * kFwRawBytes + 2048 + 128;
 
 struct FwGeom {
   int B, H, W;
@@ -331,7 +334,8 @@ conv1_fwd_tc_kernel(const float* __restrict__ in, const float* __restrict__ w1, 
   uint8_t* smem = smem_raw + ((128u - (smem_u32(smem_raw) & 127u)) & 127u);
   uint8_t* s_x = smem;                                   // [kFwStages][hi | lo][planes][rows][16 B]
   uint8_t* s_w = smem + kFwStages * kFwStageBytes;       // [hi | lo][dy][chunk][n][16 B]
-  uint64_t* bars = reinterpret_cast<uint64_t*>(s_w + 2 * kFwWBytes);
+  uint8_t* s_raw = s_w + 2 * kFwWBytes;                  // [2][132][72] fp32, filled by cp.async
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_raw + 2 * kFwRawBytes);
   uint64_t* xfull = bars;                   // [2]
   uint64_t* xempty = xfull + kFwStages;     // [2]
   uint64_t* tfull = xempty + kFwStages;     // [4]
@@ -405,31 +409,45 @@ conv1_fwd_tc_kernel(const float* __restrict__ in, const float* __restrict__ w1, 
     }
   } else if (warp <= kFwProdWarps) {
     // ================= producers: fp32 input tile -> bf16 hi/lo column planes =================
+    // The tile of item n+1 is fetched with 8-byte cp.async (zero-fill outside the image) into an fp32
+    // staging buffer while item n is converted, so HBM latency is off the critical path and costs no
+    // registers.  Every thread converts exactly the pieces it fetched: no barrier between the two steps.
     const int pt = threadIdx.x - 32;                    // 0..127
-    constexpr int kTileW = kFwPlanes * 8;               // 72 input columns
-    constexpr int kTileH = kFwRows + 4;                 // 132 input rows
-    uint32_t n = 0;
-    for (int item = blockIdx.x; item < g.nitems; item += gridDim.x, ++n) {
+    constexpr int kPieces = kFwTileH * kFwTileW / 2;    // 8-byte pieces (2 pixels) per tile
+    auto fetch = [&](int item, int buf) {
       const int xs = item % g.nxs;
       const int ys = (item / g.nxs) % g.nys;
       const int b = item / (g.nxs * g.nys);
       const int y0 = ys * kFwRows, x0 = xs * kFwSegPx;
+      const float* src = in + (size_t)b * g.H * g.W;
+      uint8_t* raw = s_raw + buf * kFwRawBytes;
+      for (int i = pt; i < kPieces; i += 32 * kFwProdWarps) {
+        const int rho = i / (kFwTileW / 2), sx = 2 * (i - rho * (kFwTileW / 2));
+        const int gy = y0 - 2 + rho, gx = x0 - 2 + sx;        // gx even, W even: both pixels in or both out
+        const bool ok = gy >= 0 && gy < g.H && gx >= 0 && gx < g.W;
+        cp_async8(raw + (size_t)i * 8, src + (ok ? (size_t)gy * g.W + gx : 0), ok ? 8u : 0u);
+      }
+      cp_async_commit();
+    };
+    if ((int)blockIdx.x < g.nitems) fetch(blockIdx.x, 0);
+    uint32_t n = 0;
+    for (int item = blockIdx.x; item < g.nitems; item += gridDim.x, ++n) {
       const uint32_t s = n % kFwStages;
       uint8_t* xh = s_x + s * kFwStageBytes;
       uint8_t* xl = xh + kFwXBytes;
+      const bool more = item + (int)gridDim.x < g.nitems;
+      if (more) fetch(item + gridDim.x, (n + 1) & 1);
+      if (more) cp_async_wait<1>(); else cp_async_wait<0>();   // this item's pieces (of this thread) have landed
       mbar_wait(&xempty[s], ((n / kFwStages) & 1) ^ 1);
-      const float* src = in + (size_t)b * g.H * g.W;
-#pragma unroll 8
-      for (int i = pt; i < kTileH * kTileW; i += 32 * kFwProdWarps) {
-        const int rho = i / kTileW, sx = i - rho * kTileW;
-        const int gy = y0 - 2 + rho, gx = x0 - 2 + sx;
-        float v = 0.f;
-        if (gy >= 0 && gy < g.H && gx >= 0 && gx < g.W) v = __ldg(src + (size_t)gy * g.W + gx);
-        const __nv_bfloat16 hi = __float2bfloat16_rn(v);
-        const __nv_bfloat16 lo = __float2bfloat16_rn(v - __bfloat162float(hi));
+      const uint8_t* raw = s_raw + (n & 1) * kFwRawBytes;
+      for (int i = pt; i < kPieces; i += 32 * kFwProdWarps) {
+        const int rho = i / (kFwTileW / 2), sx = 2 * (i - rho * (kFwTileW / 2));
+        const float2 v = *reinterpret_cast<const float2*>(raw + (size_t)i * 8);
+        const uint32_t hi = pack_bf16x2(v.x, v.y);
+        const uint32_t lo = pack_bf16x2(v.x - bf16_lo(hi), v.y - bf16_hi(hi));
         const int off = (sx >> 3) * kFwPlaneBytes + rho * 16 + (sx & 7) * 2;
-        *reinterpret_cast<__nv_bfloat16*>(xh + off) = hi;
-        *reinterpret_cast<__nv_bfloat16*>(xl + off) = lo;
+        *reinterpret_cast<uint32_t*>(xh + off) = hi;
+        *reinterpret_cast<uint32_t*>(xl + off) = lo;
       }
       fence_proxy_async_smem();
       __syncwarp();
