@@ -243,6 +243,49 @@ allreduce_nvls_f32_kernel(Peers P, Peers Wp, size_t n4, float scale, float lr, u
   sys_barrier(P, epoch + 1);         // all multicast stores have landed everywhere
 }
 
+// "Exclusive" variant for the overlapped DDP bucket: few, fat CTAs (1024 threads, 8 x 16 B in flight per
+// thread) that request kExclusiveSmem bytes of dynamic shared memory they never touch, so no persistent
+// tensor-core CTA (all need > 67 KB) can share their SM.  See b200_set_reserved_sms (common.cu).
+constexpr int kExclusiveSmem = 160 * 1024;
+__global__ void __launch_bounds__(1024, 1)
+allreduce_nvls_f32_excl_kernel(Peers P, Peers Wp, size_t n4, float scale, float lr, uint32_t epoch) {
+  const int r = P.rank, n = P.world;
+  const size_t per = (n4 + n - 1) / n;
+  const size_t lo = per * r, hi = min(n4, lo + per);
+  const bool fused = Wp.ptr[0] != nullptr;
+  const float4* src = reinterpret_cast<const float4*>(P.mc);
+  float4* dst = reinterpret_cast<float4*>(fused ? Wp.mc : P.mc);
+  const float4* wl = reinterpret_cast<const float4*>(Wp.ptr[r]);
+  sys_barrier(P, epoch);
+  constexpr int U = 8;
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  size_t i = lo + (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  for (; i + (U - 1) * stride < hi; i += U * stride) {
+    float4 v[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) v[u] = mc_ld_reduce_f32(src + i + u * stride);
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      float4 g = make_float4(v[u].x * scale, v[u].y * scale, v[u].z * scale, v[u].w * scale);
+      if (fused) {
+        const float4 w = wl[i + u * stride];
+        g = make_float4(fmaf(-lr, g.x, w.x), fmaf(-lr, g.y, w.y), fmaf(-lr, g.z, w.z), fmaf(-lr, g.w, w.w));
+      }
+      mc_st_f32(dst + i + u * stride, g);
+    }
+  }
+  for (; i < hi; i += stride) {
+    const float4 v = mc_ld_reduce_f32(src + i);
+    float4 g = make_float4(v.x * scale, v.y * scale, v.z * scale, v.w * scale);
+    if (fused) {
+      const float4 w = wl[i];
+      g = make_float4(fmaf(-lr, g.x, w.x), fmaf(-lr, g.y, w.y), fmaf(-lr, g.z, w.z), fmaf(-lr, g.w, w.w));
+    }
+    mc_st_f32(dst + i, g);
+  }
+  sys_barrier(P, epoch + 1);
+}
+
 // bf16 buffer (8 elements per 16 B), fp32 accumulation in the switch; scale applied here.
 __global__ void __launch_bounds__(512)
 allreduce_nvls_bf16_kernel(Peers P, size_t n16, float scale, uint32_t epoch) {
@@ -345,7 +388,7 @@ B200_API int b200_ar_oneshot_f32x4(void* const* ptrs, void* const* flags, int ra
 }
 
 // In-place fp32 SUM over the symmetric buffer (n floats, n % 4 == 0).  algo: 1 = two-shot P2P,
-// 2 = two-shot NVLS (needs mc).  wptrs/wmc != null fuses SGD: W -= lr * (scale * sum g).
+// 2 = two-shot NVLS (needs mc), 3 = NVLS with SM-exclusive fat CTAs (DDP overlap).  wptrs/wmc != null fuses SGD: W -= lr * (scale * sum g).
 B200_API int b200_ar_large_f32(void* const* ptrs, void* mc, void* const* flags, void* const* wptrs, void* wmc,
                                int rank, int world, size_t n, float scale, float lr, int algo, int blocks,
                                uint32_t epoch, void* stream) {
@@ -354,7 +397,13 @@ B200_API int b200_ar_large_f32(void* const* ptrs, void* mc, void* const* flags, 
   Peers P = make_peers(ptrs, flags, mc, rank, world);
   Peers Wp = make_peers(wptrs, nullptr, wmc, rank, world);
   cudaStream_t s = (cudaStream_t)stream;
-  if (algo == 2) {
+  if (algo == 3) {
+    B200_CHECK(mc != nullptr && (!wptrs || wmc), "allreduce: NVLS requested but no multicast mapping");
+    static cudaError_t attr_err = cudaFuncSetAttribute(allreduce_nvls_f32_excl_kernel,
+                                                       cudaFuncAttributeMaxDynamicSharedMemorySize, kExclusiveSmem);
+    B200_CUDA(attr_err);
+    allreduce_nvls_f32_excl_kernel<<<blocks, 1024, kExclusiveSmem, s>>>(P, Wp, n / 4, scale, lr, epoch);
+  } else if (algo == 2) {
     B200_CHECK(mc != nullptr && (!wptrs || wmc), "allreduce: NVLS requested but no multicast mapping");
     allreduce_nvls_f32_kernel<4><<<blocks, 512, 0, s>>>(P, Wp, n / 4, scale, lr, epoch);
   } else {

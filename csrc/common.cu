@@ -22,6 +22,22 @@ int b200_num_sms() {
 
 B200_API int b200_sm_count() { return b200_num_sms(); }
 
+// SM partition for data-parallel runs: the bucket all-reduce kernel claims `n` SMs exclusively (it asks
+// for more shared memory than can co-reside with a persistent tensor-core CTA), and the persistent
+// tcgen05 kernels size their grids to the remaining SMs instead of having a few of their statically
+// scheduled CTAs start late behind the collective.
+static int g_reserved_sms = 0;
+B200_API int b200_set_reserved_sms(int n) {
+  if (n < 0 || n > 64) return b200_fail(-2, "reserved SM count must be in [0, 64]");
+  g_reserved_sms = n;
+  return 0;
+}
+B200_API int b200_get_reserved_sms() { return g_reserved_sms; }
+int b200_compute_sms() {
+  const int n = b200_num_sms() - g_reserved_sms;
+  return n > 1 ? n : 1;
+}
+
 // Writes > L2-size bytes so the next timed kernel starts from a cold L2
 // (B200_PROFILING.md timing hygiene).
 __global__ void l2_flush_kernel(float4* buf, size_t n4, float v) {

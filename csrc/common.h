@@ -30,7 +30,8 @@ inline int b200_fail(int code, const char* fmt, ...) {
   } while (0)
 #define B200_LAUNCH_CHECK() B200_CUDA(cudaGetLastError())
 
-int b200_num_sms();  // SM count of the current device (cached per device)
+int b200_num_sms();      // SM count of the current device (cached per device)
+int b200_compute_sms();  // b200_num_sms() minus the SMs reserved for an overlapped collective (b200_set_reserved_sms)
 
 // cross-file C-ABI helpers
 extern "C" int b200_reduce_partials(const void* partials, int nparts, int len, void* out, float scale, void* stream);

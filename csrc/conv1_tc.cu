@@ -58,7 +58,7 @@ struct WgGeom {
   int nstrips, ngroups, nitems;
 };
 
-__global__ void __maxnreg__(160)     // 288 threads x 160 regs = 46 K: leaves room for a comm CTA on the SM
+__global__ void __launch_bounds__(kWgThreads, 1)
 conv1_wgrad_tc_kernel(const float* __restrict__ in, const __nv_bfloat16* __restrict__ x1,
                       const __nv_bfloat16* __restrict__ dp1, const float* __restrict__ bn,
                       const float* __restrict__ red, float* __restrict__ partials, WgGeom g) {
@@ -278,7 +278,7 @@ B200_API int b200_conv1_wgrad_tc(const void* in_f32, const void* x1, const void*
   g.nstrips = (W + kXW - 1) / kXW;
   g.ngroups = (H + kRows - 1) / kRows;
   g.nitems = B * g.nstrips * g.ngroups;
-  const int nsm = b200_num_sms();
+  const int nsm = b200_compute_sms();
   const int grid = g.nitems < nsm ? g.nitems : nsm;
   conv1_wgrad_tc_kernel<<<grid, kWgThreads, kSmemBytes, s>>>((const float*)in_f32, (const __nv_bfloat16*)x1,
                                                              (const __nv_bfloat16*)dp1, (const float*)bn,
@@ -327,7 +327,7 @@ struct FwGeom {
   int nys, nxs, nitems;
 };
 
-__global__ void __maxnreg__(112)     // 416 threads x 112 regs = 46.6 K: leaves room for a comm CTA on the SM
+__global__ void __launch_bounds__(kFwThreads, 1)
 conv1_fwd_tc_kernel(const float* __restrict__ in, const float* __restrict__ w1, const float* __restrict__ b1,
                     __nv_bfloat16* __restrict__ x1, float* __restrict__ partials, FwGeom g) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -458,9 +458,9 @@ conv1_fwd_tc_kernel(const float* __restrict__ in, const float* __restrict__ w1, 
     const int ew = warp - (1 + kFwProdWarps);           // 0..7
     const int quarter = warp & 3, grp = ew >> 2;
     const int m = quarter * 32 + lane;
-    float ssum[16], ssq[16];
+    float ssum[16], ssq[16], bias[16];
 #pragma unroll
-    for (int c = 0; c < 16; ++c) { ssum[c] = 0.f; ssq[c] = 0.f; }
+    for (int c = 0; c < 16; ++c) { ssum[c] = 0.f; ssq[c] = 0.f; bias[c] = s_bias[c]; }
     uint32_t q = 0;
     for (int item = blockIdx.x; item < g.nitems; item += gridDim.x) {
       const int xs = item % g.nxs;
@@ -475,19 +475,27 @@ conv1_fwd_tc_kernel(const float* __restrict__ in, const float* __restrict__ w1, 
         tc_fence_after();
         const int xb = xs * kFwSegPx + j * 8;
         __nv_bfloat16* orow = x1 + (((size_t)b * g.H + (row_ok ? y : 0)) * g.W + xb) * 16;
+        // 4 chunks of 2 pixels x 16 channels; the tcgen05.ld of chunk k+1 is in flight while chunk k is
+        // converted (tcgen05.wait::ld waits for ALL outstanding loads, so it comes after the math)
+        const uint32_t tbase = tmem_base + ((uint32_t)(quarter * 32) << 16) + ts * 128;
+        uint32_t va[32], vb[32];
+        tmem_ld16(tbase, *reinterpret_cast<uint32_t(*)[16]>(&va[0]));
+        tmem_ld16(tbase + 16, *reinterpret_cast<uint32_t(*)[16]>(&va[16]));
+        tmem_ld_wait();
 #pragma unroll
-        for (int c0 = 0; c0 < 128; c0 += 32) {              // 2 pixels x 16 channels per chunk
-          uint32_t v[32];
-          const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + ts * 128 + c0;
-          tmem_ld16(taddr, *reinterpret_cast<uint32_t(*)[16]>(&v[0]));
-          tmem_ld16(taddr + 16, *reinterpret_cast<uint32_t(*)[16]>(&v[16]));
-          tmem_ld_wait();
-          if (c0 == 96) { tc_fence_before(); mbar_arrive(&tempty[ts]); }
+        for (int k = 0; k < 4; ++k) {
+          uint32_t* v = (k & 1) ? vb : va;
+          uint32_t* vn = (k & 1) ? va : vb;
+          if (k < 3) {
+            tmem_ld16(tbase + (k + 1) * 32, *reinterpret_cast<uint32_t(*)[16]>(&vn[0]));
+            tmem_ld16(tbase + (k + 1) * 32 + 16, *reinterpret_cast<uint32_t(*)[16]>(&vn[16]));
+          }
+          const int c0 = k * 32;
           const bool ok = row_ok && (xb + (c0 >> 4)) < g.W;     // W % 2 == 0: both pixels or neither
           uint32_t pk[16];
 #pragma unroll
           for (int e = 0; e < 32; e += 2) {
-            pk[e >> 1] = pack_bf16x2(__uint_as_float(v[e]) + s_bias[e & 15], __uint_as_float(v[e + 1]) + s_bias[(e + 1) & 15]);
+            pk[e >> 1] = pack_bf16x2(__uint_as_float(v[e]) + bias[e & 15], __uint_as_float(v[e + 1]) + bias[(e + 1) & 15]);
             // statistics of the ROUNDED values: BN backward relies on mean/var being exactly those of the
             // stored tensor (sum dx = 0, sum dx*xhat = 0); unrounded stats leave a coherent residual
             const float f0 = bf16_lo(pk[e >> 1]), f1 = bf16_hi(pk[e >> 1]);
@@ -503,6 +511,8 @@ conv1_fwd_tc_kernel(const float* __restrict__ in, const float* __restrict__ w1, 
             o[2] = make_uint4(pk[8], pk[9], pk[10], pk[11]);
             o[3] = make_uint4(pk[12], pk[13], pk[14], pk[15]);
           }
+          if (k < 3) tmem_ld_wait();
+          else { tc_fence_before(); mbar_arrive(&tempty[ts]); }
         }
       }
     }
@@ -542,7 +552,7 @@ B200_API int b200_conv1_fwd_tc(const void* in_f32, const void* w1, const void* b
   g.nys = (H + kFwRows - 1) / kFwRows;
   g.nxs = (W + kFwSegPx - 1) / kFwSegPx;
   g.nitems = B * g.nys * g.nxs;
-  const int nsm = b200_num_sms();
+  const int nsm = b200_compute_sms();
   const int grid = g.nitems < nsm ? g.nitems : nsm;
   conv1_fwd_tc_kernel<<<grid, kFwThreads, kFwSmemBytes, s>>>((const float*)in_f32, (const float*)w1, (const float*)b1,
                                                              (__nv_bfloat16*)x1_bf16, (float*)partials, g);

@@ -959,7 +959,7 @@ int launch_conv_rs(const void* act, const void* w, const void* bias, void* out, 
   CUtensorMap tm;
   int rc = make_act_tmap(&tm, act, B, H, W, CIN, kPW);
   if (rc) return rc;
-  const int nsm = b200_num_sms();
+  const int nsm = b200_compute_sms();
   ConvGeom g = make_geom(B, H, W, nsm, 4);
   const int grid = g.nitems < nsm ? g.nitems : nsm;
   kern<<<grid, kThreads, Cfg::kSmemBytes, s>>>(tm, (const __nv_bfloat16*)act, (const float*)w, (const float*)bias,
@@ -987,7 +987,7 @@ int launch_conv(const void* act, const void* w, const void* bias, void* out, voi
   CUtensorMap tm;
   int rc = make_act_tmap(&tm, act, B, H, W, CIN, kPW);
   if (rc) return rc;
-  const int nsm = b200_num_sms();
+  const int nsm = b200_compute_sms();
   ConvGeom g = make_geom(B, H, W, nsm, 4);
   const int grid = g.nitems < nsm ? g.nitems : nsm;
   kern<<<grid, kThreads, Cfg::kSmemBytes, s>>>(tm, (const float*)w, (const float*)bias, (__nv_bfloat16*)out,
@@ -1041,7 +1041,7 @@ B200_API int b200_conv2_wgrad_tc(const void* p1_bf16, const void* dx2_bf16, void
   if (rc) return rc;
   rc = make_act_tmap(&tmb, dx2_bf16, B, H, W, 32, kBM);
   if (rc) return rc;
-  const int nsm = b200_num_sms();
+  const int nsm = b200_compute_sms();
   ConvGeom g = make_geom(B, H, W, nsm, 4);
   const int grid = g.nitems < nsm ? g.nitems : nsm;
   if (g_conv_tc_version == 3)

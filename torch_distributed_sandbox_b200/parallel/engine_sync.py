@@ -35,6 +35,7 @@ class EngineGradSync:
         self.blocks = int(os.environ.get("B200DP_AR_BLOCKS", "32"))     # CTAs of the overlapped bucket all-reduce (tuned at N=2)
         self._fc_event = None
         self._steps = 0
+        self.reserved_sms = int(os.environ.get("B200DP_RESERVED_SMS", "8"))    # SM partition (common.cu); 0 = share SMs
         self._debug_skip_fc = os.environ.get("B200DP_DEBUG_SKIP_FC_ALLREDUCE", "0") == "1"   # timing experiments only
         be = self.backend
         if self.world > 1 and getattr(be, "name", "") != "native":
@@ -50,6 +51,10 @@ class EngineGradSync:
                 sg = be.alloc_symmetric(engine.small_grad.numel(), torch.float32, multicast=False)
                 engine.rebind_storage(fcw=wsym, fcw_grad=grad, bn_flat=bn, small_grad=sg)
             self.comm_stream = be.comm_stream
+            if self.reserved_sms > 0 and be.multicast and (self.algo in (None, "nvls", "nvls_excl")):
+                from .. import _native
+                _native.check(_native.cuda().b200_set_reserved_sms(self.reserved_sms), "set_reserved_sms")
+                self.algo, self.blocks = "nvls_excl", self.reserved_sms
         if init_sync:
             self._sync_params()
 
@@ -65,6 +70,7 @@ class EngineGradSync:
         mc = bool(d.get("nvls_multicast"))
         algo = self.algo or ("nvls" if mc else "p2p")
         d.update({"fc_bucket_algo": f"two-shot-{algo}", "fused_sgd_in_allreduce": self.fuse_sgd,
+                  "sm_partition": self.reserved_sms if algo == "nvls_excl" else 0,
                   "small_bucket_algo": "one-shot", "comm_blocks": self.blocks, "nccl_calls_on_grad_path": 0})
         return d
 

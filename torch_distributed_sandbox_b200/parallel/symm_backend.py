@@ -194,7 +194,7 @@ class SymmBackend:
         large_ok = t.dtype == torch.float32 and op == 0 and nbytes > ONESHOT_MAX_BYTES
         if large_ok and sym is not None and sym[1] % 16 == 0 and flat.numel() % 4 == 0:
             buf, off = sym
-            use_nvls = (algo or ("nvls" if buf.mc else "p2p")) == "nvls"
+            use_nvls = (algo or ("nvls" if buf.mc else "p2p")) in ("nvls", "nvls_excl")
             w_arr, w_mc, lr = None, None, 0.0
             if sgd is not None:
                 wsym = self.lookup(sgd[0])
@@ -204,7 +204,8 @@ class SymmBackend:
                 use_nvls = use_nvls and bool(w_mc)
             rc = lib.b200_ar_large_f32(buf.ptr_array(off), (buf.mc + off) if buf.mc else 0, self._flag_arr[channel],
                                        w_arr, w_mc, self.rank, self.size, flat.numel(), scale, lr,
-                                       2 if use_nvls else 1, blocks or 64, self._next_epoch(channel), self._stream())
+                                       (3 if algo == "nvls_excl" else 2) if use_nvls else 1, blocks or 64,
+                                       self._next_epoch(channel), self._stream())
             _native.check(rc, "all_reduce(large)")
         else:
             if sgd is not None:
