@@ -425,6 +425,9 @@ conv5x5_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tm_act, const __grid
 // consecutive TMEM column blocks of a 16-deep ring, so that single MMA accumulates straight
 // into five different output rows.  5 (x CIN/16) fat MMAs per row instead of 25 thin ones,
 // each input row is needed only while its own MMAs run, and the epilogue is unchanged.
+constexpr int kRsEpiWarps = 8;                       // two groups of 4 (one per TMEM lane quarter), alternating rows
+constexpr int kRsThreads = 32 * (2 + kRsEpiWarps);  // warp0 feed, warp1 MMA issue, warps 2-9 epilogue
+
 template <int CIN, int COUT>
 struct RsCfg {
   static constexpr int kPlanes = CIN / 8;
@@ -437,7 +440,7 @@ struct RsCfg {
   static constexpr int kWBytes = 5 * kKSteps * kWStepBytes;  // == 25*CIN*COUT*2
   static constexpr int kTStages = 16;
   static constexpr int kTmemCols = kTStages * COUT;          // 512 (COUT=32) / 256 (COUT=16)
-  static constexpr int kSmemBytes = kWBytes + kSlots * kSlotBytes + 2048 + 128;
+  static constexpr int kSmemBytes = kWBytes + kSlots * kSlotBytes + 4096 + 128;
   static_assert(kWBytes % 128 == 0 && kSlotBytes % 128 == 0, "alignment");
   static_assert(kTmemCols <= 512 && (kTmemCols & (kTmemCols - 1)) == 0, "TMEM columns");
 };
@@ -464,12 +467,19 @@ __device__ __forceinline__ void cp_row(uint8_t* dst, const __nv_bfloat16* __rest
   }
 }
 
-template <int CIN, int COUT, bool TRANSPOSED, bool STATS, bool LDGSTS>
-__global__ void __launch_bounds__(kThreads, 1)
+// STATS: 0 = none, 1 = BatchNorm forward statistics of the output (sum, sum of squares; conv2 forward),
+// 2 = BatchNorm BACKWARD reductions of the layer below (dgrad): the output IS dp1, the gradient of the
+//     pooled layer-1 activation, so with `pooled` = p1 (read before it is overwritten in place) and
+//     bnprev = [scale|shift|mean|rstd] of BN1:  dy = dp1 where p1 > 0,
+//     partials = [sum(dy) | sum(dy * xhat)],  xhat = ((p1 - shift)/scale - mean) * rstd.
+//     This replaces a separate pass over the 1.44 GB conv1 output.
+template <int CIN, int COUT, bool TRANSPOSED, int STATS, bool LDGSTS>
+__global__ void __launch_bounds__(kRsThreads, 1)
 conv5x5_rs_kernel(const __grid_constant__ CUtensorMap tm_act, const __nv_bfloat16* __restrict__ act,
                   const float* __restrict__ w,
                   const float* __restrict__ bias, __nv_bfloat16* __restrict__ out,
-                  float* __restrict__ partials, ConvGeom g) {
+                  float* __restrict__ partials, const __nv_bfloat16* pooled, const float* __restrict__ bnprev,
+                  ConvGeom g) {
   using Cfg = RsCfg<CIN, COUT>;
   constexpr int RT = Cfg::kTStages;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -483,11 +493,19 @@ conv5x5_rs_kernel(const __grid_constant__ CUtensorMap tm_act, const __nv_bfloat1
   uint64_t* tempty = tfull + RT;               // [RT]
   uint32_t* s_tmem = reinterpret_cast<uint32_t*>(tempty + RT);
   float* s_bias = reinterpret_cast<float*>(s_tmem + 4);
-  float* s_stat = s_bias + COUT;               // [4][2*COUT]
+  float* s_stat = s_bias + COUT;               // [8 warps][2*COUT]
+  float* s_bnp = s_stat + 2 * kRsEpiWarps * COUT;            // [4][COUT]: (shift, 1/scale, mean, rstd) of the layer below
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (STATS == 2 && threadIdx.x < COUT) {
+    const float sc = bnprev[threadIdx.x];
+    s_bnp[threadIdx.x] = bnprev[COUT + threadIdx.x];
+    s_bnp[COUT + threadIdx.x] = sc != 0.f ? 1.f / sc : 0.f;
+    s_bnp[2 * COUT + threadIdx.x] = bnprev[2 * COUT + threadIdx.x];
+    s_bnp[3 * COUT + threadIdx.x] = bnprev[3 * COUT + threadIdx.x];
+  }
 
   // weights: byte(dx, kk, c, n=(jj,co), e) = ((((dx*KSTEPS + kk)*2 + c)*kNB + n)*8 + e)*2, dy = 4 - jj
-  for (int i = threadIdx.x; i < kTaps * CIN * COUT; i += kThreads) {
+  for (int i = threadIdx.x; i < kTaps * CIN * COUT; i += kRsThreads) {
     const int e = i & 7;
     int r = i >> 3;
     const int n = r % Cfg::kNB; r /= Cfg::kNB;
@@ -626,12 +644,22 @@ conv5x5_rs_kernel(const __grid_constant__ CUtensorMap tm_act, const __nv_bfloat1
       qbase += rows;
     }
   } else {
-    const int quarter = warp & 3;
+    const int quarter = warp & 3, ew = warp - 2, grp = ew >> 2;      // group g drains rows with (q & 1) == g
     const int m = quarter * 32 + lane;
     float ssum[STATS ? COUT : 1], ssq[STATS ? COUT : 1];
     if (STATS) {
 #pragma unroll
       for (int c = 0; c < COUT; ++c) { ssum[c] = 0.f; ssq[c] = 0.f; }
+    }
+    // STATS == 2: xhat = ((y - shift)/scale - mean) * rstd = y * kA + kB, constants in registers
+    float kA[STATS == 2 ? COUT : 1], kB[STATS == 2 ? COUT : 1];
+    if (STATS == 2) {
+#pragma unroll
+      for (int c = 0; c < COUT; ++c) {
+        const float inv = s_bnp[COUT + c], rs = s_bnp[3 * COUT + c];
+        kA[c] = inv * rs;
+        kB[c] = -(s_bnp[c] * inv + s_bnp[2 * COUT + c]) * rs;
+      }
     }
     uint32_t q = 0;
     for (int item = blockIdx.x; item < g.nitems; item += gridDim.x) {
@@ -643,7 +671,16 @@ conv5x5_rs_kernel(const __grid_constant__ CUtensorMap tm_act, const __nv_bfloat1
       const int x = strip * kBM + m;
       const bool valid = x < g.W;
       for (int j = 0; j < rows; ++j, ++q) {
+        if ((int)(q & 1u) != grp) continue;
         const uint32_t stage = q % RT, use = q / RT;
+        // STATS == 2: fetch this pixel's pooled activation now, so the load latency overlaps the wait for
+        // the accumulator (it is read here, before the gradient written below overwrites it in place)
+        uint4 pvv[STATS == 2 ? COUT / 8 : 1];
+        if (STATS == 2 && valid) {
+          const uint4* pp = reinterpret_cast<const uint4*>(pooled + (((size_t)b * g.H + (y0 + j)) * g.W + x) * COUT);
+#pragma unroll
+          for (int i = 0; i < COUT / 8; ++i) pvv[i] = pp[i];
+        }
         mbar_wait(&tfull[stage], use & 1);
         tc_fence_after();
         const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + stage * COUT;
@@ -657,7 +694,7 @@ conv5x5_rs_kernel(const __grid_constant__ CUtensorMap tm_act, const __nv_bfloat1
 #pragma unroll
         for (int c = 0; c < COUT; c += 2) {
           pk[c / 2] = pack_bf16x2(__uint_as_float(v[c]) + s_bias[c], __uint_as_float(v[c + 1]) + s_bias[c + 1]);
-          if (STATS && valid) {
+          if (STATS == 1 && valid) {
             const float r0 = bf16_lo(pk[c / 2]), r1 = bf16_hi(pk[c / 2]);
             ssum[c] += r0; ssq[c] = fmaf(r0, r0, ssq[c]);
             ssum[c + 1] += r1; ssq[c + 1] = fmaf(r1, r1, ssq[c + 1]);
@@ -665,6 +702,17 @@ conv5x5_rs_kernel(const __grid_constant__ CUtensorMap tm_act, const __nv_bfloat1
         }
         if (valid) {
           uint4* o = reinterpret_cast<uint4*>(out + (((size_t)b * g.H + (y0 + j)) * g.W + x) * COUT);
+          if (STATS == 2) {
+#pragma unroll
+            for (int c = 0; c < COUT; ++c) {
+              const uint32_t pw = (&pvv[c / 8].x)[(c & 7) >> 1];
+              const float y = (c & 1) ? bf16_hi(pw) : bf16_lo(pw);
+              const float gq = (c & 1) ? bf16_hi(pk[c / 2]) : bf16_lo(pk[c / 2]);
+              const float gg = y > 0.f ? gq : 0.f;
+              ssum[c] += gg;
+              ssq[c] = fmaf(gg, fmaf(y, kA[c], kB[c]), ssq[c]);
+            }
+          }
 #pragma unroll
           for (int i = 0; i < COUT / 8; ++i) o[i] = make_uint4(pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
         }
@@ -674,7 +722,7 @@ conv5x5_rs_kernel(const __grid_constant__ CUtensorMap tm_act, const __nv_bfloat1
 #pragma unroll
       for (int c = 0; c < COUT; ++c) {
         const float a = warp_sum(ssum[c]), s2 = warp_sum(ssq[c]);
-        if (lane == 0) { s_stat[quarter * 2 * COUT + c] = a; s_stat[quarter * 2 * COUT + COUT + c] = s2; }
+        if (lane == 0) { s_stat[ew * 2 * COUT + c] = a; s_stat[ew * 2 * COUT + COUT + c] = s2; }
       }
     }
   }
@@ -684,7 +732,7 @@ conv5x5_rs_kernel(const __grid_constant__ CUtensorMap tm_act, const __nv_bfloat1
   if (STATS && threadIdx.x < 2 * COUT) {
     float a = 0.f;
 #pragma unroll
-    for (int w4 = 0; w4 < 4; ++w4) a += s_stat[w4 * 2 * COUT + threadIdx.x];
+    for (int w4 = 0; w4 < kRsEpiWarps; ++w4) a += s_stat[w4 * 2 * COUT + threadIdx.x];
     partials[(size_t)blockIdx.x * 2 * COUT + threadIdx.x] = a;
   }
   if (warp == 1) { __syncwarp(); tmem_dealloc<Cfg::kTmemCols>(tmem_base); }
@@ -945,9 +993,9 @@ ConvGeom make_geom(int B, int H, int W, int nsm, int halo_rows) {
 // 1 = tap-stationary + TMA, 2 = row-stationary + TMA, 3 = row-stationary + cp.async feed (default)
 int g_conv_tc_version = 3;
 
-template <int CIN, int COUT, bool TRANSPOSED, bool STATS, bool LDGSTS>
+template <int CIN, int COUT, bool TRANSPOSED, int STATS, bool LDGSTS>
 int launch_conv_rs(const void* act, const void* w, const void* bias, void* out, void* partials, int B, int H, int W,
-                   cudaStream_t s, int* grid_out) {
+                   cudaStream_t s, int* grid_out, const void* pooled = nullptr, const void* bnprev = nullptr) {
   using Cfg = RsCfg<CIN, COUT>;
   auto kern = conv5x5_rs_kernel<CIN, COUT, TRANSPOSED, STATS, LDGSTS>;
   static std::once_flag once;
@@ -962,8 +1010,9 @@ int launch_conv_rs(const void* act, const void* w, const void* bias, void* out, 
   const int nsm = b200_compute_sms();
   ConvGeom g = make_geom(B, H, W, nsm, 4);
   const int grid = g.nitems < nsm ? g.nitems : nsm;
-  kern<<<grid, kThreads, Cfg::kSmemBytes, s>>>(tm, (const __nv_bfloat16*)act, (const float*)w, (const float*)bias,
-                                                (__nv_bfloat16*)out, (float*)partials, g);
+  kern<<<grid, kRsThreads, Cfg::kSmemBytes, s>>>(tm, (const __nv_bfloat16*)act, (const float*)w, (const float*)bias,
+                                                (__nv_bfloat16*)out, (float*)partials, (const __nv_bfloat16*)pooled,
+                                                (const float*)bnprev, g);
   B200_LAUNCH_CHECK();
   if (grid_out) *grid_out = grid;
   return 0;
@@ -973,9 +1022,9 @@ template <int CIN, int COUT, bool TRANSPOSED, bool STATS>
 int launch_conv(const void* act, const void* w, const void* bias, void* out, void* partials, int B, int H, int W,
                 cudaStream_t s, int* grid_out) {
   if (g_conv_tc_version == 3)
-    return launch_conv_rs<CIN, COUT, TRANSPOSED, STATS, true>(act, w, bias, out, partials, B, H, W, s, grid_out);
+    return launch_conv_rs<CIN, COUT, TRANSPOSED, STATS ? 1 : 0, true>(act, w, bias, out, partials, B, H, W, s, grid_out);
   if (g_conv_tc_version == 2)
-    return launch_conv_rs<CIN, COUT, TRANSPOSED, STATS, false>(act, w, bias, out, partials, B, H, W, s, grid_out);
+    return launch_conv_rs<CIN, COUT, TRANSPOSED, STATS ? 1 : 0, false>(act, w, bias, out, partials, B, H, W, s, grid_out);
   using Cfg = ConvCfg<CIN, COUT>;
   auto kern = conv5x5_tc_kernel<CIN, COUT, TRANSPOSED, STATS>;
   static std::once_flag once;
@@ -1020,6 +1069,19 @@ B200_API int b200_conv2_dgrad_tc(const void* dx2_bf16, const void* w2, void* dp1
                                  void* stream) {
   return launch_conv<32, 16, true, false>(dx2_bf16, w2, nullptr, dp1_bf16, nullptr, B, H, W, (cudaStream_t)stream,
                                           nullptr);
+}
+
+// dgrad with the BatchNorm-1 backward reductions fused into its epilogue (row-stationary kernel only).
+// pooled = p1 (may alias dp1_bf16: each pixel is read before it is overwritten), bn1 = [scale|shift|mean|rstd],
+// partials: [b200_conv_tc_max_grid()][32] = per-CTA [sum(dy) | sum(dy*xhat)]; *nparts_out = rows written.
+B200_API int b200_conv2_dgrad_stats_tc(const void* dx2_bf16, const void* w2, const void* pooled, const void* bn1,
+                                       void* dp1_bf16, void* partials, int B, int H, int W, int* nparts_out,
+                                       void* stream) {
+  if (g_conv_tc_version == 2)
+    return launch_conv_rs<32, 16, true, 2, false>(dx2_bf16, w2, nullptr, dp1_bf16, partials, B, H, W,
+                                                  (cudaStream_t)stream, nparts_out, pooled, bn1);
+  return launch_conv_rs<32, 16, true, 2, true>(dx2_bf16, w2, nullptr, dp1_bf16, partials, B, H, W,
+                                               (cudaStream_t)stream, nparts_out, pooled, bn1);
 }
 
 // partials: [b200_conv_tc_max_grid()][32*16*25] floats of scratch; dw2: [32][16][5][5].

@@ -616,13 +616,32 @@ __global__ void ce_kernel(const float* __restrict__ logits, const long long* __r
 //   dp2[b][j] = sum_k dl[b][k] * W[k][j]            (bf16)
 // and, on the single-GPU path (lr != 0), applies SGD in place (W -= lr * dW)
 // so the 720 MB gradient is never written or re-read.
+// Optionally (bn2 != nullptr) it also produces the BatchNorm-2 backward reductions, which otherwise cost a
+// separate pass over the 1.44 GB conv2 output: with dy = dp2 where the pooled activation is positive,
+// sum(dy) and sum(dy * xhat) only involve the arg-max element of each pooling window, and its xhat follows
+// from the pooled value itself: y = p2 = scale*x + shift  =>  xhat = ((p2 - shift)/scale - mean) * rstd.
+// bn2 = [scale | shift | mean | rstd] (32 channels; channel = j % 32 in the HWC flatten order).
 template <int BT>
 __global__ void __launch_bounds__(256)
 fc_bwd_kernel(const float* __restrict__ dl, const __nv_bfloat16* __restrict__ p2, float* W,
-              float* dW, __nv_bfloat16* __restrict__ dp2, size_t F, float lr, int accumulate, float gscale) {
+              float* dW, __nv_bfloat16* __restrict__ dp2, size_t F, float lr, int accumulate, float gscale,
+              const float* __restrict__ bn2, float* __restrict__ bwd_partials) {
   __shared__ float s_dl[BT * kNC];
+  __shared__ float s_bp[8][64];
   if (threadIdx.x < BT * kNC) s_dl[threadIdx.x] = dl[threadIdx.x];
   __syncthreads();
+  // this thread always sees channels c0..c0+3 (the grid stride is a multiple of 8 quads = 32 channels)
+  const int c0 = 4 * (threadIdx.x & 7);
+  float k_shift[4], k_inv[4], k_mu[4], k_rs[4], a_dy[4], a_dyx[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    a_dy[i] = 0.f; a_dyx[i] = 0.f;
+    const float sc = bn2 ? bn2[c0 + i] : 1.f;
+    k_inv[i] = sc != 0.f ? 1.f / sc : 0.f;
+    k_shift[i] = bn2 ? bn2[32 + c0 + i] : 0.f;
+    k_mu[i] = bn2 ? bn2[64 + c0 + i] : 0.f;
+    k_rs[i] = bn2 ? bn2[96 + c0 + i] : 0.f;
+  }
   float d[BT][kNC];
 #pragma unroll
   for (int b = 0; b < BT; ++b)
@@ -651,8 +670,18 @@ fc_bwd_kernel(const float* __restrict__ dl, const __nv_bfloat16* __restrict__ p2
         s.x = fmaf(d[b][k], w[k].x, s.x); s.y = fmaf(d[b][k], w[k].y, s.y);
         s.z = fmaf(d[b][k], w[k].z, s.z); s.w = fmaf(d[b][k], w[k].w, s.w);
       }
-      *reinterpret_cast<uint2*>(dp2 + (size_t)b * F + 4 * j) =
-          make_uint2(pack_bf16x2(s.x, s.y), pack_bf16x2(s.z, s.w));
+      const uint2 o = make_uint2(pack_bf16x2(s.x, s.y), pack_bf16x2(s.z, s.w));
+      *reinterpret_cast<uint2*>(dp2 + (size_t)b * F + 4 * j) = o;
+      if (bn2) {     // BN2 backward reductions from the ROUNDED gradient (what the apply pass will read)
+        const float gq[4] = {bf16_lo(o.x), bf16_hi(o.x), bf16_lo(o.y), bf16_hi(o.y)};
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const float y = av[b][i];
+          const float gg = y > 0.f ? gq[i] : 0.f;
+          a_dy[i] += gg;
+          a_dyx[i] = fmaf(gg, ((y - k_shift[i]) * k_inv[i] - k_mu[i]) * k_rs[i], a_dyx[i]);
+        }
+      }
     }
     // dW (+ optional in-place SGD)
 #pragma unroll
@@ -674,6 +703,24 @@ fc_bwd_kernel(const float* __restrict__ dl, const __nv_bfloat16* __restrict__ p2
                                fmaf(-lr, g.z, w[k].z), fmaf(-lr, g.w, w[k].w));
         *reinterpret_cast<float4*>(W + (size_t)k * F + 4 * j) = o;
       }
+    }
+  }
+  if (bn2) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      float a = a_dy[i], q = a_dyx[i];
+      a += __shfl_xor_sync(0xffffffffu, a, 8);  q += __shfl_xor_sync(0xffffffffu, q, 8);
+      a += __shfl_xor_sync(0xffffffffu, a, 16); q += __shfl_xor_sync(0xffffffffu, q, 16);
+      if (lane < 8) { s_bp[warp][4 * lane + i] = a; s_bp[warp][32 + 4 * lane + i] = q; }
+    }
+    __syncthreads();
+    if (threadIdx.x < 64) {
+      float a = 0.f;
+#pragma unroll
+      for (int w8 = 0; w8 < 8; ++w8) a += s_bp[w8][threadIdx.x];
+      float* dst = bwd_partials + (size_t)blockIdx.x * 64 + threadIdx.x;
+      *dst = accumulate ? *dst + a : a;
     }
   }
 }
@@ -946,14 +993,16 @@ B200_API int b200_cross_entropy(const void* logits, const void* labels_i64, int 
   return 0;
 }
 
+// bn2 / bwd_partials (both nullable): fused BatchNorm-2 backward reductions, partials [b200_fc_grid()][64].
 B200_API int b200_fc_bwd(const void* dlogits, const void* p2, void* W, void* dW, void* dp2, int bt, size_t F,
-                         float lr, int accumulate, float gscale, void* stream) {
+                         float lr, int accumulate, float gscale, const void* bn2, void* bwd_partials, void* stream) {
   B200_CHECK(bt >= 1 && bt <= 8, "fc_bwd: batch chunk must be 1..8 (got %d)", bt);
   B200_CHECK(F % 4 == 0, "fc_bwd: F must be a multiple of 4");
+  B200_CHECK(!bn2 || (F % 32 == 0 && bwd_partials), "fc_bwd: fused BN statistics need F %% 32 == 0 and a partials buffer");
   cudaStream_t s = (cudaStream_t)stream;
   const int grid = b200_fc_grid();
   switch (bt) {
-#define B200_FCB(N) case N: fc_bwd_kernel<N><<<grid, 256, 0, s>>>((const float*)dlogits, (const __nv_bfloat16*)p2, (float*)W, (float*)dW, (__nv_bfloat16*)dp2, F, lr, accumulate, gscale); break;
+#define B200_FCB(N) case N: fc_bwd_kernel<N><<<grid, 256, 0, s>>>((const float*)dlogits, (const __nv_bfloat16*)p2, (float*)W, (float*)dW, (__nv_bfloat16*)dp2, F, lr, accumulate, gscale, (const float*)bn2, (float*)bwd_partials); break;
     B200_FCB(1) B200_FCB(2) B200_FCB(3) B200_FCB(4) B200_FCB(5) B200_FCB(6) B200_FCB(7) B200_FCB(8)
 #undef B200_FCB
   }

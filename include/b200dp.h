@@ -68,14 +68,26 @@ int b200_conv1_wgrad_noalloc(const void* in_f32, const void* x1_bf16, const void
                              const void* red, void* dw1, int B, int H, int W, float gscale, int nblocks,
                              void* stream);
 
+/* conv1 on tcgen05 (same contracts as b200_conv1_fwd / b200_conv1_wgrad; partial rows = grid, returned). */
+int b200_conv1_fwd_tc(const void* in_f32, const void* w1, const void* b1, void* x1_bf16, void* partials, int B, int H,
+                      int W, int* nparts_out, void* stream);
+int b200_conv1_wgrad_tc(const void* in_f32, const void* x1_bf16, const void* dp1_bf16, const void* bn, const void* red,
+                        void* partials, void* dw1, int B, int H, int W, float gscale, void* stream);
+
 /* ------------------------------------------- layer 2, tcgen05 (K6/K12) --- */
 /* ref: nn.Conv2d(16,32,5,1,2) forward / input gradient / weight gradient (cuDNN in the reference),
  * mnist_distributed.py:34,96.  partials (fwd): [b200_conv_tc_max_grid()][64];
  * partials (wgrad): [b200_conv_tc_max_grid()][12800] scratch. */
 int b200_conv_tc_max_grid(void);
+int b200_conv_tc_set_version(int v);   /* 1 tap-stationary+TMA, 2 row-stationary+TMA, 3 row-stationary+cp.async (default) */
+int b200_conv_tc_get_version(void);
+int b200_set_reserved_sms(int n);      /* SM partition for an overlapped collective (DDP); 0 = none */
+int b200_get_reserved_sms(void);
 int b200_conv2_fwd_tc(const void* p1_bf16, const void* w2, const void* b2, void* x2_bf16, void* partials, int B, int H,
                       int W, int* nparts_out, void* stream);
 int b200_conv2_dgrad_tc(const void* dx2_bf16, const void* w2, void* dp1_bf16, int B, int H, int W, void* stream);
+int b200_conv2_dgrad_stats_tc(const void* dx2_bf16, const void* w2, const void* pooled_p1, const void* bn1,
+                              void* dp1_bf16, void* partials, int B, int H, int W, int* nparts_out, void* stream);
 int b200_conv2_wgrad_tc(const void* p1_bf16, const void* dx2_bf16, void* partials, void* dw2, int B, int H, int W,
                         float gscale, void* stream);
 
@@ -88,7 +100,8 @@ int b200_fc_fwd(const void* p2_bf16, const void* W, const void* bias, void* part
 int b200_cross_entropy(const void* logits, const void* labels_i64, int B, void* loss, void* dlogits, void* dbias,
                        float gscale, void* stream);
 int b200_fc_bwd(const void* dlogits, const void* p2_bf16, void* W, void* dW_or_null, void* dp2_bf16, int bt, size_t F,
-                float lr_fused_sgd, int accumulate, float gscale, void* stream);
+                float lr_fused_sgd, int accumulate, float gscale, const void* bn2_or_null, void* bwd_partials_or_null,
+                void* stream);
 
 /* ------------------------------------------------------ optimizer (K14) --- */
 /* ref: torch.optim.SGD(model.parameters(), 1e-4).step(), mnist_distributed.py:65,97. */

@@ -146,7 +146,7 @@ def test_autograd_front_end_matches_train_step():
         # iteration 0 runs identical kernels on identical weights; afterwards torch's CE backward vs our
         # fused one differ in the last bit and bf16 rounding of activations amplifies that a little
         assert abs(float(loss1.detach()) - float(loss2)) < (1e-6 if it == 0 else 1e-3)
-    assert rel(m1.engine.fcw, m2.engine.fcw) < 1e-4 and rel(m1.engine.small, m2.engine.small) < 1e-4
+    assert rel(m1.engine.fcw, m2.engine.fcw) < 1e-3 and rel(m1.engine.small, m2.engine.small) < 1e-3
     assert list(m1.state_dict().keys())[0] == "layer1.0.weight"
 
 

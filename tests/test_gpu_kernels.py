@@ -283,3 +283,63 @@ def test_sgd_and_permute(ops):
     assert torch.equal(hwc, ref_hwc)
     ops.fcw_permute(hwc, back, C, Hd, Wd, False)
     assert torch.equal(back, src)
+
+
+def _bn_case(ops, C, B, H, W, seed):
+    g = torch.Generator(device=DEV).manual_seed(seed)
+    xb = nhwc_bf16(torch.randn(B, C, H, W, device=DEV, generator=g) * 1.3 + 0.2)
+    gamma = torch.rand(C, device=DEV, generator=g) + 0.5
+    gamma[1::4] *= -1
+    beta = torch.randn(C, device=DEV, generator=g) * 0.3
+    xf = xb.float()
+    mean, var = xf.mean((0, 1, 2)), xf.var((0, 1, 2), unbiased=False)
+    rstd = 1 / torch.sqrt(var + 1e-5)
+    bn = torch.stack([gamma * rstd, beta - mean * gamma * rstd, mean, rstd]).contiguous()
+    p = torch.empty(B, H // 2, W // 2, C, device=DEV, dtype=torch.bfloat16)
+    ops.bn_relu_pool(xb, bn, p)
+    return g, xb, bn, p
+
+
+def test_fc_bwd_fused_bn2_backward_stats(ops):
+    """sum(dy), sum(dy*xhat) produced inside fc_bwd from (dp2, p2) == the separate pass over x2."""
+    B, H, W, C = 5, 16, 24, 32
+    g, xb, bn, p2 = _bn_case(ops, C, B, H, W, 21)
+    Fd = C * (H // 2) * (W // 2)
+    Wt = torch.randn(10, Fd, device=DEV, generator=g) * 0.05
+    dl = torch.randn(B, 10, device=DEV, generator=g) * 0.1
+    dp2 = torch.empty_like(p2)
+    part = torch.zeros(ops.fc_grid(), 64, device=DEV)
+    ops.fc_bwd(dl, p2.view(B, Fd), Wt, None, dp2.view(B, Fd), bn2=bn, bwd_partials=part)
+    red_f, dg_f, db_f = torch.zeros(2, C, device=DEV), torch.zeros(C, device=DEV), torch.zeros(C, device=DEV)
+    ops.bn_bwd_finalize(part, ops.fc_grid(), C, B * H * W, red_f, dg_f, db_f)
+    grid = ops.pool_bn_bwd_grid()
+    part2 = torch.zeros(grid, 64, device=DEV)
+    red_r, dg_r, db_r = torch.zeros(2, C, device=DEV), torch.zeros(C, device=DEV), torch.zeros(C, device=DEV)
+    ops.pool_bn_bwd(xb, dp2, bn, red_r, part2, None, mode=0)
+    ops.bn_bwd_finalize(part2, grid, C, B * H * W, red_r, dg_r, db_r)
+    report("fused bn2 bwd dbeta", rel(db_f, db_r), 1e-5)
+    report("fused bn2 bwd dgamma", rel(dg_f, dg_r), 1e-2)
+
+
+@pytest.mark.parametrize("shape", [(2, 24, 200), (1, 50, 128)])
+def test_conv2_dgrad_fused_bn1_backward_stats(ops, shape):
+    """dgrad epilogue reductions (dp1 with p1 read-before-overwrite, in place) == the separate pass over x1."""
+    B, H, W = shape                                  # pooled-resolution geometry of layer 1
+    g, x1, bn1, p1 = _bn_case(ops, 16, B, 2 * H, 2 * W, 22)
+    dy = nhwc_bf16(torch.randn(B, 32, H, W, device=DEV, generator=g))
+    w = torch.randn(32, 16, 5, 5, device=DEV, generator=g) * 0.05
+    ref_dp1 = torch.empty(B, H, W, 16, device=DEV, dtype=torch.bfloat16)
+    ops.conv2_dgrad_tc(dy, w, ref_dp1)
+    part = torch.zeros(ops.conv_tc_max_grid(), 32, device=DEV)
+    inplace = p1.clone()
+    n = ops.conv2_dgrad_stats_tc(dy, w, inplace, bn1, inplace, part)     # p1 buffer becomes dp1
+    assert torch.equal(inplace, ref_dp1)
+    red_f, dg_f, db_f = torch.zeros(2, 16, device=DEV), torch.zeros(16, device=DEV), torch.zeros(16, device=DEV)
+    ops.bn_bwd_finalize(part, n, 16, B * 4 * H * W, red_f, dg_f, db_f)
+    grid = ops.pool_bn_bwd_grid()
+    part2 = torch.zeros(grid, 64, device=DEV)
+    red_r, dg_r, db_r = torch.zeros(2, 16, device=DEV), torch.zeros(16, device=DEV), torch.zeros(16, device=DEV)
+    ops.pool_bn_bwd(x1, ref_dp1, bn1, red_r, part2, None, mode=0)
+    ops.bn_bwd_finalize(part2, grid, 16, B * 4 * H * W, red_r, dg_r, db_r)
+    report(f"fused bn1 bwd dbeta {shape}", rel(db_f, db_r), 1e-5)
+    report(f"fused bn1 bwd dgamma {shape}", rel(dg_f, dg_r), 1e-2)

@@ -82,6 +82,8 @@ class FusedConvNet:
         self.lr = float(lr)
         self.conv_backend = conv_backend
         self.conv1_backend = os.environ.get("B200DP_CONV1", "tc")      # "tc" (tcgen05) | "ffma"
+        # BN-backward reductions fused into fc_bwd / the conv2-dgrad epilogue (0: separate passes over x2 / x1)
+        self.fuse_bwd_stats = os.environ.get("B200DP_FUSE_BWD_STATS", "1") == "1"
         self.fuse_fc_sgd = bool(fuse_fc_sgd)
         self.F = rn.feature_size((H, W))
         self.comm = None           # set by parallel.ddp for data-parallel runs
@@ -131,6 +133,7 @@ class FusedConvNet:
             self.part_wg1 = torch.empty(self.g_wg1, 400, **f32)
             self.part_wg2 = torch.empty(self.g_tc, 32 * 16 * 25, **f32)
             self.part_fc = torch.empty(self.g_fc, 80, **f32)
+            self.part_fcb = torch.empty(self.g_fc, 64, **f32)
             self.bn1 = torch.zeros(4, 16, **f32)
             self.bn2 = torch.zeros(4, 32, **f32)
             self.red1 = torch.zeros(2, 16, **f32)
@@ -318,29 +321,42 @@ class FusedConvNet:
             self.fcw_grad = torch.empty_like(self.fcw)
         p2 = self.p2.view(B, self.F)
         dp2 = self.dp2.view(B, self.F)
+        fuse_stats = self.fuse_bwd_stats and self.conv_backend == "tc"
         for b0 in range(0, B, 8):
             b1 = min(B, b0 + 8)
             ops.fc_bwd(self.dlogits[b0:b1], p2[b0:b1], self.fcw, None if fused else self.fcw_grad, dp2[b0:b1],
-                       lr=self.lr if fused else 0.0, accumulate=b0 > 0, gscale=gs)
+                       lr=self.lr if fused else 0.0, accumulate=b0 > 0, gscale=gs,
+                       bn2=self.bn2 if fuse_stats else None, bwd_partials=self.part_fcb if fuse_stats else None)
         self._fc_fused_done = fused
         if self.comm is not None:
             self.comm.fc_grad_ready(self)            # async all-reduce of the 720 MB bucket
-        # ---- layer 2
+        # ---- layer 2 (statistics pass fused into fc_bwd above unless disabled)
         H2, W2 = H // 2, W // 2
-        ops.pool_bn_bwd(self.x2, self.dp2, self.bn2, self.red2, self.part_bwd, None, mode=0)
-        ops.bn_bwd_finalize(self.part_bwd, self.g_pbb, 32, B * H2 * W2, self.red2, G["layer2.1.weight"],
-                            G["layer2.1.bias"], gs)
+        if fuse_stats:
+            ops.bn_bwd_finalize(self.part_fcb, self.g_fc, 32, B * H2 * W2, self.red2, G["layer2.1.weight"],
+                                G["layer2.1.bias"], gs)
+        else:
+            ops.pool_bn_bwd(self.x2, self.dp2, self.bn2, self.red2, self.part_bwd, None, mode=0)
+            ops.bn_bwd_finalize(self.part_bwd, self.g_pbb, 32, B * H2 * W2, self.red2, G["layer2.1.weight"],
+                                G["layer2.1.bias"], gs)
         ops.pool_bn_bwd(self.x2, self.dp2, self.bn2, self.red2, None, self.dx2, mode=1)
         if self.conv_backend == "tc":
             ops.conv2_wgrad_tc(self.p1, self.dx2, self.part_wg2, G["layer2.0.weight"], gs)
-            ops.conv2_dgrad_tc(self.dx2, P["layer2.0.weight"], self.dp1)
+            if fuse_stats:   # dgrad epilogue also reduces BN1's backward sums (reads p1 before dp1 overwrites it)
+                n1 = ops.conv2_dgrad_stats_tc(self.dx2, P["layer2.0.weight"], self.p1, self.bn1, self.dp1, self.part_bwd)
+            else:
+                ops.conv2_dgrad_tc(self.dx2, P["layer2.0.weight"], self.dp1)
         else:
             self._conv2_bwd_torch(gs)
         G["layer2.0.bias"].zero_()      # a bias feeding BatchNorm has an analytically zero gradient
         # ---- layer 1
-        ops.pool_bn_bwd(self.x1, self.dp1, self.bn1, self.red1, self.part_bwd, None, mode=0)
-        ops.bn_bwd_finalize(self.part_bwd, self.g_pbb, 16, B * H * W, self.red1, G["layer1.1.weight"],
-                            G["layer1.1.bias"], gs)
+        if fuse_stats:
+            ops.bn_bwd_finalize(self.part_bwd, n1, 16, B * H * W, self.red1, G["layer1.1.weight"],
+                                G["layer1.1.bias"], gs)
+        else:
+            ops.pool_bn_bwd(self.x1, self.dp1, self.bn1, self.red1, self.part_bwd, None, mode=0)
+            ops.bn_bwd_finalize(self.part_bwd, self.g_pbb, 16, B * H * W, self.red1, G["layer1.1.weight"],
+                                G["layer1.1.bias"], gs)
         wg1 = ops.conv1_wgrad_tc if self.conv1_backend == "tc" else ops.conv1_wgrad
         wg1(self.x, self.x1, self.dp1, self.bn1, self.red1, self.part_wg1, G["layer1.0.weight"], gs)
         G["layer1.0.bias"].zero_()

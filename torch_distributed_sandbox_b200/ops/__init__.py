@@ -39,7 +39,9 @@ def _lib():
     if not getattr(lib, "_b200_ops_bound", False):
         lib.b200_fc_fwd.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_size_t, c_void_p]
         lib.b200_fc_bwd.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_size_t,
-                                    c_float, c_int, c_float, c_void_p]
+                                    c_float, c_int, c_float, c_void_p, c_void_p, c_void_p]
+        lib.b200_conv2_dgrad_stats_tc.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int,
+                                                  c_int, c_int, ctypes.POINTER(c_int), c_void_p]
         lib.b200_sgd.argtypes = [c_void_p, c_void_p, c_size_t, c_float, c_void_p]
         lib.b200_bn_finalize.argtypes = [c_void_p, c_int, c_int, c_double, c_void_p, c_void_p, c_void_p, c_void_p,
                                          c_void_p, c_float, c_float, c_void_p, c_void_p]
@@ -214,12 +216,25 @@ def cross_entropy(logits, labels, loss, dlogits, dbias, gscale=1.0):
     _count(1)
 
 
-def fc_bwd(dlogits, p2_bf16, W, dW, dp2_bf16, lr=0.0, accumulate=False, gscale=1.0):
-    """K10(+K14): dW (optional), dp2 and optional in-place SGD on W, one streaming pass."""
+def fc_bwd(dlogits, p2_bf16, W, dW, dp2_bf16, lr=0.0, accumulate=False, gscale=1.0, bn2=None, bwd_partials=None):
+    """K10(+K14): dW (optional), dp2 and optional in-place SGD on W, one streaming pass.  With ``bn2`` the
+    BatchNorm-2 backward reductions are produced too (partials [fc_grid()][64]), replacing a pass over x2."""
     bt, F = p2_bf16.shape[0], p2_bf16[0].numel()
     _native.check(_lib().b200_fc_bwd(_p(dlogits), _p(p2_bf16), _p(W), _p(dW), _p(dp2_bf16), bt, F, lr,
-                                     1 if accumulate else 0, gscale, _stream()), "fc_bwd")
+                                     1 if accumulate else 0, gscale, _p(bn2), _p(bwd_partials), _stream()), "fc_bwd")
     _count(1)
+
+
+def conv2_dgrad_stats_tc(dx2_bf16, w2, pooled_p1, bn1, dp1_bf16, partials) -> int:
+    """K12a + K13-stats: conv2 data gradient with the BatchNorm-1 backward reductions fused into its epilogue
+    (``pooled_p1`` may alias ``dp1_bf16``).  Returns the number of partial rows ([rows][32])."""
+    B, H, W, _ = dx2_bf16.shape
+    n = c_int(0)
+    _native.check(_lib().b200_conv2_dgrad_stats_tc(_p(dx2_bf16), _p(w2), _p(pooled_p1), _p(bn1), _p(dp1_bf16),
+                                                   _p(partials), B, H, W, ctypes.byref(n), _stream()),
+                  "conv2_dgrad_stats_tc")
+    _count(1)
+    return n.value
 
 
 def sgd(p, g, lr):
