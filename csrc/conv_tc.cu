@@ -432,7 +432,7 @@ template <int CIN, int COUT>
 struct RsCfg {
   static constexpr int kPlanes = CIN / 8;
   static constexpr int kSlotBytes = kPlanes * kPlaneBytes;
-  static constexpr int kSlots = 10;          // >= kCpDepth + 2
+  static constexpr int kSlots = 16;          // >= kCpDepth + 2; power of two (cheap ring arithmetic)
   static constexpr int kKSteps = CIN / 16;
   static constexpr int kNB = 5 * COUT;                       // B rows per (dx, kk): n = jj*COUT + co
   static constexpr int kWChunkBytes = kNB * 16;              // one 8-channel k-chunk of all n rows
@@ -450,22 +450,45 @@ struct RsCfg {
 // LDGSTS=true has the whole producer warp issue 16-byte cp.async copies (zero-fill = padding),
 // 9-25 warp instructions per row, software-pipelined kCpDepth rows deep with wait_group,
 // then fence.proxy.async + one mbarrier arrive per row.
-constexpr int kCpDepth = 6;      // rows of cp.async in flight per producer warp (memory-level parallelism)
+constexpr int kCpDepth = 10;      // rows of cp.async in flight per producer warp (memory-level parallelism)
 
-template <int C>
-__device__ __forceinline__ void cp_row(uint8_t* dst, const __nv_bfloat16* __restrict__ src, int b, int y, int x_first,
-                                       int npix, int plane_bytes, int H, int W, int lane) {
-  // dst: [C/8 planes][npix][16 B];  src pixel (b, y, x_first + p), channels plane*8..+7
-  const bool row_ok = (y >= 0) && (y < H);
-  const __nv_bfloat16* row = src + ((size_t)b * H + (row_ok ? y : 0)) * (size_t)W * C;
-  const int total = (C / 8) * npix;
-  for (int i = lane; i < total; i += 32) {
-    const int pl = i / npix, p = i - pl * npix;
-    const int x = x_first + p;
-    const bool ok = row_ok && x >= 0 && x < W;
-    cp_async16(dst + pl * plane_bytes + p * 16, row + (size_t)(ok ? x : 0) * C + pl * 8, ok ? 16u : 0u);
+// Per-lane copy plan of one image-row segment: which 16-byte pieces this lane moves, where they land in
+// shared memory and where they come from relative to the row start.  It only depends on the strip (x_first),
+// so it is built once per work item; a row then costs ~4 instructions per piece instead of ~30 (the single
+// producer warp was issue-bound re-deriving plane / pixel / bounds for every piece of every row).
+template <int C, int NPIX>
+struct RowPlan {
+  static constexpr int kTotal = (C / 8) * NPIX;
+  static constexpr int kPer = (kTotal + 31) / 32;
+  uint32_t soff[kPer];     // byte offset inside the slot
+  uint32_t goff[kPer];     // element offset from the row start
+  uint32_t ok;             // bit k: piece k is inside the image horizontally
+  uint32_t use;            // bit k: piece k exists (lane + 32k < kTotal)
+  __device__ __forceinline__ void build(int x_first, int plane_bytes, int W, int lane) {
+    ok = 0; use = 0;
+#pragma unroll
+    for (int k = 0; k < kPer; ++k) {
+      const int i = lane + 32 * k;
+      const int pl = i / NPIX, p = i - pl * NPIX;
+      const int x = x_first + p;
+      const bool in = (i < kTotal) && x >= 0 && x < W;
+      soff[k] = (uint32_t)(pl * plane_bytes + p * 16);
+      goff[k] = in ? (uint32_t)(x * C + pl * 8) : 0u;
+      if (i < kTotal) use |= 1u << k;
+      if (in) ok |= 1u << k;
+    }
   }
-}
+  // dst: [C/8 planes][NPIX][16 B];  src pixel (b, y, x_first + p), channels plane*8..+7; zero-fill outside
+  __device__ __forceinline__ void copy(uint8_t* dst, const __nv_bfloat16* __restrict__ src, int b, int y, int H,
+                                       int W) const {
+    const bool row_ok = (y >= 0) && (y < H);
+    const __nv_bfloat16* row = src + ((size_t)b * H + (row_ok ? y : 0)) * (size_t)W * C;
+    const uint32_t okr = row_ok ? ok : 0u;
+#pragma unroll
+    for (int k = 0; k < kPer; ++k)
+      if ((use >> k) & 1u) cp_async16(dst + soff[k], row + goff[k], ((okr >> k) & 1u) ? 16u : 0u);
+  }
+};
 
 // STATS: 0 = none, 1 = BatchNorm forward statistics of the output (sum, sum of squares; conv2 forward),
 // 2 = BatchNorm BACKWARD reductions of the layer below (dgrad): the output IS dp1, the gradient of the
@@ -545,10 +568,12 @@ conv5x5_rs_kernel(const __grid_constant__ CUtensorMap tm_act, const __nv_bfloat1
         const int y0 = seg * g.rseg;
         const int rows = min(g.rseg, g.H - y0);
         const int x0 = strip * kBM;
+        RowPlan<CIN, kPW> plan;
+        plan.build(x0 - 2, kPlaneBytes, g.W, lane);
         for (int i = 0; i < rows + 4; ++i, ++gcount) {
           const uint32_t slot = gcount % Cfg::kSlots, use = gcount / Cfg::kSlots;
           mbar_wait(&empty[slot], (use & 1) ^ 1);
-          cp_row<CIN>(s_slots + slot * Cfg::kSlotBytes, act, b, y0 - 2 + i, x0 - 2, kPW, kPlaneBytes, g.H, g.W, lane);
+          plan.copy(s_slots + slot * Cfg::kSlotBytes, act, b, y0 - 2 + i, g.H, g.W);
           cp_async_commit();
           if (gcount >= (uint32_t)kCpDepth) {
             cp_async_wait<kCpDepth>();
@@ -615,6 +640,26 @@ conv5x5_rs_kernel(const __grid_constant__ CUtensorMap tm_act, const __nv_bfloat1
         const uint32_t s0 = (qbase + (uint32_t)(i - 4 + jj_lo)) % RT;
         const uint32_t a_lo_row = a_lo0 + ((slots_addr + slot * Cfg::kSlotBytes) >> 4);
         if (elect_one()) {
+          if (i >= 4 && starts_row && s0 + 5 <= (uint32_t)RT) {
+            // steady state (all five target rows live, no TMEM-ring wrap): straight-line issue.  The issuing
+            // warp is the one serial role of this kernel, so instructions per row are what bound it.
+            const uint32_t d0 = tmem_base + s0 * COUT;
+#pragma unroll
+            for (int dx = 0; dx < 5; ++dx) {
+#pragma unroll
+              for (int kk = 0; kk < Cfg::kKSteps; ++kk) {
+                const uint64_t a_desc = ((uint64_t)a_hi << 32) | (uint64_t)(a_lo_row + ((2 * kk) * kPlaneBytes >> 4) + dx);
+                const uint32_t b_lo = b_lo0 + (((dx * Cfg::kKSteps + kk) * Cfg::kWStepBytes) >> 4);
+                if (dx == 0 && kk == 0) {
+                  umma_bf16(d0, a_desc, ((uint64_t)b_hi << 32) | (uint64_t)b_lo, idesc0 | ((uint32_t)((4 * COUT) >> 3) << 17), 1u);
+                  umma_bf16(d0 + 4 * COUT, a_desc, ((uint64_t)b_hi << 32) | (uint64_t)(b_lo + 4 * COUT),
+                            idesc0 | ((uint32_t)(COUT >> 3) << 17), 0u);
+                } else {
+                  umma_bf16(d0, a_desc, ((uint64_t)b_hi << 32) | (uint64_t)b_lo, idesc0 | ((uint32_t)((5 * COUT) >> 3) << 17), 1u);
+                }
+              }
+            }
+          } else {
 #pragma unroll
           for (int dx = 0; dx < 5; ++dx) {
 #pragma unroll
@@ -635,6 +680,7 @@ conv5x5_rs_kernel(const __grid_constant__ CUtensorMap tm_act, const __nv_bfloat1
                 umma_bf16(tmem_base + ((qbase + (uint32_t)i) % RT) * COUT, a_desc,
                           ((uint64_t)b_hi << 32) | (uint64_t)(b_lo + 4 * COUT), idesc0 | ((uint32_t)(COUT >> 3) << 17), 0u);
             }
+          }
           }
           umma_commit(&empty[slot]);                                        // this input row is consumed
           if (i >= 4) umma_commit(&tfull[(qbase + (uint32_t)(i - 4)) % RT]);  // output row i-4 is complete
@@ -741,7 +787,7 @@ conv5x5_rs_kernel(const __grid_constant__ CUtensorMap tm_act, const __nv_bfloat1
 // wgrad, row-stationary: the act (p1) row is the stationary operand; the five dx2 rows it
 // pairs with (y = r-2 .. r+2) are five CONSECUTIVE slots of the dx2 ring, i.e. 20 consecutive
 // 8-channel planes, i.e. one MN-major B operand with N = 160.  D[pl][(dx,ci8)][(jj,co)], dy = 4-jj.
-constexpr int kWg2SlotsA = 8, kWg2SlotsB = 12;      // A >= kCpDepth + 1, B >= 5 + kCpDepth
+constexpr int kWg2SlotsA = 12, kWg2SlotsB = 16;      // A >= kCpDepth + 1, B >= 5 + kCpDepth
 constexpr int kWg2SmemBytes = kWg2SlotsA * kWgSlotABytes + kWg2SlotsB * kWgSlotBBytes + 1024 + 128;
 
 template <bool LDGSTS>
@@ -786,18 +832,22 @@ conv5x5_wgrad_rs_kernel(const __grid_constant__ CUtensorMap tm_act, const __grid
         const int r0 = seg * g.rseg;
         const int rows = min(g.rseg, g.H - r0);
         const int x0 = strip * kBM;
+        RowPlan<32, kBM> planB;
+        planB.build(x0, kWgPlaneBBytes, g.W, lane);
+        RowPlan<16, kPW> planA;
+        planA.build(x0 - 2, kPlaneBytes, g.W, lane);
         for (int i = 0; i < rows + 4; ++i, ++it) {
           {
             const uint32_t slot = gb % kWg2SlotsB, use = gb / kWg2SlotsB;
             mbar_wait(&emptyB[slot], (use & 1) ^ 1);
-            cp_row<32>(s_b + slot * kWgSlotBBytes, dxo, b, r0 - 2 + i, x0, kBM, kWgPlaneBBytes, g.H, g.W, lane);
+            planB.copy(s_b + slot * kWgSlotBBytes, dxo, b, r0 - 2 + i, g.H, g.W);
             ++gb;
           }
           has_a <<= 1;
           if (i >= 4) {
             const uint32_t slot = ga % kWg2SlotsA, use = ga / kWg2SlotsA;
             mbar_wait(&emptyA[slot], (use & 1) ^ 1);
-            cp_row<16>(s_a + slot * kWgSlotABytes, act, b, r0 + i - 4, x0 - 2, kPW, kPlaneBytes, g.H, g.W, lane);
+            planA.copy(s_a + slot * kWgSlotABytes, act, b, r0 + i - 4, g.H, g.W);
             ++ga;
             has_a |= 1u;
           }
