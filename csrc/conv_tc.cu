@@ -432,7 +432,7 @@ template <int CIN, int COUT>
 struct RsCfg {
   static constexpr int kPlanes = CIN / 8;
   static constexpr int kSlotBytes = kPlanes * kPlaneBytes;
-  static constexpr int kSlots = 16;          // >= kCpDepth + 2; power of two (cheap ring arithmetic)
+  static constexpr int kSlots = 16;          // input-row ring = cp.async pipeline depth; power of two
   static constexpr int kKSteps = CIN / 16;
   static constexpr int kNB = 5 * COUT;                       // B rows per (dx, kk): n = jj*COUT + co
   static constexpr int kWChunkBytes = kNB * 16;              // one 8-channel k-chunk of all n rows
@@ -447,46 +447,50 @@ struct RsCfg {
 
 // Operand feed: LDGSTS=false uses TMA (one 5-D tensor-map request per plane and row; measured
 // ~4-7 cycles per 16-byte box row, i.e. 1-3 k cycles per image row: the bottleneck of v2);
-// LDGSTS=true has the whole producer warp issue 16-byte cp.async copies (zero-fill = padding),
-// 9-25 warp instructions per row, software-pipelined kCpDepth rows deep with wait_group,
-// then fence.proxy.async + one mbarrier arrive per row.
-constexpr int kCpDepth = 10;      // rows of cp.async in flight per producer warp (memory-level parallelism)
-
-// Per-lane copy plan of one image-row segment: which 16-byte pieces this lane moves, where they land in
-// shared memory and where they come from relative to the row start.  It only depends on the strip (x_first),
-// so it is built once per work item; a row then costs ~4 instructions per piece instead of ~30 (the single
-// producer warp was issue-bound re-deriving plane / pixel / bounds for every piece of every row).
+// LDGSTS=true has the whole producer warp issue 16-byte cp.async copies (zero-fill = padding) and
+// then `cp.async.mbarrier.arrive.noinc` on the row's full barrier (count 32): the arrival fires when
+// the lane's copies have landed, so the producer never waits for data and the number of rows in
+// flight is the ring size.  (The earlier wait_group + fence + arrive scheme exposed the load latency
+// once per row: ncu showed the warp parked on the scoreboard of the oldest LDGSTS.)
+//
+// Per-lane copy plan of one image-row segment.  Lane l moves the 16-byte pieces l, l+32, l+64, ... of
+// the row segment in GLOBAL order (a pixel is C/8 consecutive pieces), so one warp instruction reads
+// 512 contiguous bytes, and both the source and the shared-memory destination of piece k are the
+// lane's base plus a compile-time constant: the address registers of an in-flight LDGSTS stay
+// reserved until its data returns, so the row loop must not recompute per-piece addresses.
 template <int C, int NPIX>
 struct RowPlan {
-  static constexpr int kTotal = (C / 8) * NPIX;
+  static constexpr int kPP = C / 8;                      // 16-byte pieces per pixel (= smem planes)
+  static constexpr int kTotal = kPP * NPIX;
   static constexpr int kPer = (kTotal + 31) / 32;
-  uint32_t soff[kPer];     // byte offset inside the slot
-  uint32_t goff[kPer];     // element offset from the row start
+  static constexpr int kStepPix = 32 / kPP;              // pixels between a lane's consecutive pieces
+  uint32_t soff;           // byte offset of the lane's first piece inside the slot
   uint32_t ok;             // bit k: piece k is inside the image horizontally
-  uint32_t use;            // bit k: piece k exists (lane + 32k < kTotal)
-  __device__ __forceinline__ void build(int x_first, int plane_bytes, int W, int lane) {
-    ok = 0; use = 0;
+  int x_first;
+  __device__ __forceinline__ void build(int x_first_, int plane_bytes, int W, int lane) {
+    x_first = x_first_;
+    soff = (uint32_t)((lane % kPP) * plane_bytes + (lane / kPP) * 16);
+    ok = 0;
 #pragma unroll
     for (int k = 0; k < kPer; ++k) {
-      const int i = lane + 32 * k;
-      const int pl = i / NPIX, p = i - pl * NPIX;
-      const int x = x_first + p;
-      const bool in = (i < kTotal) && x >= 0 && x < W;
-      soff[k] = (uint32_t)(pl * plane_bytes + p * 16);
-      goff[k] = in ? (uint32_t)(x * C + pl * 8) : 0u;
-      if (i < kTotal) use |= 1u << k;
-      if (in) ok |= 1u << k;
+      const int j = lane + 32 * k;
+      const int x = x_first + j / kPP;
+      if (j < kTotal && x >= 0 && x < W) ok |= 1u << k;
     }
   }
   // dst: [C/8 planes][NPIX][16 B];  src pixel (b, y, x_first + p), channels plane*8..+7; zero-fill outside
+  // (a piece with source size 0 reads nothing, so its address may lie outside the row)
   __device__ __forceinline__ void copy(uint8_t* dst, const __nv_bfloat16* __restrict__ src, int b, int y, int H,
-                                       int W) const {
+                                       int W, int lane) const {
     const bool row_ok = (y >= 0) && (y < H);
-    const __nv_bfloat16* row = src + ((size_t)b * H + (row_ok ? y : 0)) * (size_t)W * C;
+    const char* row = reinterpret_cast<const char*>(src) +
+                      (((int64_t)b * H + (row_ok ? y : 0)) * (int64_t)W + x_first) * (int64_t)(C * 2);
     const uint32_t okr = row_ok ? ok : 0u;
+    const char* lsrc = row + (uint32_t)(lane * 16);
+    uint8_t* ldst = dst + soff;
 #pragma unroll
     for (int k = 0; k < kPer; ++k)
-      if ((use >> k) & 1u) cp_async16(dst + soff[k], row + goff[k], ((okr >> k) & 1u) ? 16u : 0u);
+      if (lane + 32 * k < kTotal) cp_async16(ldst + k * (kStepPix * 16), lsrc + k * 512, ((okr >> k) & 1u) ? 16u : 0u);
   }
 };
 
@@ -545,7 +549,7 @@ conv5x5_rs_kernel(const __grid_constant__ CUtensorMap tm_act, const __nv_bfloat1
   if (threadIdx.x < COUT) s_bias[threadIdx.x] = bias ? bias[threadIdx.x] : 0.f;
   fence_proxy_async_smem();
   if (threadIdx.x == 0) {
-    for (int i = 0; i < Cfg::kSlots; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+    for (int i = 0; i < Cfg::kSlots; ++i) { mbar_init(&full[i], LDGSTS ? 32 : 1); mbar_init(&empty[i], 1); }
     for (int i = 0; i < RT; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], 128); }
     mbar_fence_init();
     tma_prefetch_desc(&tm_act);
@@ -558,9 +562,8 @@ conv5x5_rs_kernel(const __grid_constant__ CUtensorMap tm_act, const __nv_bfloat1
 
   if (warp == 0) {
     if (LDGSTS) {
-      // whole warp: cp.async feed, kCpDepth rows in flight
+      // whole warp: cp.async feed; completion of each lane's copies arrives on the row's full barrier
       uint32_t gcount = 0;          // rows issued
-      uint32_t gdone = 0;           // rows published
       for (int item = blockIdx.x; item < g.nitems; item += gridDim.x) {
         const int seg = item % g.nseg;
         const int strip = (item / g.nseg) % g.nstrips;
@@ -573,22 +576,10 @@ conv5x5_rs_kernel(const __grid_constant__ CUtensorMap tm_act, const __nv_bfloat1
         for (int i = 0; i < rows + 4; ++i, ++gcount) {
           const uint32_t slot = gcount % Cfg::kSlots, use = gcount / Cfg::kSlots;
           mbar_wait(&empty[slot], (use & 1) ^ 1);
-          plan.copy(s_slots + slot * Cfg::kSlotBytes, act, b, y0 - 2 + i, g.H, g.W);
-          cp_async_commit();
-          if (gcount >= (uint32_t)kCpDepth) {
-            cp_async_wait<kCpDepth>();
-            fence_proxy_async_smem();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&full[gdone % Cfg::kSlots]);
-            ++gdone;
-          }
+          plan.copy(s_slots + slot * Cfg::kSlotBytes, act, b, y0 - 2 + i, g.H, g.W, lane);
+          cp_async_mbar_arrive_noinc(&full[slot]);
         }
       }
-      cp_async_wait<0>();
-      fence_proxy_async_smem();
-      __syncwarp();
-      for (; gdone < gcount; ++gdone)
-        if (lane == 0) mbar_arrive(&full[gdone % Cfg::kSlots]);
     } else if (lane == 0) {
       uint32_t gcount = 0;
       for (int item = blockIdx.x; item < g.nitems; item += gridDim.x) {
@@ -787,7 +778,7 @@ conv5x5_rs_kernel(const __grid_constant__ CUtensorMap tm_act, const __nv_bfloat1
 // wgrad, row-stationary: the act (p1) row is the stationary operand; the five dx2 rows it
 // pairs with (y = r-2 .. r+2) are five CONSECUTIVE slots of the dx2 ring, i.e. 20 consecutive
 // 8-channel planes, i.e. one MN-major B operand with N = 160.  D[pl][(dx,ci8)][(jj,co)], dy = 4-jj.
-constexpr int kWg2SlotsA = 12, kWg2SlotsB = 16;      // A >= kCpDepth + 1, B >= 5 + kCpDepth
+constexpr int kWg2SlotsA = 12, kWg2SlotsB = 16;      // rows in flight: the rings are the cp.async pipeline depth
 constexpr int kWg2SmemBytes = kWg2SlotsA * kWgSlotABytes + kWg2SlotsB * kWgSlotBBytes + 1024 + 128;
 
 template <bool LDGSTS>
@@ -809,8 +800,8 @@ conv5x5_wgrad_rs_kernel(const __grid_constant__ CUtensorMap tm_act, const __grid
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
   if (threadIdx.x == 0) {
-    for (int i = 0; i < kWg2SlotsA; ++i) { mbar_init(&fullA[i], 1); mbar_init(&emptyA[i], 1); }
-    for (int i = 0; i < kWg2SlotsB; ++i) { mbar_init(&fullB[i], 1); mbar_init(&emptyB[i], 1); }
+    for (int i = 0; i < kWg2SlotsA; ++i) { mbar_init(&fullA[i], LDGSTS ? 32 : 1); mbar_init(&emptyA[i], 1); }
+    for (int i = 0; i < kWg2SlotsB; ++i) { mbar_init(&fullB[i], LDGSTS ? 32 : 1); mbar_init(&emptyB[i], 1); }
     mbar_init(done, 1);
     mbar_fence_init();
     tma_prefetch_desc(&tm_act);
@@ -824,7 +815,7 @@ conv5x5_wgrad_rs_kernel(const __grid_constant__ CUtensorMap tm_act, const __grid
 
   if (warp == 0) {
     if (LDGSTS) {
-      uint32_t ga = 0, gb = 0, ga_done = 0, gb_done = 0, it = 0, has_a = 0;   // has_a: bit k = iteration (it-1-k) carried an act row
+      uint32_t ga = 0, gb = 0;
       for (int item = blockIdx.x; item < g.nitems; item += gridDim.x) {
         const int seg = item % g.nseg;
         const int strip = (item / g.nseg) % g.nstrips;
@@ -836,42 +827,23 @@ conv5x5_wgrad_rs_kernel(const __grid_constant__ CUtensorMap tm_act, const __grid
         planB.build(x0, kWgPlaneBBytes, g.W, lane);
         RowPlan<16, kPW> planA;
         planA.build(x0 - 2, kPlaneBytes, g.W, lane);
-        for (int i = 0; i < rows + 4; ++i, ++it) {
+        for (int i = 0; i < rows + 4; ++i) {
           {
             const uint32_t slot = gb % kWg2SlotsB, use = gb / kWg2SlotsB;
             mbar_wait(&emptyB[slot], (use & 1) ^ 1);
-            planB.copy(s_b + slot * kWgSlotBBytes, dxo, b, r0 - 2 + i, g.H, g.W);
+            planB.copy(s_b + slot * kWgSlotBBytes, dxo, b, r0 - 2 + i, g.H, g.W, lane);
+            cp_async_mbar_arrive_noinc(&fullB[slot]);
             ++gb;
           }
-          has_a <<= 1;
           if (i >= 4) {
             const uint32_t slot = ga % kWg2SlotsA, use = ga / kWg2SlotsA;
             mbar_wait(&emptyA[slot], (use & 1) ^ 1);
-            planA.copy(s_a + slot * kWgSlotABytes, act, b, r0 + i - 4, g.H, g.W);
+            planA.copy(s_a + slot * kWgSlotABytes, act, b, r0 + i - 4, g.H, g.W, lane);
+            cp_async_mbar_arrive_noinc(&fullA[slot]);
             ++ga;
-            has_a |= 1u;
-          }
-          cp_async_commit();
-          if (it >= (uint32_t)kCpDepth) {
-            cp_async_wait<kCpDepth>();
-            fence_proxy_async_smem();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&fullB[gb_done % kWg2SlotsB]);
-            ++gb_done;
-            if ((has_a >> kCpDepth) & 1u) {
-              if (lane == 0) mbar_arrive(&fullA[ga_done % kWg2SlotsA]);
-              ++ga_done;
-            }
           }
         }
       }
-      cp_async_wait<0>();
-      fence_proxy_async_smem();
-      __syncwarp();
-      for (; gb_done < gb; ++gb_done)
-        if (lane == 0) mbar_arrive(&fullB[gb_done % kWg2SlotsB]);
-      for (; ga_done < ga; ++ga_done)
-        if (lane == 0) mbar_arrive(&fullA[ga_done % kWg2SlotsA]);
     } else if (lane == 0) {
       uint32_t ga = 0, gb = 0;
       for (int item = blockIdx.x; item < g.nitems; item += gridDim.x) {
