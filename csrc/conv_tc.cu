@@ -453,44 +453,49 @@ struct RsCfg {
 // flight is the ring size.  (The earlier wait_group + fence + arrive scheme exposed the load latency
 // once per row: ncu showed the warp parked on the scoreboard of the oldest LDGSTS.)
 //
-// Per-lane copy plan of one image-row segment.  Lane l moves the 16-byte pieces l, l+32, l+64, ... of
-// the row segment in GLOBAL order (a pixel is C/8 consecutive pieces), so one warp instruction reads
-// 512 contiguous bytes, and both the source and the shared-memory destination of piece k are the
-// lane's base plus a compile-time constant: the address registers of an in-flight LDGSTS stay
-// reserved until its data returns, so the row loop must not recompute per-piece addresses.
+// Per-lane copy plan of one image-row segment.  One warp instruction moves 32/kPP consecutive pixels
+// (all kPP planes of each): 512 contiguous bytes of global memory, landing as kPP contiguous runs in
+// shared memory (one per plane) - whole sectors on the read side, conflict-free 128-byte wavefronts
+// on the write side (splitting a 64-byte run of lanes across two planes doubled the LSU bank-conflict
+// count in ncu).  Source and destination of a lane's k-th piece are its base plus a compile-time
+// constant: the address registers of an in-flight LDGSTS stay reserved until its data returns, so the
+// row loop must not recompute per-piece addresses.
 template <int C, int NPIX>
 struct RowPlan {
   static constexpr int kPP = C / 8;                      // 16-byte pieces per pixel (= smem planes)
-  static constexpr int kTotal = kPP * NPIX;
-  static constexpr int kPer = (kTotal + 31) / 32;
-  static constexpr int kStepPix = 32 / kPP;              // pixels between a lane's consecutive pieces
+  static constexpr int kLP = 32 / kPP;                   // pixels per warp instruction
+  static constexpr int kPer = (NPIX + kLP - 1) / kLP;    // warp instructions per row
   uint32_t soff;           // byte offset of the lane's first piece inside the slot
+  uint32_t goff;           // byte offset of the lane's first piece from pixel x_first of the row
   uint32_t ok;             // bit k: piece k is inside the image horizontally
-  int x_first;
+  int x_first, px0;
   __device__ __forceinline__ void build(int x_first_, int plane_bytes, int W, int lane) {
     x_first = x_first_;
-    soff = (uint32_t)((lane % kPP) * plane_bytes + (lane / kPP) * 16);
+    const int pl = lane / kLP;
+    px0 = lane % kLP;
+    soff = (uint32_t)(pl * plane_bytes + px0 * 16);
+    goff = (uint32_t)(px0 * (C * 2) + pl * 16);
     ok = 0;
 #pragma unroll
     for (int k = 0; k < kPer; ++k) {
-      const int j = lane + 32 * k;
-      const int x = x_first + j / kPP;
-      if (j < kTotal && x >= 0 && x < W) ok |= 1u << k;
+      const int p = px0 + k * kLP, x = x_first + p;
+      if (p < NPIX && x >= 0 && x < W) ok |= 1u << k;
     }
   }
   // dst: [C/8 planes][NPIX][16 B];  src pixel (b, y, x_first + p), channels plane*8..+7; zero-fill outside
   // (a piece with source size 0 reads nothing, so its address may lie outside the row)
   __device__ __forceinline__ void copy(uint8_t* dst, const __nv_bfloat16* __restrict__ src, int b, int y, int H,
-                                       int W, int lane) const {
+                                       int W) const {
     const bool row_ok = (y >= 0) && (y < H);
     const char* row = reinterpret_cast<const char*>(src) +
                       (((int64_t)b * H + (row_ok ? y : 0)) * (int64_t)W + x_first) * (int64_t)(C * 2);
     const uint32_t okr = row_ok ? ok : 0u;
-    const char* lsrc = row + (uint32_t)(lane * 16);
+    const char* lsrc = row + goff;
     uint8_t* ldst = dst + soff;
 #pragma unroll
     for (int k = 0; k < kPer; ++k)
-      if (lane + 32 * k < kTotal) cp_async16(ldst + k * (kStepPix * 16), lsrc + k * 512, ((okr >> k) & 1u) ? 16u : 0u);
+      if ((k + 1) * kLP <= NPIX || px0 + k * kLP < NPIX)
+        cp_async16(ldst + k * (kLP * 16), lsrc + k * 512, ((okr >> k) & 1u) ? 16u : 0u);
   }
 };
 
@@ -576,7 +581,7 @@ conv5x5_rs_kernel(const __grid_constant__ CUtensorMap tm_act, const __nv_bfloat1
         for (int i = 0; i < rows + 4; ++i, ++gcount) {
           const uint32_t slot = gcount % Cfg::kSlots, use = gcount / Cfg::kSlots;
           mbar_wait(&empty[slot], (use & 1) ^ 1);
-          plan.copy(s_slots + slot * Cfg::kSlotBytes, act, b, y0 - 2 + i, g.H, g.W, lane);
+          plan.copy(s_slots + slot * Cfg::kSlotBytes, act, b, y0 - 2 + i, g.H, g.W);
           cp_async_mbar_arrive_noinc(&full[slot]);
         }
       }
@@ -730,7 +735,9 @@ conv5x5_rs_kernel(const __grid_constant__ CUtensorMap tm_act, const __nv_bfloat1
         uint32_t pk[COUT / 2];
 #pragma unroll
         for (int c = 0; c < COUT; c += 2) {
-          pk[c / 2] = pack_bf16x2(__uint_as_float(v[c]) + s_bias[c], __uint_as_float(v[c + 1]) + s_bias[c + 1]);
+          // the transposed (dgrad) convolution has no bias
+          pk[c / 2] = TRANSPOSED ? pack_bf16x2(__uint_as_float(v[c]), __uint_as_float(v[c + 1]))
+                                 : pack_bf16x2(__uint_as_float(v[c]) + s_bias[c], __uint_as_float(v[c + 1]) + s_bias[c + 1]);
           if (STATS == 1 && valid) {
             const float r0 = bf16_lo(pk[c / 2]), r1 = bf16_hi(pk[c / 2]);
             ssum[c] += r0; ssq[c] = fmaf(r0, r0, ssq[c]);
@@ -738,7 +745,7 @@ conv5x5_rs_kernel(const __grid_constant__ CUtensorMap tm_act, const __nv_bfloat1
           }
         }
         if (valid) {
-          uint4* o = reinterpret_cast<uint4*>(out + (((size_t)b * g.H + (y0 + j)) * g.W + x) * COUT);
+          __nv_bfloat16* o = out + (((size_t)b * g.H + (y0 + j)) * g.W + x) * COUT;
           if (STATS == 2) {
 #pragma unroll
             for (int c = 0; c < COUT; ++c) {
@@ -751,7 +758,7 @@ conv5x5_rs_kernel(const __grid_constant__ CUtensorMap tm_act, const __nv_bfloat1
             }
           }
 #pragma unroll
-          for (int i = 0; i < COUT / 8; ++i) o[i] = make_uint4(pk[4 * i], pk[4 * i + 1], pk[4 * i + 2], pk[4 * i + 3]);
+          for (int i = 0; i < COUT / 16; ++i) st_global_v8(o + 16 * i, &pk[8 * i]);   // 32-byte stores: whole sectors
         }
       }
     }
@@ -831,14 +838,14 @@ conv5x5_wgrad_rs_kernel(const __grid_constant__ CUtensorMap tm_act, const __grid
           {
             const uint32_t slot = gb % kWg2SlotsB, use = gb / kWg2SlotsB;
             mbar_wait(&emptyB[slot], (use & 1) ^ 1);
-            planB.copy(s_b + slot * kWgSlotBBytes, dxo, b, r0 - 2 + i, g.H, g.W, lane);
+            planB.copy(s_b + slot * kWgSlotBBytes, dxo, b, r0 - 2 + i, g.H, g.W);
             cp_async_mbar_arrive_noinc(&fullB[slot]);
             ++gb;
           }
           if (i >= 4) {
             const uint32_t slot = ga % kWg2SlotsA, use = ga / kWg2SlotsA;
             mbar_wait(&emptyA[slot], (use & 1) ^ 1);
-            planA.copy(s_a + slot * kWgSlotABytes, act, b, r0 + i - 4, g.H, g.W, lane);
+            planA.copy(s_a + slot * kWgSlotABytes, act, b, r0 + i - 4, g.H, g.W);
             cp_async_mbar_arrive_noinc(&fullA[slot]);
             ++ga;
           }

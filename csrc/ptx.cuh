@@ -74,6 +74,12 @@ __device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc, uin
 __device__ __forceinline__ void cp_async8(void* smem_dst, const void* gsrc, uint32_t src_bytes) {
   asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" ::"r"(smem_u32(smem_dst)), "l"(gsrc), "r"(src_bytes) : "memory");
 }
+// 256-bit global store (sm_100: STG.E.ENL2.256); p must be 32-byte aligned
+__device__ __forceinline__ void st_global_v8(void* p, const uint32_t* v) {
+  asm volatile("st.global.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]),
+               "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7])
+               : "memory");
+}
 // mbarrier arrival triggered when all cp.async copies this thread has issued so far have completed
 // (.noinc: the arrival is one of the barrier's expected count, so init the barrier with one per thread)
 __device__ __forceinline__ void cp_async_mbar_arrive_noinc(uint64_t* bar) {
