@@ -47,10 +47,10 @@ constexpr int kSmemBytes = kStages * kStageBytes + kStages * kERows * kInW * 4 +
 __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }
-__device__ __forceinline__ uint4 ldg16(const void* p) {
-  uint4 r;
-  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
-  return r;
+// one 32-byte pixel (16 bf16 channels) per 256-bit load: half the LSU wavefronts of two 128-bit loads
+__device__ __forceinline__ void ldg32(const void* p, uint4& a, uint4& b) {
+  asm volatile("ld.global.nc.L1::no_allocate.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=r"(a.x), "=r"(a.y), "=r"(a.z), "=r"(a.w), "=r"(b.x), "=r"(b.y), "=r"(b.z), "=r"(b.w) : "l"(p));
 }
 
 struct WgGeom {
@@ -146,12 +146,12 @@ conv1_wgrad_tc_kernel(const float* __restrict__ in, const __nv_bfloat16* __restr
       wvalid = gy < g.H && gx < g.W;
       if (wvalid) {
         const __nv_bfloat16* xb = x1 + (((size_t)b * g.H + gy) * g.W + gx) * kC1;
-        xr[0][0] = ldg16(xb); xr[0][1] = ldg16(xb + 8);
-        xr[1][0] = ldg16(xb + kC1); xr[1][1] = ldg16(xb + kC1 + 8);
-        xr[2][0] = ldg16(xb + (size_t)g.W * kC1); xr[2][1] = ldg16(xb + (size_t)g.W * kC1 + 8);
-        xr[3][0] = ldg16(xb + (size_t)g.W * kC1 + kC1); xr[3][1] = ldg16(xb + (size_t)g.W * kC1 + kC1 + 8);
+        ldg32(xb, xr[0][0], xr[0][1]);
+        ldg32(xb + kC1, xr[1][0], xr[1][1]);
+        ldg32(xb + (size_t)g.W * kC1, xr[2][0], xr[2][1]);
+        ldg32(xb + (size_t)g.W * kC1 + kC1, xr[3][0], xr[3][1]);
         const __nv_bfloat16* gb = dp1 + (((size_t)b * Ho + (gy >> 1)) * Wo + (gx >> 1)) * kC1;
-        gr[0] = ldg16(gb); gr[1] = ldg16(gb + 8);
+        ldg32(gb, gr[0], gr[1]);
       }
     };
     if ((int)blockIdx.x < g.nitems) issue_loads(blockIdx.x);
@@ -505,11 +505,10 @@ conv1_fwd_tc_kernel(const float* __restrict__ in, const float* __restrict__ w1, 
             }
           }
           if (ok) {
-            uint4* o = reinterpret_cast<uint4*>(orow + (c0 >> 4) * 16);
-            o[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-            o[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
-            o[2] = make_uint4(pk[8], pk[9], pk[10], pk[11]);
-            o[3] = make_uint4(pk[12], pk[13], pk[14], pk[15]);
+            // lanes are image ROWS here, so every store instruction touches 32 lines: 256-bit stores halve them
+            __nv_bfloat16* o = orow + (c0 >> 4) * 16;
+            st_global_v8(o, &pk[0]);
+            st_global_v8(o + 16, &pk[8]);
           }
           if (k < 3) tmem_ld_wait();
           else { tc_fence_before(); mbar_arrive(&tempty[ts]); }

@@ -1,6 +1,6 @@
 """Run ONE kernel of the training step at the flagship size (batch 5, 3000x3000) a few times,
 standalone, so it can be profiled with `ncu -k regex:<name>` (B200_PROFILING.md recipe).
-usage: run_one_kernel.py <conv2_fwd|conv2_dgrad|conv2_wgrad|conv1_fwd|conv1_wgrad|step> [tc version] [iters]"""
+usage: run_one_kernel.py <conv2_fwd|conv2_dgrad|conv2_dgrad_stats|conv2_wgrad|conv1_fwd|conv1_wgrad|step> [tc version] [iters]"""
 import os
 import sys
 
@@ -27,6 +27,8 @@ s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True
 fn = {
     "conv2_fwd": lambda: ops.conv2_fwd_tc(eng.p1, P["layer2.0.weight"], P["layer2.0.bias"], eng.x2, eng.part_c2),
     "conv2_dgrad": lambda: ops.conv2_dgrad_tc(eng.x2, P["layer2.0.weight"], torch.empty_like(eng.p1)),
+    "conv2_dgrad_stats": lambda: ops.conv2_dgrad_stats_tc(eng.dx2, P["layer2.0.weight"], eng.p1, eng.bn1,
+                                                          torch.empty_like(eng.p1), eng.part_bwd),
     "conv2_wgrad": lambda: ops.conv2_wgrad_tc(eng.p1, eng.x2, eng.part_wg2, eng.grads["layer2.0.weight"]),
     "conv1_fwd_tc": lambda: ops.conv1_fwd_tc(eng.x, P["layer1.0.weight"], P["layer1.0.bias"], eng.x1, eng.part_c1),
     "conv1_fwd": lambda: ops.conv1_fwd(eng.x, P["layer1.0.weight"], P["layer1.0.bias"], eng.x1, eng.part_c1),
