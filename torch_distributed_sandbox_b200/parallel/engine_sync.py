@@ -35,7 +35,7 @@ class EngineGradSync:
         self.blocks = int(os.environ.get("B200DP_AR_BLOCKS", "32"))     # CTAs of the overlapped bucket all-reduce (tuned at N=2)
         self._fc_event = None
         self._steps = 0
-        self.reserved_sms = int(os.environ.get("B200DP_RESERVED_SMS", "8"))    # SM partition (common.cu); 0 = share SMs
+        self.reserved_sms = int(os.environ.get("B200DP_RESERVED_SMS", "6"))    # SM partition (common.cu); 0 = share SMs
         self._debug_skip_fc = os.environ.get("B200DP_DEBUG_SKIP_FC_ALLREDUCE", "0") == "1"   # timing experiments only
         be = self.backend
         if self.world > 1 and getattr(be, "name", "") != "native":
