@@ -8,7 +8,7 @@ run() { echo "=== $*" >> $L; timeout ${TMO:-300} "$@" >> $L 2>&1; echo "=== rc=$
 TR="python -m torch.distributed.run --nnodes=1 --master-addr 127.0.0.1"
 run python -m pytest -q -s -p no:cacheprovider -m gpu tests/test_gpu_multi.py
 run $TR --nproc-per-node $N --master-port 29511 bench.py --gpus $N --steps 30 --warmup 5
-run env B200DP_RESERVED_SMS=6 $TR --nproc-per-node $N --master-port 29521 bench.py --gpus $N --steps 30 --warmup 5
+run env B200DP_RESERVED_SMS=8 $TR --nproc-per-node $N --master-port 29521 bench.py --gpus $N --steps 30 --warmup 5
 run env B200DP_RESERVED_SMS=12 $TR --nproc-per-node $N --master-port 29522 bench.py --gpus $N --steps 30 --warmup 5
 if [ $N -ge 4 ]; then
   H=$((N/2))

@@ -328,8 +328,12 @@ class FusedConvNet:
                        lr=self.lr if fused else 0.0, accumulate=b0 > 0, gscale=gs,
                        bn2=self.bn2 if fuse_stats else None, bwd_partials=self.part_fcb if fuse_stats else None)
         self._fc_fused_done = fused
-        if self.comm is not None:
-            self.comm.fc_grad_ready(self)            # async all-reduce of the 720 MB bucket
+        # async all-reduce of the 720 MB bucket.  By default it starts after the next kernel instead of here:
+        # pool_bn_bwd is HBM-bound and lost 0.16 ms to the all-reduce's 1.4 GB of HBM traffic, while the
+        # conv kernels after it are bound by the shared-memory pipe / tensor pipe and have DRAM headroom.
+        defer_ar = self.comm is not None and getattr(self.comm, "start_after_pool", False)
+        if self.comm is not None and not defer_ar:
+            self.comm.fc_grad_ready(self)
         # ---- layer 2 (statistics pass fused into fc_bwd above unless disabled)
         H2, W2 = H // 2, W // 2
         if fuse_stats:
@@ -340,6 +344,8 @@ class FusedConvNet:
             ops.bn_bwd_finalize(self.part_bwd, self.g_pbb, 32, B * H2 * W2, self.red2, G["layer2.1.weight"],
                                 G["layer2.1.bias"], gs)
         ops.pool_bn_bwd(self.x2, self.dp2, self.bn2, self.red2, None, self.dx2, mode=1)
+        if defer_ar:
+            self.comm.fc_grad_ready(self)
         if self.conv_backend == "tc":
             ops.conv2_wgrad_tc(self.p1, self.dx2, self.part_wg2, G["layer2.0.weight"], gs)
             if fuse_stats:   # dgrad epilogue also reduces BN1's backward sums (reads p1 before dp1 overwrites it)

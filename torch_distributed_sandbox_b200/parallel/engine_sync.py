@@ -35,7 +35,11 @@ class EngineGradSync:
         self.blocks = int(os.environ.get("B200DP_AR_BLOCKS", "32"))     # CTAs of the overlapped bucket all-reduce (tuned at N=2)
         self._fc_event = None
         self._steps = 0
-        self.reserved_sms = int(os.environ.get("B200DP_RESERVED_SMS", "6"))    # SM partition (common.cu); 0 = share SMs
+        # SM partition (common.cu); 0 = share SMs.  Each rank reduces 1/world of the bucket, so the comm CTAs a
+        # step needs shrink with the world size (measured best: 8 at N=2, 4 at N=8).
+        self.reserved_sms = int(os.environ.get("B200DP_RESERVED_SMS", str({2: 8, 4: 6}.get(self.world, 4))))
+        # start the big-bucket all-reduce after the HBM-bound pool/BN backward kernel ("pool") or right after fc_bwd ("fc")
+        self.start_after_pool = os.environ.get("B200DP_AR_START", "pool") == "pool"
         self._debug_skip_fc = os.environ.get("B200DP_DEBUG_SKIP_FC_ALLREDUCE", "0") == "1"   # timing experiments only
         be = self.backend
         if self.world > 1 and getattr(be, "name", "") != "native":
