@@ -122,3 +122,24 @@ def test_resize_tables_match_pillow_and_torchvision():
         assert np.array_equal(ref, resize_u8_reference(a, hw)), hw
     tv = T.Compose([T.Resize([300, 300]), T.ToTensor()])(Image.fromarray(a, mode="L"))[0]
     assert torch.equal(tv, torch.from_numpy(resize_u8_reference(a, (300, 300))).float() / 255.0)
+
+
+def test_trace_step_timer_and_nvtx_noop():
+    """step timer (host clock without a GPU) and NVTX ranges that cost nothing when disabled."""
+    import time
+    from torch_distributed_sandbox_b200.utils import trace
+    t = trace.StepTimer(skip=1)
+    for _ in range(4):
+        with t.step():
+            time.sleep(0.002)
+    s = t.summary()
+    assert s["steps"] == 3 and s["min_ms"] >= 1.5 and s["max_ms"] >= s["mean_ms"] >= s["min_ms"]
+    assert not trace.nvtx_enabled()
+    with trace.nvtx_range("x"):
+        pass
+    trace.enable_nvtx(True)
+    try:
+        with trace.nvtx_range("y"):      # no CUDA here: still a no-op, must not raise
+            pass
+    finally:
+        trace.enable_nvtx(False)

@@ -38,6 +38,8 @@ from typing import Optional, Sequence
 import torch
 import torch.nn.functional as F
 
+from ..utils import trace
+
 from .. import ops
 from ..data.resize import pil_bilinear_table
 from . import reference_net as rn
@@ -389,9 +391,17 @@ class FusedConvNet:
                 ops.sgd(self.fcw, self.fcw_grad, self.lr)
 
     def train_step(self, images: torch.Tensor, labels: torch.Tensor) -> torch.Tensor:
-        self.forward(images)
-        self.loss_backward(labels)
-        self.step()
+        if not trace.nvtx_enabled():
+            self.forward(images)
+            self.loss_backward(labels)
+            self.step()
+            return self.loss
+        with trace.nvtx_range("b200dp.forward"):
+            self.forward(images)
+        with trace.nvtx_range("b200dp.loss+backward"):
+            self.loss_backward(labels)
+        with trace.nvtx_range("b200dp.optimizer"):
+            self.step()
         return self.loss
 
     __call__ = forward

@@ -22,6 +22,7 @@ from typing import Dict, List
 import torch
 
 from .. import distributed as dist
+from ..utils import trace
 
 
 class EngineGradSync:
@@ -96,7 +97,7 @@ class EngineGradSync:
         main = torch.cuda.current_stream()
         ready = torch.cuda.Event()
         ready.record(main)
-        with torch.cuda.stream(self.comm_stream):
+        with torch.cuda.stream(self.comm_stream), trace.nvtx_range("b200dp.allreduce.fc_bucket"):
             self.comm_stream.wait_event(ready)
             self.backend.all_reduce(engine.fcw_grad, dist.ReduceOp.SUM, channel=1, scale=1.0 / self.world,
                                     sgd=(engine.fcw, engine.lr) if self.fuse_sgd else None, algo=self.algo,
