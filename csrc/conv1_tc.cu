@@ -290,26 +290,31 @@ B200_API int b200_conv1_wgrad_tc(const void* in_f32, const void* x1, const void*
 // =====================================================================================
 // K3 (+K4 statistics), conv1 forward as a Toeplitz GEMM on tcgen05.
 //
-//   out[y, x0+xo, c] = sum_{dy} sum_{k} in[y+dy-2, x0-2+k] * T_dy[k][(xo, c)],
-//   T_dy[k][(xo,c)] = w[c][dy][k - xo]  (0 <= k - xo <= 4, else 0),   k = 0..15, xo = 0..7
+//   out[y0+yo, x, c] = sum_{dx} sum_{k} in[y0-2+k, x+dx-2] * T_dx[k][(yo, c)],
+//   T_dx[k][(yo,c)] = w[c][k - yo][dx]  (0 <= k - yo <= 4, else 0),   k = 0..15, yo = 0..7
 //
-// i.e. for 8 output columns at a time, M = 128 image ROWS, N = 8 columns x 16 channels = 128,
-// K = 16 input columns, five MMAs (one per dy; A = the same input planes shifted down by dy
-// rows).  31 % of the MACs are useful; a 64-cycle MMA still replaces 409,600 FFMAs.
-// The input tile is written by producer warps as bf16 "column planes" (8 pixels = 16 B per
-// row, rows 16 B apart) so that it is directly the no-swizzle K-major A operand.
+// i.e. for 8 output rows at a time, M = 128 image COLUMNS, N = 8 rows x 16 channels = 128,
+// K = 16 input rows, five MMAs (one per dx; A = the same input planes shifted right by dx
+// columns = start address + dx * 16 B).  31 % of the MACs are useful; a 64-cycle MMA still
+// replaces 409,600 FFMAs.  The input tile is written by producer warps as bf16 "row planes"
+// (8 vertically consecutive pixels = 16 B per column, columns 16 B apart) so that it is directly
+// the no-swizzle K-major A operand.
+// Orientation matters for the epilogue: a TMEM lane is an image column, so a warp's 256-bit store
+// of one output row covers 32 consecutive pixels = 1 KB of contiguous NHWC memory.  (The first
+// version put image ROWS on the lanes: every store instruction touched 32 different lines and the
+// kernel was bound by LSU wavefronts in the L1 data pipe, ncu: 65 %.)
 // Accuracy: inputs and weights are split into bf16 hi + lo parts and three MMAs
 // (hi*hi + hi*lo + lo*hi) are accumulated in fp32, which restores ~16 mantissa bits - the
 // result matches the fp32 FFMA kernel to output rounding.  The kernel is bounded by writing
 // its 16-channel bf16 output (1.44 GB at batch 5).
 namespace {
 
-constexpr int kFwRows = 128;                 // M: image rows per item
-constexpr int kFwSegPx = 64;                 // output pixels per item along x (8 x-blocks of 8)
-constexpr int kFwBlocks = kFwSegPx / 8;
-constexpr int kFwPlanes = kFwBlocks + 1;     // input planes of 8 pixels
-constexpr int kFwPlaneRows = 136;            // 132 needed, padded so a plane is 17 * 128 B
-constexpr int kFwPlaneBytes = kFwPlaneRows * 16;
+constexpr int kFwCols = 128;                 // M: image columns per item
+constexpr int kFwSegRows = 64;               // output rows per item (8 row-blocks of 8)
+constexpr int kFwBlocks = kFwSegRows / 8;
+constexpr int kFwPlanes = kFwBlocks + 1;     // input planes of 8 rows
+constexpr int kFwPlaneCols = 136;            // 132 needed, padded so a plane is 17 * 128 B
+constexpr int kFwPlaneBytes = kFwPlaneCols * 16;
 constexpr int kFwXBytes = kFwPlanes * kFwPlaneBytes;          // one of hi / lo
 constexpr int kFwStageBytes = 2 * kFwXBytes;                  // hi + lo
 constexpr int kFwStages = 2;
@@ -317,8 +322,8 @@ constexpr int kFwWBytes = 5 * 2 * 128 * 16;                   // Toeplitz weight
 constexpr int kFwProdWarps = 4, kFwEpiWarps = 8;
 constexpr int kFwThreads = 32 * (1 + kFwProdWarps + kFwEpiWarps);   // 416
 constexpr int kFwTStages = 4;
-constexpr int kFwTileW = kFwPlanes * 8;      // 72 input columns
-constexpr int kFwTileH = kFwRows + 4;        // 132 input rows
+constexpr int kFwTileH = kFwPlanes * 8;      // 72 input rows
+constexpr int kFwTileW = kFwCols + 4;        // 132 input columns
 constexpr int kFwRawBytes = kFwTileH * kFwTileW * 4;          // fp32 staging of one input tile (38 KB)
 constexpr int kFwSmemBytes = kFwStages * kFwStageBytes + 2 * kFwWBytes + 2 * kFwRawBytes + 2048 + 128;
 
@@ -332,9 +337,9 @@ conv1_fwd_tc_kernel(const float* __restrict__ in, const float* __restrict__ w1, 
                     __nv_bfloat16* __restrict__ x1, float* __restrict__ partials, FwGeom g) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((128u - (smem_u32(smem_raw) & 127u)) & 127u);
-  uint8_t* s_x = smem;                                   // [kFwStages][hi | lo][planes][rows][16 B]
-  uint8_t* s_w = smem + kFwStages * kFwStageBytes;       // [hi | lo][dy][chunk][n][16 B]
-  uint8_t* s_raw = s_w + 2 * kFwWBytes;                  // [2][132][72] fp32, filled by cp.async
+  uint8_t* s_x = smem;                                   // [kFwStages][hi | lo][row planes][columns][16 B]
+  uint8_t* s_w = smem + kFwStages * kFwStageBytes;       // [hi | lo][dx][chunk][n][16 B]
+  uint8_t* s_raw = s_w + 2 * kFwWBytes;                  // [2][72][132] fp32, filled by cp.async
   uint64_t* bars = reinterpret_cast<uint64_t*>(s_raw + 2 * kFwRawBytes);
   uint64_t* xfull = bars;                   // [2]
   uint64_t* xempty = xfull + kFwStages;     // [2]
@@ -351,9 +356,9 @@ conv1_fwd_tc_kernel(const float* __restrict__ in, const float* __restrict__ w1, 
     int r = i >> 3;
     const int n = r & 127; r >>= 7;
     const int c = r & 1;
-    const int dy = r >> 1;
-    const int k = c * 8 + e, xo = n >> 4, ch = n & 15, dx = k - xo;
-    const float v = (dx >= 0 && dx <= 4) ? w1[ch * 25 + dy * 5 + dx] : 0.f;
+    const int dx = r >> 1;
+    const int k = c * 8 + e, yo = n >> 4, ch = n & 15, dy = k - yo;
+    const float v = (dy >= 0 && dy <= 4) ? w1[ch * 25 + dy * 5 + dx] : 0.f;
     const __nv_bfloat16 hi = __float2bfloat16_rn(v);
     reinterpret_cast<__nv_bfloat16*>(s_w)[i] = hi;
     reinterpret_cast<__nv_bfloat16*>(s_w + kFwWBytes)[i] = __float2bfloat16_rn(v - __bfloat162float(hi));
@@ -392,12 +397,12 @@ conv1_fwd_tc_kernel(const float* __restrict__ in, const float* __restrict__ w1, 
         const uint32_t pj = (uint32_t)j * (kFwPlaneBytes >> 4);
         if (elect_one()) {
 #pragma unroll
-          for (int dy = 0; dy < 5; ++dy) {
-            const uint64_t ah = ((uint64_t)a_hi32 << 32) | (uint64_t)(xh + pj + dy);
-            const uint64_t al = ((uint64_t)a_hi32 << 32) | (uint64_t)(xl + pj + dy);
-            const uint64_t bh = ((uint64_t)b_hi32 << 32) | (uint64_t)(w_hi_lo + dy * (4096 >> 4));
-            const uint64_t bl = ((uint64_t)b_hi32 << 32) | (uint64_t)(w_lo_lo + dy * (4096 >> 4));
-            umma_bf16(d, ah, bh, idesc, dy == 0 ? 0u : 1u);
+          for (int dx = 0; dx < 5; ++dx) {
+            const uint64_t ah = ((uint64_t)a_hi32 << 32) | (uint64_t)(xh + pj + dx);
+            const uint64_t al = ((uint64_t)a_hi32 << 32) | (uint64_t)(xl + pj + dx);
+            const uint64_t bh = ((uint64_t)b_hi32 << 32) | (uint64_t)(w_hi_lo + dx * (4096 >> 4));
+            const uint64_t bl = ((uint64_t)b_hi32 << 32) | (uint64_t)(w_lo_lo + dx * (4096 >> 4));
+            umma_bf16(d, ah, bh, idesc, dx == 0 ? 0u : 1u);
             umma_bf16(d, ah, bl, idesc, 1u);
             umma_bf16(d, al, bh, idesc, 1u);
           }
@@ -408,17 +413,19 @@ conv1_fwd_tc_kernel(const float* __restrict__ in, const float* __restrict__ w1, 
       }
     }
   } else if (warp <= kFwProdWarps) {
-    // ================= producers: fp32 input tile -> bf16 hi/lo column planes =================
+    // ================= producers: fp32 input tile -> bf16 hi/lo row planes =================
     // The tile of item n+1 is fetched with 8-byte cp.async (zero-fill outside the image) into an fp32
     // staging buffer while item n is converted, so HBM latency is off the critical path and costs no
-    // registers.  Every thread converts exactly the pieces it fetched: no barrier between the two steps.
+    // registers.  The conversion transposes (8 vertically consecutive pixels become one 16-byte piece),
+    // so a thread converts pixels other threads fetched: one named barrier per item orders both the
+    // landing of item n and the reuse of the staging buffer item n-1 was converted from.
     const int pt = threadIdx.x - 32;                    // 0..127
     constexpr int kPieces = kFwTileH * kFwTileW / 2;    // 8-byte pieces (2 pixels) per tile
     auto fetch = [&](int item, int buf) {
       const int xs = item % g.nxs;
       const int ys = (item / g.nxs) % g.nys;
       const int b = item / (g.nxs * g.nys);
-      const int y0 = ys * kFwRows, x0 = xs * kFwSegPx;
+      const int y0 = ys * kFwSegRows, x0 = xs * kFwCols;
       const float* src = in + (size_t)b * g.H * g.W;
       uint8_t* raw = s_raw + buf * kFwRawBytes;
       for (int i = pt; i < kPieces; i += 32 * kFwProdWarps) {
@@ -435,19 +442,24 @@ conv1_fwd_tc_kernel(const float* __restrict__ in, const float* __restrict__ w1, 
       const uint32_t s = n % kFwStages;
       uint8_t* xh = s_x + s * kFwStageBytes;
       uint8_t* xl = xh + kFwXBytes;
-      const bool more = item + (int)gridDim.x < g.nitems;
-      if (more) fetch(item + gridDim.x, (n + 1) & 1);
-      if (more) cp_async_wait<1>(); else cp_async_wait<0>();   // this item's pieces (of this thread) have landed
+      cp_async_wait<0>();                                     // this thread's pieces of item n have landed
+      named_bar_sync(2, 32 * kFwProdWarps);                   // ... everyone's have, and item n-1 is fully converted
+      if (item + (int)gridDim.x < g.nitems) fetch(item + gridDim.x, (n + 1) & 1);
       mbar_wait(&xempty[s], ((n / kFwStages) & 1) ^ 1);
-      const uint8_t* raw = s_raw + (n & 1) * kFwRawBytes;
-      for (int i = pt; i < kPieces; i += 32 * kFwProdWarps) {
-        const int rho = i / (kFwTileW / 2), sx = 2 * (i - rho * (kFwTileW / 2));
-        const float2 v = *reinterpret_cast<const float2*>(raw + (size_t)i * 8);
-        const uint32_t hi = pack_bf16x2(v.x, v.y);
-        const uint32_t lo = pack_bf16x2(v.x - bf16_lo(hi), v.y - bf16_hi(hi));
-        const int off = (sx >> 3) * kFwPlaneBytes + rho * 16 + (sx & 7) * 2;
-        *reinterpret_cast<uint32_t*>(xh + off) = hi;
-        *reinterpret_cast<uint32_t*>(xl + off) = lo;
+      const float* raw = reinterpret_cast<const float*>(s_raw + (n & 1) * kFwRawBytes);
+      for (int p = pt; p < kFwPlanes * kFwTileW; p += 32 * kFwProdWarps) {
+        const int pr = p / kFwTileW, x = p - pr * kFwTileW;
+        const float* col = raw + (size_t)(8 * pr) * kFwTileW + x;
+        uint32_t hi[4], lo[4];
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+          const float v0 = col[(2 * r) * kFwTileW], v1 = col[(2 * r + 1) * kFwTileW];
+          hi[r] = pack_bf16x2(v0, v1);
+          lo[r] = pack_bf16x2(v0 - bf16_lo(hi[r]), v1 - bf16_hi(hi[r]));
+        }
+        const int off = pr * kFwPlaneBytes + x * 16;
+        *reinterpret_cast<uint4*>(xh + off) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+        *reinterpret_cast<uint4*>(xl + off) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
       }
       fence_proxy_async_smem();
       __syncwarp();
@@ -466,16 +478,16 @@ conv1_fwd_tc_kernel(const float* __restrict__ in, const float* __restrict__ w1, 
       const int xs = item % g.nxs;
       const int ys = (item / g.nxs) % g.nys;
       const int b = item / (g.nxs * g.nys);
-      const int y = ys * kFwRows + m;
-      const bool row_ok = y < g.H;
+      const int x = xs * kFwCols + m;
+      const bool col_ok = x < g.W;
       for (int j = 0; j < kFwBlocks; ++j, ++q) {
         if ((int)(q & 1) != grp) continue;
         const uint32_t ts = q % kFwTStages;
         mbar_wait(&tfull[ts], (q / kFwTStages) & 1);
         tc_fence_after();
-        const int xb = xs * kFwSegPx + j * 8;
-        __nv_bfloat16* orow = x1 + (((size_t)b * g.H + (row_ok ? y : 0)) * g.W + xb) * 16;
-        // 4 chunks of 2 pixels x 16 channels; the tcgen05.ld of chunk k+1 is in flight while chunk k is
+        const int yb = ys * kFwSegRows + j * 8;
+        __nv_bfloat16* ocol = x1 + (((size_t)b * g.H + yb) * g.W + (col_ok ? x : 0)) * 16;
+        // 4 chunks of 2 rows x 16 channels; the tcgen05.ld of chunk k+1 is in flight while chunk k is
         // converted (tcgen05.wait::ld waits for ALL outstanding loads, so it comes after the math)
         const uint32_t tbase = tmem_base + ((uint32_t)(quarter * 32) << 16) + ts * 128;
         uint32_t va[32], vb[32];
@@ -491,7 +503,7 @@ conv1_fwd_tc_kernel(const float* __restrict__ in, const float* __restrict__ w1, 
             tmem_ld16(tbase + (k + 1) * 32 + 16, *reinterpret_cast<uint32_t(*)[16]>(&vn[16]));
           }
           const int c0 = k * 32;
-          const bool ok = row_ok && (xb + (c0 >> 4)) < g.W;     // W % 2 == 0: both pixels or neither
+          const bool ok = col_ok && (yb + (c0 >> 4)) < g.H;     // H % 2 == 0: both rows or neither
           uint32_t pk[16];
 #pragma unroll
           for (int e = 0; e < 32; e += 2) {
@@ -505,10 +517,10 @@ conv1_fwd_tc_kernel(const float* __restrict__ in, const float* __restrict__ w1, 
             }
           }
           if (ok) {
-            // lanes are image ROWS here, so every store instruction touches 32 lines: 256-bit stores halve them
-            __nv_bfloat16* o = orow + (c0 >> 4) * 16;
+            // lanes are image columns: each instruction writes 32 consecutive pixels of one row (1 KB contiguous)
+            __nv_bfloat16* o = ocol + (size_t)(c0 >> 4) * g.W * 16;
             st_global_v8(o, &pk[0]);
-            st_global_v8(o + 16, &pk[8]);
+            st_global_v8(o + (size_t)g.W * 16, &pk[8]);
           }
           if (k < 3) tmem_ld_wait();
           else { tc_fence_before(); mbar_arrive(&tempty[ts]); }
@@ -548,8 +560,8 @@ B200_API int b200_conv1_fwd_tc(const void* in_f32, const void* w1, const void* b
   B200_CUDA(attr_err);
   FwGeom g;
   g.B = B; g.H = H; g.W = W;
-  g.nys = (H + kFwRows - 1) / kFwRows;
-  g.nxs = (W + kFwSegPx - 1) / kFwSegPx;
+  g.nys = (H + kFwSegRows - 1) / kFwSegRows;
+  g.nxs = (W + kFwCols - 1) / kFwCols;
   g.nitems = B * g.nys * g.nxs;
   const int nsm = b200_compute_sms();
   const int grid = g.nitems < nsm ? g.nitems : nsm;
