@@ -47,6 +47,14 @@ constexpr int kSmemBytes = kStages * kStageBytes + kStages * kERows * kInW * 4 +
 __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }
+// packed bf16x2 helpers on raw 32-bit words
+__device__ __forceinline__ uint32_t bf2_max(uint32_t a, uint32_t b) {
+  __nv_bfloat162 r = __hmax2(*reinterpret_cast<__nv_bfloat162*>(&a), *reinterpret_cast<__nv_bfloat162*>(&b));
+  return *reinterpret_cast<uint32_t*>(&r);
+}
+__device__ __forceinline__ uint32_t bf2_eq_mask(uint32_t a, uint32_t b) {
+  return __heq2_mask(*reinterpret_cast<__nv_bfloat162*>(&a), *reinterpret_cast<__nv_bfloat162*>(&b));
+}
 // one 32-byte pixel (16 bf16 channels) per 256-bit load: half the LSU wavefronts of two 128-bit loads
 __device__ __forceinline__ void ldg32(const void* p, uint4& a, uint4& b) {
   asm volatile("ld.global.nc.L1::no_allocate.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
@@ -173,36 +181,42 @@ conv1_wgrad_tc_kernel(const float* __restrict__ in, const __nv_bfloat16* __restr
         if (i < kERows * kInW) sI[i] = pin[j];
       }
       // (2) g for this thread's window (from the prefetched registers) -> A[(2r+pl)][k][e]
+      // Two channels per instruction where the math allows it.  A 32-bit word of x1 holds channels (2p, 2p+1):
+      // the 2x2 arg-max runs on packed bf16 (sign-flipped where the BN scale is negative, so it is always a
+      // max; first maximum in row-major order like ATen) instead of four fp32 FMAs + compare/select chains per
+      // channel; only the ReLU test, the routed gradient and the dense BN term use fp32.
       {
         uint32_t o[4][kC1 / 2];
 #pragma unroll
-        for (int c = 0; c < kC1; c += 2) {
-          float res[2][4];
+        for (int cp = 0; cp < kC1 / 2; ++cp) {
+          const float4 k0 = s_const[2 * cp], k1 = s_const[2 * cp + 1];      // (sc, sh, ca, cb)
+          const uint32_t sgn = ((__float_as_uint(k0.x) >> 16) & 0x8000u) | (__float_as_uint(k1.x) & 0x80000000u);
+          uint32_t xw[4], f[4];
 #pragma unroll
-          for (int h = 0; h < 2; ++h) {
-            const int ch = c + h;
-            const float4 k4 = s_const[ch];           // (sc, sh, ca, cb)
-            float xv[4];
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-              const uint32_t w = (&xr[i][ch >> 3].x)[(ch & 7) >> 1];
-              xv[i] = h ? bf16_hi(w) : bf16_lo(w);
-            }
-            int am = 0;
-            float best = fmaf(xv[0], k4.x, k4.y);
-#pragma unroll
-            for (int i = 1; i < 4; ++i) {
-              const float y = fmaf(xv[i], k4.x, k4.y);
-              if (y > best) { best = y; am = i; }
-            }
-            const uint32_t gw = (&gr[ch >> 3].x)[(ch & 7) >> 1];
-            float gv = h ? bf16_hi(gw) : bf16_lo(gw);
-            gv = best > 0.f ? gv * k4.x : 0.f;
-#pragma unroll
-            for (int i = 0; i < 4; ++i) res[h][i] = fmaf(k4.w, xv[i], k4.z) + ((am == i) ? gv : 0.f);
+          for (int i = 0; i < 4; ++i) {
+            xw[i] = (&xr[i][cp >> 2].x)[cp & 3];
+            f[i] = xw[i] ^ sgn;
           }
+          const uint32_t m = bf2_max(bf2_max(f[0], f[1]), bf2_max(f[2], f[3]));
+          const uint32_t e0 = bf2_eq_mask(f[0], m), e1 = bf2_eq_mask(f[1], m), e2 = bf2_eq_mask(f[2], m);
+          uint32_t sel[4];
+          sel[0] = e0;
+          sel[1] = e1 & ~e0;
+          sel[2] = e2 & ~(e0 | e1);
+          sel[3] = ~(e0 | e1 | e2);                      // m is one of the four: if none of the first three, the last
+          const uint32_t mx = m ^ sgn;                   // the pre-BN value at the arg-max
+          const uint32_t gw = (&gr[cp >> 2].x)[cp & 3];
+          const float g0 = fmaf(bf16_lo(mx), k0.x, k0.y) > 0.f ? bf16_lo(gw) * k0.x : 0.f;   // ReLU mask, dy * scale
+          const float g1 = fmaf(bf16_hi(mx), k1.x, k1.y) > 0.f ? bf16_hi(gw) * k1.x : 0.f;
+          // value at the arg-max pixel: dense term + routed gradient, summed in fp32 and rounded ONCE.  (Adding
+          // two already-rounded bf16 numbers loses the small dense term at every arg-max pixel the same way,
+          // a bias that grows with the pixel count and BN backward's cancellation then amplifies: 10 % on dW1.)
+          const uint32_t r2 = pack_bf16x2(fmaf(k0.w, bf16_lo(mx), k0.z) + g0, fmaf(k1.w, bf16_hi(mx), k1.z) + g1);
 #pragma unroll
-          for (int i = 0; i < 4; ++i) o[i][c / 2] = wvalid ? pack_bf16x2(res[0][i], res[1][i]) : 0u;
+          for (int i = 0; i < 4; ++i) {
+            const uint32_t d2 = pack_bf16x2(fmaf(k0.w, bf16_lo(xw[i]), k0.z), fmaf(k1.w, bf16_hi(xw[i]), k1.z));
+            o[i][cp] = wvalid ? ((d2 & ~sel[i]) | (r2 & sel[i])) : 0u;
+          }
         }
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
