@@ -1,0 +1,11 @@
+#!/bin/bash
+# Round-end rehearsal on one GPU: full gpu test tier, smoke(), bench both arms.
+mkdir -p gpurun_out
+L=gpurun_out/final.log
+: > $L
+run() { echo "=== $*" >> $L; timeout ${TMO:-900} "$@" >> $L 2>&1; echo "=== rc=$?" >> $L; }
+run python -m pytest tests -x -q -m gpu -p no:cacheprovider
+run python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')"
+run python bench.py --steps 30 --warmup 5
+TMO=600 run python bench.py --impl reference --steps 3 --warmup 3
+grep -E "passed|failed|rc=|rror|smoke ok" $L | head -20; grep -E "^\{" $L | cut -c1-1500
