@@ -68,7 +68,8 @@ def timed_loop(step_fn, K, W, sync_all, max_over_ranks, local_rank, sample_clock
     torch.cuda.synchronize()
     ms = start.elapsed_time(end) / K
     if sampler:
-        time.sleep(0.15)
+        if getattr(sampler, "_thread", None) is None:
+            time.sleep(0.15)              # nvidia-smi fallback: let its 100 ms poll catch the tail of the region
         sampler.__exit__(None, None, None)
     sync_all()
     return max_over_ranks(ms), (sampler.summary() if sampler else None)
