@@ -28,7 +28,7 @@ B200_API int b200_sm_count() { return b200_num_sms(); }
 // scheduled CTAs start late behind the collective.
 static int g_reserved_sms = 0;
 B200_API int b200_set_reserved_sms(int n) {
-  if (n < 0 || n > 64) return b200_fail(-2, "reserved SM count must be in [0, 64]");
+  if (n < 0 || n >= b200_num_sms()) return b200_fail(-2, "reserved SM count must be in [0, SM count - 1]");
   g_reserved_sms = n;
   return 0;
 }

@@ -139,6 +139,68 @@ def test_conv2_fwd_tc(ops, shape, tc_version):
     report("conv2_fwd_tc sumsq", rel(s[32:], (r ** 2).sum((0, 1, 2))), 1e-4)
 
 
+@pytest.fixture
+def few_ctas(ops):
+    """Leave the persistent tcgen05 kernels 2 SMs: every CTA then walks several long work items back to back, so
+    the accumulator / operand rings wrap many times and carry their position across items - the situation of the
+    full-size step, which the small shapes on 148 SMs (one short item per CTA) never reach."""
+    ops.set_reserved_sms(ops.sm_count() - 2)
+    yield
+    ops.set_reserved_sms(0)
+
+
+@pytest.mark.parametrize("ver", [3, 2])
+def test_conv2_tc_long_items(ops, few_ctas, ver):
+    ops.conv_tc_set_version(ver)
+    try:
+        B, H, W = 3, 150, 300
+        g = torch.Generator(device=DEV).manual_seed(21)
+        x = torch.randn(B, 16, H, W, device=DEV, generator=g)
+        w = torch.randn(32, 16, 5, 5, device=DEV, generator=g) * 0.05
+        b = torch.randn(32, device=DEV, generator=g) * 0.1
+        xb = nhwc_bf16(x)
+        out = torch.full((B, H, W, 32), float("nan"), device=DEV, dtype=torch.bfloat16)
+        part = torch.zeros(ops.conv_tc_max_grid(), 64, device=DEV)
+        n = ops.conv2_fwd_tc(xb, w, b, out, part)
+        torch.cuda.synchronize()
+        assert n <= 2
+        ref = F.conv2d(to_nchw(xb), w.to(torch.bfloat16).float(), b, padding=2)
+        report(f"conv2_fwd_tc long items v{ver}", rel(to_nchw(out), ref), 5e-3)
+        s = part[:n].double().sum(0)
+        report("conv2_fwd_tc long items sum", rel(s[:32], out.float().double().sum((0, 1, 2))), 1e-4)
+        dy = nhwc_bf16(torch.randn(B, 32, H, W, device=DEV, generator=g))
+        dx = torch.full((B, H, W, 16), float("nan"), device=DEV, dtype=torch.bfloat16)
+        ops.conv2_dgrad_tc(dy, w, dx)
+        torch.cuda.synchronize()
+        refd = torch.nn.grad.conv2d_input((B, 16, H, W), w.to(torch.bfloat16).float(), to_nchw(dy), padding=2)
+        report(f"conv2_dgrad_tc long items v{ver}", rel(to_nchw(dx), refd), 5e-3)
+        pw = torch.zeros(ops.conv_tc_max_grid(), 32 * 16 * 25, device=DEV)
+        dw = torch.zeros(32, 16, 5, 5, device=DEV)
+        ops.conv2_wgrad_tc(xb, dy, pw, dw)
+        torch.cuda.synchronize()
+        refw = torch.nn.grad.conv2d_weight(to_nchw(xb), (32, 16, 5, 5), to_nchw(dy), padding=2)
+        report(f"conv2_wgrad_tc long items v{ver}", rel(dw, refw), 5e-3)
+    finally:
+        ops.conv_tc_set_version(3)
+
+
+def test_conv1_tc_many_items_per_cta(ops, few_ctas):
+    """conv1 forward on 2 CTAs: each walks ~10 tiles, so the input-stage and TMEM rings carry across items."""
+    B, H, W = 2, 150, 300
+    g = torch.Generator(device=DEV).manual_seed(22)
+    x = torch.rand(B, H, W, device=DEV, generator=g)
+    w = torch.randn(16, 1, 5, 5, device=DEV, generator=g) * 0.2
+    b = torch.randn(16, device=DEV, generator=g) * 0.1
+    x1 = torch.full((B, H, W, 16), float("nan"), device=DEV, dtype=torch.bfloat16)
+    part = torch.zeros(ops.conv1_fwd_grid(), 32, device=DEV)
+    n = ops.conv1_fwd_tc(x, w, b, x1, part)
+    torch.cuda.synchronize()
+    assert n <= 2
+    report("conv1_fwd[tc] many items", rel(to_nchw(x1), F.conv2d(x[:, None], w, b, padding=2)), 4e-3)
+    s = part[:n].double().sum(0)
+    report("conv1_fwd[tc] many items sum", rel(s[:16], x1.float().double().sum((0, 1, 2))), 1e-5)
+
+
 @pytest.mark.parametrize("shape", [(2, 24, 200), (1, 50, 128), (1, 2, 24), (2, 133, 260)])
 def test_conv2_dgrad_tc(ops, shape, tc_version):
     B, H, W = shape

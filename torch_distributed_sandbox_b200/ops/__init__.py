@@ -69,6 +69,11 @@ def sm_count() -> int:
     return int(_lib().b200_sm_count())
 
 
+def set_reserved_sms(n: int) -> None:
+    """SMs the persistent tcgen05 kernels leave to an overlapped collective (parallel/engine_sync.py); 0 = none."""
+    _native.check(_lib().b200_set_reserved_sms(int(n)), "set_reserved_sms")
+
+
 # ---- grid sizes (callers size their partial buffers with these) ------------
 def conv1_fwd_grid() -> int:
     return int(_lib().b200_conv1_fwd_grid())
