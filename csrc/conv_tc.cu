@@ -438,8 +438,11 @@ struct RsCfg {
   static constexpr int kWChunkBytes = kNB * 16;              // one 8-channel k-chunk of all n rows
   static constexpr int kWStepBytes = 2 * kWChunkBytes;       // one (dx, kk) B tile
   static constexpr int kWBytes = 5 * kKSteps * kWStepBytes;  // == 25*CIN*COUT*2
-  static constexpr int kTStages = 16;
-  static constexpr int kTmemCols = kTStages * COUT;          // 512 (COUT=32) / 256 (COUT=16)
+  // The accumulator ring takes all 512 TMEM columns (16 slots at COUT=32, 32 at COUT=16).  A five-slot window that
+  // reaches the end of the ring has to be split into two MMAs (a D range past column 511 faults), and each half
+  // re-reads the whole A operand, so the longer ring of dgrad halves how often that happens.
+  static constexpr int kTStages = 512 / COUT;
+  static constexpr int kTmemCols = kTStages * COUT;          // 512
   static constexpr int kSmemBytes = kWBytes + kSlots * kSlotBytes + 4096 + 128;
   static_assert(kWBytes % 128 == 0 && kSlotBytes % 128 == 0, "alignment");
   static_assert(kTmemCols <= 512 && (kTmemCols & (kTmemCols - 1)) == 0, "TMEM columns");
