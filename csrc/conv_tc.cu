@@ -789,7 +789,12 @@ conv5x5_rs_kernel(const __grid_constant__ CUtensorMap tm_act, const __nv_bfloat1
 // pairs with (y = r-2 .. r+2) are five CONSECUTIVE slots of the dx2 ring, i.e. 20 consecutive
 // 8-channel planes, i.e. one MN-major B operand with N = 160.  D[pl][(dx,ci8)][(jj,co)], dy = 4-jj.
 constexpr int kWg2SlotsA = 12, kWg2SlotsB = 16;      // rows in flight: the rings are the cp.async pipeline depth
-constexpr int kWg2SmemBytes = kWg2SlotsA * kWgSlotABytes + kWg2SlotsB * kWgSlotBBytes + 1024 + 128;
+// The five dx2 rows of a window must be CONTIGUOUS in shared memory (one B operand, N = 160).  Slots 16..19 mirror
+// slots 0..3 (the feed writes those rows twice), so a window that starts in slots 12..15 runs on into the mirror
+// instead of wrapping: one MMA per K-step for every row.  (Splitting the wrapped windows into two MMAs re-read A and
+// paid the 48-cycle MMA floor twice on a quarter of the rows of a kernel that is bound by the MMAs themselves.)
+constexpr int kWg2PhysB = kWg2SlotsB + 4;
+constexpr int kWg2SmemBytes = kWg2SlotsA * kWgSlotABytes + kWg2PhysB * kWgSlotBBytes + 1024 + 128;
 
 template <bool LDGSTS>
 __global__ void __launch_bounds__(kThreads, 1)
@@ -800,7 +805,7 @@ conv5x5_wgrad_rs_kernel(const __grid_constant__ CUtensorMap tm_act, const __grid
   uint8_t* smem = smem_raw + ((128u - (smem_u32(smem_raw) & 127u)) & 127u);
   uint8_t* s_a = smem;
   uint8_t* s_b = smem + kWg2SlotsA * kWgSlotABytes;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(s_b + kWg2SlotsB * kWgSlotBBytes);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_b + kWg2PhysB * kWgSlotBBytes);
   uint64_t* fullA = bars;
   uint64_t* emptyA = fullA + kWg2SlotsA;
   uint64_t* fullB = emptyA + kWg2SlotsA;
@@ -842,6 +847,7 @@ conv5x5_wgrad_rs_kernel(const __grid_constant__ CUtensorMap tm_act, const __grid
             const uint32_t slot = gb % kWg2SlotsB, use = gb / kWg2SlotsB;
             mbar_wait(&emptyB[slot], (use & 1) ^ 1);
             planB.copy(s_b + slot * kWgSlotBBytes, dxo, b, r0 - 2 + i, g.H, g.W);
+            if (slot < 4) planB.copy(s_b + (kWg2SlotsB + slot) * kWgSlotBBytes, dxo, b, r0 - 2 + i, g.H, g.W);   // mirror
             cp_async_mbar_arrive_noinc(&fullB[slot]);
             ++gb;
           }
@@ -867,11 +873,17 @@ conv5x5_wgrad_rs_kernel(const __grid_constant__ CUtensorMap tm_act, const __grid
           {   // dx2 row r0-2+i (zero-filled outside the image)
             const uint32_t slot = gb % kWg2SlotsB, use = gb / kWg2SlotsB;
             mbar_wait(&emptyB[slot], (use & 1) ^ 1);
-            mbar_expect_tx(&fullB[slot], kWgSlotBBytes);
+            mbar_expect_tx(&fullB[slot], slot < 4 ? 2 * kWgSlotBBytes : kWgSlotBBytes);
             uint8_t* dst = s_b + slot * kWgSlotBBytes;
 #pragma unroll
             for (int p = 0; p < 4; ++p)
               tma_load_5d(dst + p * kWgPlaneBBytes, &tm_dxo, &fullB[slot], 0, p, x0, r0 - 2 + i, b);
+            if (slot < 4) {   // mirror slot (see kWg2PhysB)
+              uint8_t* dst2 = s_b + (kWg2SlotsB + slot) * kWgSlotBBytes;
+#pragma unroll
+              for (int p = 0; p < 4; ++p)
+                tma_load_5d(dst2 + p * kWgPlaneBBytes, &tm_dxo, &fullB[slot], 0, p, x0, r0 - 2 + i, b);
+            }
             ++gb;
           }
           if (i >= 4) {   // act row r0+i-4: all five dx2 rows it needs are now in flight
@@ -907,22 +919,18 @@ conv5x5_wgrad_rs_kernel(const __grid_constant__ CUtensorMap tm_act, const __grid
         mbar_wait(&fullA[slotA], (ga / kWg2SlotsA) & 1);
         tc_fence_after();
         const uint32_t s0 = (gbase + i) % kWg2SlotsB;          // ring slot of the window's first row
-        const int n1 = min(5, (int)(kWg2SlotsB - s0));
         const uint32_t arow = a_base + slotA * (kWgSlotABytes >> 4);
-        const uint32_t brow1 = b_base + s0 * (kWgSlotBBytes >> 4);
+        const uint32_t brow = b_base + s0 * (kWgSlotBBytes >> 4);   // slots s0..s0+4 (<= 19: mirror slots) are contiguous
         const uint32_t acc0 = first ? 0u : 1u;
         if (elect_one()) {
 #pragma unroll
           for (int kb = 0; kb < kBM / 16; ++kb) {
             const uint32_t acc = kb == 0 ? acc0 : 1u;
-            const uint64_t b1 = ((uint64_t)b_hi << 32) | (uint64_t)(brow1 + kb * 16);
-            const uint64_t b2 = ((uint64_t)b_hi << 32) | (uint64_t)(b_base + kb * 16);
+            const uint64_t bd = ((uint64_t)b_hi << 32) | (uint64_t)(brow + kb * 16);
 #pragma unroll
             for (int pl = 0; pl < 2; ++pl) {
               const uint64_t a_desc = ((uint64_t)a_hi << 32) | (uint64_t)(arow + pl * (kPlaneBytes >> 4) + kb * 16);
-              umma_bf16(tmem_base + pl * 160, a_desc, b1, idesc0 | ((uint32_t)((n1 * 32) >> 3) << 17), acc);
-              if (n1 < 5)
-                umma_bf16(tmem_base + pl * 160 + n1 * 32, a_desc, b2, idesc0 | ((uint32_t)(((5 - n1) * 32) >> 3) << 17), acc);
+              umma_bf16(tmem_base + pl * 160, a_desc, bd, idesc0 | ((uint32_t)(160 >> 3) << 17), acc);
             }
           }
           umma_commit(&emptyA[slotA]);
