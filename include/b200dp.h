@@ -81,7 +81,7 @@ int b200_conv1_wgrad_tc(const void* in_f32, const void* x1_bf16, const void* dp1
 int b200_conv_tc_max_grid(void);
 int b200_conv_tc_set_version(int v);   /* 1 tap-stationary+TMA, 2 row-stationary+TMA, 3 row-stationary+cp.async (default) */
 int b200_conv_tc_get_version(void);
-int b200_set_reserved_sms(int n);      /* SM partition for an overlapped collective (DDP); 0 = none */
+int b200_set_reserved_sms(int n);      /* SM partition for an overlapped collective (DDP); 0 = none, at most SM count - 1 */
 int b200_get_reserved_sms(void);
 int b200_conv2_fwd_tc(const void* p1_bf16, const void* w2, const void* b2, void* x2_bf16, void* partials, int B, int H,
                       int W, int* nparts_out, void* stream);
