@@ -55,6 +55,53 @@ def _stock_train(ref, local_rank, world, steps, batch):
     return int(m.group(1)) * 3600 + int(m.group(2)) * 60 + float(m.group(3))
 
 
+def _stock_main(argv):
+    """Child process of the stock-loader stage (world 1 only): its own rendezvous on a fresh port
+    for every train() call, nothing inherited from a torchrun agent.  Prints one JSON line."""
+    ref_dir, steps, batch, image = argv[0], int(argv[1]), int(argv[2]), int(argv[3])
+    for k in list(os.environ):
+        if k.startswith(("TORCHELASTIC_", "TORCH_NCCL_", "PET_")) or k in (
+                "RANK", "LOCAL_RANK", "WORLD_SIZE", "GROUP_RANK", "ROLE_RANK", "LOCAL_WORLD_SIZE", "ROLE_WORLD_SIZE",
+                "GROUP_WORLD_SIZE", "ROLE_NAME", "MASTER_PORT", "MASTER_ADDR"):
+            del os.environ[k]
+    sys.path.insert(0, ref_dir)
+    import mnist_distributed as ref
+    if image != 3000:
+        ref.IMAGE_SHAPE = [image, image]
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    out = {}
+    for tag, n in (("warmup", 2), ("timed", steps)):
+        os.environ["MASTER_PORT"] = ref.find_free_port()
+        out[tag] = _stock_train(ref, 0, 1, n, batch)
+    print(json.dumps(out), flush=True)
+
+
+def _stock_stage(ref_dir, a, local_rank, timeout_s):
+    """Stock train() (torchvision loader + PIL resize) timed in a fresh process under a hard timeout.
+    A process group is never re-initialised on the launcher's store: round 1 did that after a
+    destroy_process_group() and hung every world > 1 run (ranks dialled a closed NCCL bootstrap socket)."""
+    import subprocess
+    env = dict(os.environ)
+    vis = env.get("CUDA_VISIBLE_DEVICES")
+    env["CUDA_VISIBLE_DEVICES"] = vis.split(",")[local_rank] if vis else str(local_rank)
+    cmd = [sys.executable, os.path.abspath(__file__), "--stock", ref_dir, str(a.stock_loader_steps), str(a.batch),
+           str(a.image)]
+    try:
+        r = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=timeout_s)
+    except subprocess.TimeoutExpired:
+        return {"error": f"stock train() did not finish within {timeout_s} s (killed)"}
+    line = next((ln for ln in reversed(r.stdout.splitlines()) if ln.startswith("{")), None)
+    if r.returncode != 0 or line is None:
+        return {"error": f"rc={r.returncode}: {(r.stderr or r.stdout)[-300:]}"}
+    secs = json.loads(line).get("timed")
+    if not secs:
+        return {"error": "no 'Training complete in' line"}
+    return {"value": a.stock_loader_steps * a.batch / secs, "unit": "img/s", "steps": a.stock_loader_steps,
+            "seconds": secs, "world": 1,
+            "note": "stock train(): torchvision MNIST + PIL Resize(3000) + ToTensor on the CPU, num_workers=0, "
+                    "180 MB H2D per step, per-step new_group; own process, own rendezvous"}
+
+
 def run(a, ref_dir, ranks, timed_loop):
     rank, local_rank, world = ranks
     sys.path.insert(0, ref_dir)
@@ -122,22 +169,19 @@ def run(a, ref_dir, ranks, timed_loop):
     ms_e2e, _ = timed_loop(e2e_step, a.steps, max(3, a.warmup // 2), sync_all, max_over_ranks, local_rank,
                            sample_clocks=False)
     peak = torch.cuda.max_memory_allocated() / 2 ** 30
-    dist.destroy_process_group()
+    final_loss = last.get("loss_val")
+    if rank == 0:                                         # the measured numbers, on stderr at once: never lost
+        print(f"[ref_harness] world={world} ms_per_step={ms:.3f} e2e_ms={ms_e2e:.3f}", file=sys.stderr, flush=True)
+    dist.barrier()
+    dist.destroy_process_group()                          # last use of the launcher's store in this process
     del model, optimizer, dev_imgs, host_imgs
     torch.cuda.empty_cache()
 
     stock = None
-    if a.stock_loader_steps > 0:
-        try:
-            _stock_train(ref, local_rank, world, 2, B)                       # warm-up (cuDNN, allocator)
-            secs = _stock_train(ref, local_rank, world, a.stock_loader_steps, B)
-            if secs:
-                stock = {"value": a.stock_loader_steps * B * world / secs, "unit": "img/s",
-                         "steps": a.stock_loader_steps, "seconds": secs,
-                         "note": "stock train(): torchvision MNIST + PIL Resize(3000) + ToTensor on the CPU, "
-                                 "num_workers=0, 180 MB H2D per step, per-step new_group"}
-        except Exception as e:                                               # pragma: no cover
-            stock = {"error": f"{type(e).__name__}: {e}"[:300]}
+    if a.stock_loader_steps > 0 and world == 1:
+        stock = _stock_stage(ref_dir, a, local_rank, timeout_s=int(os.environ.get("B200DP_STOCK_TIMEOUT", "90")))
+    elif a.stock_loader_steps > 0:
+        stock = {"skipped": "stock train() is timed at world 1 only (see e2e_stock_loader of the 1-GPU line)"}
     if rank != 0:
         return
     gb = B * world
@@ -152,6 +196,11 @@ def run(a, ref_dir, ranks, timed_loop):
         "e2e": {"value": gb / ms_e2e * 1e3, "unit": "img/s", "ms_per_step": ms_e2e,
                 "h2d_bytes_per_step": int(B * S * S * 4 + B * 8), "d2h_bytes_per_step": 4,
                 "note": "pre-resized fp32 batch in pinned host memory (the reference's CPU resize is not charged)"},
-        "e2e_stock_loader": stock, "gpu_launches": None, "final_loss": last.get("loss_val"),
+        "e2e_stock_loader": stock, "gpu_launches": None, "final_loss": final_loss,
         "peak_mem_gib": round(peak, 2),
     }))
+
+
+if __name__ == "__main__":
+    if len(sys.argv) >= 6 and sys.argv[1] == "--stock":
+        _stock_main(sys.argv[2:])

@@ -30,6 +30,14 @@ inline int b200_fail(int code, const char* fmt, ...) {
   } while (0)
 #define B200_LAUNCH_CHECK() B200_CUDA(cudaGetLastError())
 
+// Opt a kernel in to > 48 KB of dynamic shared memory.  The attribute is per DEVICE, so it is set before every
+// launch (a sub-microsecond driver call) rather than once per process: a second GPU used from the same process
+// would otherwise fail its launches with "invalid argument".
+template <typename Kern>
+inline cudaError_t set_max_smem(Kern kern, int bytes) {
+  return cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+}
+
 int b200_num_sms();      // SM count of the current device (cached per device)
 int b200_compute_sms();  // b200_num_sms() minus the SMs reserved for an overlapped collective (b200_set_reserved_sms)
 

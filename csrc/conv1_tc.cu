@@ -274,6 +274,213 @@ conv1_wgrad_tc_kernel(const float* __restrict__ in, const __nv_bfloat16* __restr
   if (warp == 0) { __syncwarp(); tmem_dealloc<kTmemCols>(tmem_base); }
 }
 
+
+// ------------------------------------------------------------------------------------------------
+// The same GEMM for fp32 storage (precision "tf32"): x1 and dp1 are fp32, the conv1-output gradient g
+// and the expanded input E are written to shared memory as fp32 rounded to TF32, and the contraction
+// runs as kind::tf32 MMAs (K = 8 pixels).  MN-major TF32 operands have one legal shared-memory layout
+// (128-byte pixel rows of 32 MN elements, 32-byte units swizzled by the row index: sw32_off in ptx.cuh),
+// and a strip is 64 pixels wide to keep the tiles the size of the bf16 kernel's:
+//   A (M=128)  m = 16*r + c:    atom r/2,  unit 2*(r%2) + c/8   [atom][pixel k][128 B]   4 x 8 KB
+//   B (N=96)   n = 8*r' + dxs:  atom r'/4, unit r'%4            [atom][pixel k][128 B]   3 x 8 KB
+// D has the same (m, n) meaning as above, so the extraction is shared.  Producers work per
+// (2x2 window, 8 channels) in plain fp32: y = sc*x + sh, first maximum in row-major order, ReLU mask,
+// g = ca + cb*x (+ sc*dp at the arg-max).
+namespace tf {
+constexpr int kXW = 64;
+constexpr int kAtom = kXW * 128;                      // 8 KB: 32 MN elements over the strip
+constexpr int kABytes = 4 * kAtom;                    // 32 KB
+constexpr int kEBytes = 3 * kAtom;                    // 24 KB
+constexpr int kStageBytes = kABytes + kEBytes;
+constexpr int kInW = kXW + 8;                         // staged fp32 input row: x0-2 .. x0+69
+constexpr int kSmemBytes = kStages * kStageBytes + kStages * kERows * kInW * 4 + 1024 + 1024;
+}  // namespace tf
+
+__device__ __forceinline__ void ldg32f(const float* p, float (&v)[8]) {
+  uint32_t u[8];
+  asm volatile("ld.global.nc.L1::no_allocate.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=r"(u[0]), "=r"(u[1]), "=r"(u[2]), "=r"(u[3]), "=r"(u[4]), "=r"(u[5]), "=r"(u[6]), "=r"(u[7]) : "l"(p));
+#pragma unroll
+  for (int i = 0; i < 8; ++i) v[i] = __uint_as_float(u[i]);
+}
+
+__global__ void __launch_bounds__(kWgThreads, 1)
+conv1_wgrad_tf32_kernel(const float* __restrict__ in, const float* __restrict__ x1,
+                        const float* __restrict__ dp1, const float* __restrict__ bn,
+                        const float* __restrict__ red, float* __restrict__ partials, WgGeom g) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);    // swizzle atoms: 1 KB aligned
+  uint8_t* s_stage = smem;                                                          // [kStages][A | E]
+  float* s_in = reinterpret_cast<float*>(smem + kStages * tf::kStageBytes);         // [kStages][12][72]
+  float4* s_const = reinterpret_cast<float4*>(s_in + kStages * kERows * tf::kInW);  // [16] (sc, sh, ca, cb)
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_const + kC1);
+  uint64_t* full = bars;
+  uint64_t* empty = bars + kStages;
+  uint64_t* done = empty + kStages;
+  uint32_t* s_tmem = reinterpret_cast<uint32_t*>(done + 1);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < kStages; ++i) { mbar_init(&full[i], kProducerWarps); mbar_init(&empty[i], 1); }
+    mbar_init(done, 1);
+    mbar_fence_init();
+  }
+  if (warp == 0) tmem_alloc<kTmemCols>(s_tmem);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *s_tmem;
+  const int Ho = g.H / 2, Wo = g.W / 2;
+
+  if (warp == 0) {
+    constexpr uint32_t idesc = umma_idesc(2, 128, kNCols, 1, 1);
+    const uint64_t tmpl = smem_desc(0, tf::kAtom, 512, 1);           // MN-major SW128_32B: LBO = next atom, SBO = next 4 rows
+    const uint32_t hi = (uint32_t)(tmpl >> 32), lo0 = (uint32_t)tmpl;
+    uint32_t n = 0;
+    for (int item = blockIdx.x; item < g.nitems; item += gridDim.x, ++n) {
+      const uint32_t s = n % kStages;
+      mbar_wait(&full[s], (n / kStages) & 1);
+      tc_fence_after();
+      const uint32_t a_lo = lo0 + (smem_u32(s_stage + s * tf::kStageBytes) >> 4);
+      const uint32_t b_lo = a_lo + (tf::kABytes >> 4);
+      const uint32_t acc0 = n == 0 ? 0u : 1u;
+      if (elect_one()) {
+#pragma unroll
+        for (int kb = 0; kb < tf::kXW / 8; ++kb)
+          umma_tf32(tmem_base, ((uint64_t)hi << 32) | (uint64_t)(a_lo + kb * 64),
+                    ((uint64_t)hi << 32) | (uint64_t)(b_lo + kb * 64), idesc, kb == 0 ? acc0 : 1u);
+        umma_commit(&empty[s]);
+      }
+      __syncwarp();
+    }
+    if (elect_one()) umma_commit(done);
+    __syncwarp();
+  } else {
+    const int pt = threadIdx.x - 32;                 // 0..255
+    const int half = pt & 1, w = pt >> 1;            // 8 channels (half) of window w
+    const int wr = w >> 5, wc = w & 31;              // window row 0..3, window col 0..31
+    for (int c = pt; c < kC1; c += kProducers) {
+      const float s_ = bn[c], mu = bn[2 * kC1 + c], rs = bn[3 * kC1 + c];
+      const float mdy = red[c], mdyx = red[kC1 + c];
+      s_const[c] = make_float4(s_, bn[kC1 + c], s_ * (rs * mdyx * mu - mdy), -s_ * rs * mdyx);
+    }
+    named_bar_sync(1, kProducers);
+    constexpr int kInTot = kERows * tf::kInW;                               // 864
+    constexpr int kInPer = (kInTot + kProducers - 1) / kProducers;          // 4 staged floats per thread
+
+    struct Regs { float xr[4][8], gr[8], pin[kInPer]; bool wvalid; };
+    Regs nx;
+    nx.wvalid = false;
+    auto issue_loads = [&](int item) {
+      const int strip = item % g.nstrips;
+      const int grp = (item / g.nstrips) % g.ngroups;
+      const int b = item / (g.nstrips * g.ngroups);
+      const int y0 = grp * kRows, x0 = strip * tf::kXW;
+#pragma unroll
+      for (int j = 0; j < kInPer; ++j) {
+        const int i = pt + j * kProducers;
+        const int rr = i / tf::kInW, cc = i - rr * tf::kInW;
+        const int gy = y0 - 2 + rr, gx = x0 - 2 + cc;
+        nx.pin[j] = (i < kInTot && gy >= 0 && gy < g.H && gx >= 0 && gx < g.W)
+                        ? __ldg(in + ((size_t)b * g.H + gy) * g.W + gx) : 0.f;
+      }
+      const int gy = y0 + 2 * wr, gx = x0 + 2 * wc;
+      nx.wvalid = gy < g.H && gx < g.W;
+      if (nx.wvalid) {
+        const float* xb = x1 + (((size_t)b * g.H + gy) * g.W + gx) * kC1 + half * 8;
+        ldg32f(xb, nx.xr[0]);
+        ldg32f(xb + kC1, nx.xr[1]);
+        ldg32f(xb + (size_t)g.W * kC1, nx.xr[2]);
+        ldg32f(xb + (size_t)g.W * kC1 + kC1, nx.xr[3]);
+        ldg32f(dp1 + (((size_t)b * Ho + (gy >> 1)) * Wo + (gx >> 1)) * kC1 + half * 8, nx.gr);
+      }
+    };
+    if ((int)blockIdx.x < g.nitems) issue_loads(blockIdx.x);
+    uint32_t n = 0;
+    for (int item = blockIdx.x; item < g.nitems; item += gridDim.x, ++n) {
+      const uint32_t s = n % kStages;
+      uint8_t* sA = s_stage + s * tf::kStageBytes;
+      uint8_t* sE = sA + tf::kABytes;
+      float* sI = s_in + s * kInTot;
+      const Regs cur = nx;
+      if (item + (int)gridDim.x < g.nitems) issue_loads(item + gridDim.x);
+      mbar_wait(&empty[s], ((n / kStages) & 1) ^ 1);
+#pragma unroll
+      for (int j = 0; j < kInPer; ++j) {
+        const int i = pt + j * kProducers;
+        if (i < kInTot) sI[i] = cur.pin[j];
+      }
+      {
+        float o[4][8];
+#pragma unroll
+        for (int cc = 0; cc < 8; ++cc) {
+          const float4 k = s_const[half * 8 + cc];                // (sc, sh, ca, cb)
+          float best = fmaf(cur.xr[0][cc], k.x, k.y);
+          int am = 0;
+#pragma unroll
+          for (int i = 1; i < 4; ++i) {
+            const float y = fmaf(cur.xr[i][cc], k.x, k.y);
+            if (y > best) { best = y; am = i; }
+          }
+          const float gq = best > 0.f ? cur.gr[cc] * k.x : 0.f;   // ReLU mask, dy * scale, routed to the arg-max
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const float v = fmaf(k.w, cur.xr[i][cc], k.z) + (am == i ? gq : 0.f);
+            o[i][cc] = cur.wvalid ? to_tf32_rna(v) : 0.f;
+          }
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int kx = 2 * wc + (i & 1);                       // image row r = 2*wr + (i >> 1): atom wr
+          uint8_t* dst = sA + wr * tf::kAtom + sw32_off(kx, 2 * (i >> 1) + half);
+          *reinterpret_cast<float4*>(dst) = make_float4(o[i][0], o[i][1], o[i][2], o[i][3]);
+          *reinterpret_cast<float4*>(dst + 16) = make_float4(o[i][4], o[i][5], o[i][6], o[i][7]);
+        }
+      }
+      named_bar_sync(1, kProducers);                 // staged input complete
+      // expanded input E[r'][k][dxs]: 12 rows x 64 pixels x 2 pieces of 16 B, 6 per thread
+#pragma unroll
+      for (int j = 0; j < (2 * kERows * tf::kXW) / kProducers; ++j) {
+        const int idx = pt + j * kProducers;
+        const int kx = idx & (tf::kXW - 1), c2 = idx >> 6, rr = c2 >> 1;
+        const float* src = sI + rr * tf::kInW + kx + 4 * (c2 & 1);          // in[.., x0 + kx - 2 + dxs]
+        *reinterpret_cast<float4*>(sE + (rr >> 2) * tf::kAtom + sw32_off(kx, rr & 3) + 16 * (c2 & 1)) =
+            make_float4(to_tf32_rna(src[0]), to_tf32_rna(src[1]), to_tf32_rna(src[2]), to_tf32_rna(src[3]));
+      }
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&full[s]);
+    }
+  }
+  // extraction: identical (m, n) meaning to the bf16 kernel
+  float* s_T = reinterpret_cast<float*>(s_stage);
+  constexpr int kTP = kNCols + 1;
+  if (warp >= 1 && warp <= 4) {
+    mbar_wait(done, 0);
+    tc_fence_after();
+    const int q = warp & 3, m = q * 32 + lane;
+#pragma unroll 1
+    for (int c0 = 0; c0 < kNCols; c0 += 16) {
+      uint32_t v[16];
+      tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + c0, v);
+      tmem_ld_wait();
+#pragma unroll
+      for (int j = 0; j < 16; ++j) s_T[m * kTP + c0 + j] = __uint_as_float(v[j]);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  for (int t = threadIdx.x; t < kC1 * 25; t += kWgThreads) {
+    const int c = t / 25, tap = t % 25, dy = tap / 5, dxs = tap % 5;
+    float a = 0.f;
+#pragma unroll
+    for (int r = 0; r < kRows; ++r) a += s_T[(16 * r + c) * kTP + (r + dy) * 8 + dxs];
+    partials[(size_t)blockIdx.x * 400 + t] = a;
+  }
+  if (warp == 0) { __syncwarp(); tmem_dealloc<kTmemCols>(tmem_base); }
+}
+
 }  // namespace
 
 // Same contract as b200_conv1_wgrad (partials: [b200_conv1_wgrad_grid()][400] scratch).
@@ -281,12 +488,7 @@ B200_API int b200_conv1_wgrad_tc(const void* in_f32, const void* x1, const void*
                                  void* partials, void* dw1, int B, int H, int W, float gscale, void* stream) {
   B200_CHECK(H % 2 == 0 && W % 2 == 0, "conv1_wgrad_tc: H and W must be even");
   cudaStream_t s = (cudaStream_t)stream;
-  static std::once_flag once;
-  static cudaError_t attr_err = cudaSuccess;
-  std::call_once(once, [&] {
-    attr_err = cudaFuncSetAttribute(conv1_wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
-  });
-  B200_CUDA(attr_err);
+  B200_CUDA(set_max_smem(conv1_wgrad_tc_kernel, kSmemBytes));
   WgGeom g;
   g.B = B; g.H = H; g.W = W;
   g.nstrips = (W + kXW - 1) / kXW;
@@ -297,6 +499,27 @@ B200_API int b200_conv1_wgrad_tc(const void* in_f32, const void* x1, const void*
   conv1_wgrad_tc_kernel<<<grid, kWgThreads, kSmemBytes, s>>>((const float*)in_f32, (const __nv_bfloat16*)x1,
                                                              (const __nv_bfloat16*)dp1, (const float*)bn,
                                                              (const float*)red, (float*)partials, g);
+  B200_LAUNCH_CHECK();
+  return b200_reduce_partials(partials, grid, 400, dw1, gscale, stream);
+}
+
+// fp32 storage, kind::tf32 (same contract; x1 and dp1 are fp32).
+B200_API int b200_conv1_wgrad_tc_f32(const void* in_f32, const void* x1, const void* dp1, const void* bn,
+                                     const void* red, void* partials, void* dw1, int B, int H, int W, float gscale,
+                                     void* stream) {
+  B200_CHECK(H % 2 == 0 && W % 2 == 0, "conv1_wgrad_tc_f32: H and W must be even");
+  cudaStream_t s = (cudaStream_t)stream;
+  B200_CUDA(set_max_smem(conv1_wgrad_tf32_kernel, tf::kSmemBytes));
+  WgGeom g;
+  g.B = B; g.H = H; g.W = W;
+  g.nstrips = (W + tf::kXW - 1) / tf::kXW;
+  g.ngroups = (H + kRows - 1) / kRows;
+  g.nitems = B * g.nstrips * g.ngroups;
+  const int nsm = b200_compute_sms();
+  const int grid = g.nitems < nsm ? g.nitems : nsm;
+  conv1_wgrad_tf32_kernel<<<grid, kWgThreads, tf::kSmemBytes, s>>>((const float*)in_f32, (const float*)x1,
+                                                                   (const float*)dp1, (const float*)bn,
+                                                                   (const float*)red, (float*)partials, g);
   B200_LAUNCH_CHECK();
   return b200_reduce_partials(partials, grid, 400, dw1, gscale, stream);
 }
@@ -346,9 +569,10 @@ struct FwGeom {
   int nys, nxs, nitems;
 };
 
+template <typename OT>       // OT = storage type of the output: __nv_bfloat16 or float
 __global__ void __launch_bounds__(kFwThreads, 1)
 conv1_fwd_tc_kernel(const float* __restrict__ in, const float* __restrict__ w1, const float* __restrict__ b1,
-                    __nv_bfloat16* __restrict__ x1, float* __restrict__ partials, FwGeom g) {
+                    OT* __restrict__ x1, float* __restrict__ partials, FwGeom g) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((128u - (smem_u32(smem_raw) & 127u)) & 127u);
   uint8_t* s_x = smem;                                   // [kFwStages][hi | lo][row planes][columns][16 B]
@@ -500,7 +724,7 @@ conv1_fwd_tc_kernel(const float* __restrict__ in, const float* __restrict__ w1, 
         mbar_wait(&tfull[ts], (q / kFwTStages) & 1);
         tc_fence_after();
         const int yb = ys * kFwSegRows + j * 8;
-        __nv_bfloat16* ocol = x1 + (((size_t)b * g.H + yb) * g.W + (col_ok ? x : 0)) * 16;
+        OT* ocol = x1 + (((size_t)b * g.H + yb) * g.W + (col_ok ? x : 0)) * 16;
         // 4 chunks of 2 rows x 16 channels; the tcgen05.ld of chunk k+1 is in flight while chunk k is
         // converted (tcgen05.wait::ld waits for ALL outstanding loads, so it comes after the math)
         const uint32_t tbase = tmem_base + ((uint32_t)(quarter * 32) << 16) + ts * 128;
@@ -518,6 +742,25 @@ conv1_fwd_tc_kernel(const float* __restrict__ in, const float* __restrict__ w1, 
           }
           const int c0 = k * 32;
           const bool ok = col_ok && (yb + (c0 >> 4)) < g.H;     // H % 2 == 0: both rows or neither
+          if constexpr (sizeof(OT) == 4) {
+            // fp32 storage: accumulator + bias stored as is (hi/lo split products: fp32-level accuracy)
+#pragma unroll
+            for (int e = 0; e < 32; ++e) {
+              const float f0 = __uint_as_float(v[e]) + bias[e & 15];
+              v[e] = __float_as_uint(f0);
+              if (ok) { ssum[e & 15] += f0; ssq[e & 15] = fmaf(f0, f0, ssq[e & 15]); }
+            }
+            if (ok) {
+              float* o = reinterpret_cast<float*>(ocol) + (size_t)(c0 >> 4) * g.W * 16;
+              st_global_v8(o, &v[0]);
+              st_global_v8(o + 8, &v[8]);
+              st_global_v8(o + (size_t)g.W * 16, &v[16]);
+              st_global_v8(o + (size_t)g.W * 16 + 8, &v[24]);
+            }
+            if (k < 3) tmem_ld_wait();
+            else { tc_fence_before(); mbar_arrive(&tempty[ts]); }
+            continue;
+          }
           uint32_t pk[16];
 #pragma unroll
           for (int e = 0; e < 32; e += 2) {
@@ -532,7 +775,7 @@ conv1_fwd_tc_kernel(const float* __restrict__ in, const float* __restrict__ w1, 
           }
           if (ok) {
             // lanes are image columns: each instruction writes 32 consecutive pixels of one row (1 KB contiguous)
-            __nv_bfloat16* o = ocol + (size_t)(c0 >> 4) * g.W * 16;
+            __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(ocol) + (size_t)(c0 >> 4) * g.W * 16;
             st_global_v8(o, &pk[0]);
             st_global_v8(o + (size_t)g.W * 16, &pk[8]);
           }
@@ -562,16 +805,12 @@ conv1_fwd_tc_kernel(const float* __restrict__ in, const float* __restrict__ w1, 
 }  // namespace
 
 // Same contract as b200_conv1_fwd; partials must hold [b200_sm_count()][32]; *nparts_out = rows written.
-B200_API int b200_conv1_fwd_tc(const void* in_f32, const void* w1, const void* b1, void* x1_bf16, void* partials, int B,
-                               int H, int W, int* nparts_out, void* stream) {
+template <typename OT>
+static int conv1_fwd_tc_t(const void* in_f32, const void* w1, const void* b1, void* x1, void* partials, int B,
+                          int H, int W, int* nparts_out, void* stream) {
   B200_CHECK(H % 2 == 0 && W % 2 == 0, "conv1_fwd_tc: H and W must be even");
   cudaStream_t s = (cudaStream_t)stream;
-  static std::once_flag once;
-  static cudaError_t attr_err = cudaSuccess;
-  std::call_once(once, [&] {
-    attr_err = cudaFuncSetAttribute(conv1_fwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kFwSmemBytes);
-  });
-  B200_CUDA(attr_err);
+  B200_CUDA(set_max_smem(conv1_fwd_tc_kernel<OT>, kFwSmemBytes));
   FwGeom g;
   g.B = B; g.H = H; g.W = W;
   g.nys = (H + kFwSegRows - 1) / kFwSegRows;
@@ -579,9 +818,18 @@ B200_API int b200_conv1_fwd_tc(const void* in_f32, const void* w1, const void* b
   g.nitems = B * g.nys * g.nxs;
   const int nsm = b200_compute_sms();
   const int grid = g.nitems < nsm ? g.nitems : nsm;
-  conv1_fwd_tc_kernel<<<grid, kFwThreads, kFwSmemBytes, s>>>((const float*)in_f32, (const float*)w1, (const float*)b1,
-                                                             (__nv_bfloat16*)x1_bf16, (float*)partials, g);
+  conv1_fwd_tc_kernel<OT><<<grid, kFwThreads, kFwSmemBytes, s>>>((const float*)in_f32, (const float*)w1,
+                                                                 (const float*)b1, (OT*)x1, (float*)partials, g);
   B200_LAUNCH_CHECK();
   if (nparts_out) *nparts_out = grid;
   return 0;
+}
+B200_API int b200_conv1_fwd_tc(const void* in_f32, const void* w1, const void* b1, void* x1_bf16, void* partials, int B,
+                               int H, int W, int* nparts_out, void* stream) {
+  return conv1_fwd_tc_t<__nv_bfloat16>(in_f32, w1, b1, x1_bf16, partials, B, H, W, nparts_out, stream);
+}
+// fp32 output (precision-matched mode)
+B200_API int b200_conv1_fwd_tc_f32(const void* in_f32, const void* w1, const void* b1, void* x1_f32, void* partials,
+                                   int B, int H, int W, int* nparts_out, void* stream) {
+  return conv1_fwd_tc_t<float>(in_f32, w1, b1, x1_f32, partials, B, H, W, nparts_out, stream);
 }

@@ -33,6 +33,7 @@
 #include <cuda.h>
 #include <cstdint>
 #include <mutex>
+#include <type_traits>
 
 namespace {
 
@@ -428,16 +429,21 @@ conv5x5_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tm_act, const __grid
 constexpr int kRsEpiWarps = 8;                       // two groups of 4 (one per TMEM lane quarter), alternating rows
 constexpr int kRsThreads = 32 * (2 + kRsEpiWarps);  // warp0 feed, warp1 MMA issue, warps 2-9 epilogue
 
-template <int CIN, int COUT>
+// ET = activation storage type: __nv_bfloat16 (kind::f16 MMAs, K = 16) or float (kind::tf32, K = 8: the
+// reference's precision - fp32 tensors, TF32 convolution math).  A 16-byte plane holds kCPP channels.
+template <int CIN, int COUT, typename ET = __nv_bfloat16>
 struct RsCfg {
-  static constexpr int kPlanes = CIN / 8;
+  static constexpr int kEB = (int)sizeof(ET);
+  static constexpr int kCPP = 16 / kEB;                      // channels per 16-byte plane piece: 8 | 4
+  static constexpr int kPlanes = CIN / kCPP;
   static constexpr int kSlotBytes = kPlanes * kPlaneBytes;
-  static constexpr int kSlots = 16;          // input-row ring = cp.async pipeline depth; power of two
-  static constexpr int kKSteps = CIN / 16;
+  // input-row ring = cp.async pipeline depth; power of two (fp32 dgrad rows are 17 KB: 8 of them)
+  static constexpr int kSlots = (kEB == 4 && CIN == 32) ? 8 : 16;
+  static constexpr int kKSteps = CIN / (2 * kCPP);           // MMAs per (row, dx): each spans two planes
   static constexpr int kNB = 5 * COUT;                       // B rows per (dx, kk): n = jj*COUT + co
-  static constexpr int kWChunkBytes = kNB * 16;              // one 8-channel k-chunk of all n rows
+  static constexpr int kWChunkBytes = kNB * 16;              // one kCPP-channel k-chunk of all n rows
   static constexpr int kWStepBytes = 2 * kWChunkBytes;       // one (dx, kk) B tile
-  static constexpr int kWBytes = 5 * kKSteps * kWStepBytes;  // == 25*CIN*COUT*2
+  static constexpr int kWBytes = 5 * kKSteps * kWStepBytes;  // == 25*CIN*COUT*sizeof(ET)
   // The accumulator ring takes all 512 TMEM columns (16 slots at COUT=32, 32 at COUT=16).  A five-slot window that
   // reaches the end of the ring has to be split into two MMAs (a D range past column 511 faults), and each half
   // re-reads the whole A operand, so the longer ring of dgrad halves how often that happens.
@@ -463,36 +469,38 @@ struct RsCfg {
 // count in ncu).  Source and destination of a lane's k-th piece are its base plus a compile-time
 // constant: the address registers of an in-flight LDGSTS stay reserved until its data returns, so the
 // row loop must not recompute per-piece addresses.
-template <int C, int NPIX>
+template <int C, int NPIX, int EB = 2>
 struct RowPlan {
-  static constexpr int kPP = C / 8;                      // 16-byte pieces per pixel (= smem planes)
+  static constexpr int kPP = C * EB / 16;                // 16-byte pieces per pixel (= smem planes)
   static constexpr int kLP = 32 / kPP;                   // pixels per warp instruction
   static constexpr int kPer = (NPIX + kLP - 1) / kLP;    // warp instructions per row
+  static_assert(kPer <= 64, "edge mask is 64 bits");
+  using Mask = typename std::conditional<(kPer > 32), uint64_t, uint32_t>::type;
   uint32_t soff;           // byte offset of the lane's first piece inside the slot
   uint32_t goff;           // byte offset of the lane's first piece from pixel x_first of the row
-  uint32_t ok;             // bit k: piece k is inside the image horizontally
+  Mask ok;                 // bit k: piece k is inside the image horizontally
   int x_first, px0;
   __device__ __forceinline__ void build(int x_first_, int plane_bytes, int W, int lane) {
     x_first = x_first_;
     const int pl = lane / kLP;
     px0 = lane % kLP;
     soff = (uint32_t)(pl * plane_bytes + px0 * 16);
-    goff = (uint32_t)(px0 * (C * 2) + pl * 16);
+    goff = (uint32_t)(px0 * (C * EB) + pl * 16);
     ok = 0;
 #pragma unroll
     for (int k = 0; k < kPer; ++k) {
       const int p = px0 + k * kLP, x = x_first + p;
-      if (p < NPIX && x >= 0 && x < W) ok |= 1u << k;
+      if (p < NPIX && x >= 0 && x < W) ok |= (Mask)1 << k;
     }
   }
   // dst: [C/8 planes][NPIX][16 B];  src pixel (b, y, x_first + p), channels plane*8..+7; zero-fill outside
   // (a piece with source size 0 reads nothing, so its address may lie outside the row)
-  __device__ __forceinline__ void copy(uint8_t* dst, const __nv_bfloat16* __restrict__ src, int b, int y, int H,
+  __device__ __forceinline__ void copy(uint8_t* dst, const void* __restrict__ src, int b, int y, int H,
                                        int W) const {
     const bool row_ok = (y >= 0) && (y < H);
     const char* row = reinterpret_cast<const char*>(src) +
-                      (((int64_t)b * H + (row_ok ? y : 0)) * (int64_t)W + x_first) * (int64_t)(C * 2);
-    const uint32_t okr = row_ok ? ok : 0u;
+                      (((int64_t)b * H + (row_ok ? y : 0)) * (int64_t)W + x_first) * (int64_t)(C * EB);
+    const Mask okr = row_ok ? ok : (Mask)0;
     const char* lsrc = row + goff;
     uint8_t* ldst = dst + soff;
 #pragma unroll
@@ -508,14 +516,16 @@ struct RowPlan {
 //     bnprev = [scale|shift|mean|rstd] of BN1:  dy = dp1 where p1 > 0,
 //     partials = [sum(dy) | sum(dy * xhat)],  xhat = ((p1 - shift)/scale - mean) * rstd.
 //     This replaces a separate pass over the 1.44 GB conv1 output.
-template <int CIN, int COUT, bool TRANSPOSED, int STATS, bool LDGSTS>
+template <int CIN, int COUT, bool TRANSPOSED, int STATS, bool LDGSTS, typename ET = __nv_bfloat16>
 __global__ void __launch_bounds__(kRsThreads, 1)
-conv5x5_rs_kernel(const __grid_constant__ CUtensorMap tm_act, const __nv_bfloat16* __restrict__ act,
+conv5x5_rs_kernel(const __grid_constant__ CUtensorMap tm_act, const ET* __restrict__ act,
                   const float* __restrict__ w,
-                  const float* __restrict__ bias, __nv_bfloat16* __restrict__ out,
-                  float* __restrict__ partials, const __nv_bfloat16* pooled, const float* __restrict__ bnprev,
+                  const float* __restrict__ bias, ET* __restrict__ out,
+                  float* __restrict__ partials, const ET* pooled, const float* __restrict__ bnprev,
                   ConvGeom g) {
-  using Cfg = RsCfg<CIN, COUT>;
+  using Cfg = RsCfg<CIN, COUT, ET>;
+  constexpr bool kF32 = sizeof(ET) == 4;
+  static_assert(LDGSTS || !kF32, "the TMA feed exists for bf16 only");
   constexpr int RT = Cfg::kTStages;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((128u - (smem_u32(smem_raw) & 127u)) & 127u);
@@ -539,20 +549,21 @@ conv5x5_rs_kernel(const __grid_constant__ CUtensorMap tm_act, const __nv_bfloat1
     s_bnp[3 * COUT + threadIdx.x] = bnprev[3 * COUT + threadIdx.x];
   }
 
-  // weights: byte(dx, kk, c, n=(jj,co), e) = ((((dx*KSTEPS + kk)*2 + c)*kNB + n)*8 + e)*2, dy = 4 - jj
+  // weights: element(dx, kk, c, n=(jj,co), e) = (((dx*KSTEPS + kk)*2 + c)*kNB + n)*kCPP + e, dy = 4 - jj
   for (int i = threadIdx.x; i < kTaps * CIN * COUT; i += kRsThreads) {
-    const int e = i & 7;
-    int r = i >> 3;
+    const int e = i % Cfg::kCPP;
+    int r = i / Cfg::kCPP;
     const int n = r % Cfg::kNB; r /= Cfg::kNB;
     const int c = r & 1; r >>= 1;
     const int kk = r % Cfg::kKSteps;
     const int dx = r / Cfg::kKSteps;
     const int jj = n / COUT, co = n % COUT;
     const int tap = (4 - jj) * 5 + dx;
-    const int k = kk * 16 + c * 8 + e;
+    const int k = (kk * 2 + c) * Cfg::kCPP + e;
     const float v = TRANSPOSED ? w[((size_t)k * COUT + co) * kTaps + (kTaps - 1 - tap)]
                                : w[((size_t)co * CIN + k) * kTaps + tap];
-    reinterpret_cast<__nv_bfloat16*>(s_w)[i] = __float2bfloat16_rn(v);
+    if constexpr (kF32) reinterpret_cast<float*>(s_w)[i] = to_tf32_rna(v);
+    else reinterpret_cast<__nv_bfloat16*>(s_w)[i] = __float2bfloat16_rn(v);
   }
   if (threadIdx.x < COUT) s_bias[threadIdx.x] = bias ? bias[threadIdx.x] : 0.f;
   fence_proxy_async_smem();
@@ -560,7 +571,7 @@ conv5x5_rs_kernel(const __grid_constant__ CUtensorMap tm_act, const __nv_bfloat1
     for (int i = 0; i < Cfg::kSlots; ++i) { mbar_init(&full[i], LDGSTS ? 32 : 1); mbar_init(&empty[i], 1); }
     for (int i = 0; i < RT; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], 128); }
     mbar_fence_init();
-    tma_prefetch_desc(&tm_act);
+    if (!LDGSTS) tma_prefetch_desc(&tm_act);
   }
   if (warp == 1) tmem_alloc<Cfg::kTmemCols>(s_tmem);
   tc_fence_before();
@@ -579,7 +590,7 @@ conv5x5_rs_kernel(const __grid_constant__ CUtensorMap tm_act, const __nv_bfloat1
         const int y0 = seg * g.rseg;
         const int rows = min(g.rseg, g.H - y0);
         const int x0 = strip * kBM;
-        RowPlan<CIN, kPW> plan;
+        RowPlan<CIN, kPW, Cfg::kEB> plan;
         plan.build(x0 - 2, kPlaneBytes, g.W, lane);
         for (int i = 0; i < rows + 4; ++i, ++gcount) {
           const uint32_t slot = gcount % Cfg::kSlots, use = gcount / Cfg::kSlots;
@@ -613,7 +624,7 @@ conv5x5_rs_kernel(const __grid_constant__ CUtensorMap tm_act, const __nv_bfloat1
     // uniform registers); only the tcgen05 instructions are predicated on one elected lane.
     // (Running the loop under `if (lane == 0)` made ptxas serialise every UTCHMMA operand through
     // ELECT / R2UR / BRA.U.ANY: ~285 SASS instructions per row on one lane - the bottleneck ncu showed.)
-    constexpr uint32_t idesc0 = umma_idesc_bf16(kBM, 0, 0, 0);            // N filled in per MMA
+    constexpr uint32_t idesc0 = umma_idesc(UmmaKind<ET>::kFormat, kBM, 0, 0, 0);   // N filled in per MMA
     const uint32_t slots_addr = smem_u32(s_slots);
     const uint64_t a_tmpl = smem_desc_noswz(0, kPlaneBytes, 128);          // LBO lives in the LOW word (bits 16..29)
     const uint32_t a_hi = (uint32_t)(a_tmpl >> 32), a_lo0 = (uint32_t)a_tmpl;
@@ -650,11 +661,11 @@ conv5x5_rs_kernel(const __grid_constant__ CUtensorMap tm_act, const __nv_bfloat1
                 const uint64_t a_desc = ((uint64_t)a_hi << 32) | (uint64_t)(a_lo_row + ((2 * kk) * kPlaneBytes >> 4) + dx);
                 const uint32_t b_lo = b_lo0 + (((dx * Cfg::kKSteps + kk) * Cfg::kWStepBytes) >> 4);
                 if (dx == 0 && kk == 0) {
-                  umma_bf16(d0, a_desc, ((uint64_t)b_hi << 32) | (uint64_t)b_lo, idesc0 | ((uint32_t)((4 * COUT) >> 3) << 17), 1u);
-                  umma_bf16(d0 + 4 * COUT, a_desc, ((uint64_t)b_hi << 32) | (uint64_t)(b_lo + 4 * COUT),
+                  UmmaKind<ET>::mma(d0, a_desc, ((uint64_t)b_hi << 32) | (uint64_t)b_lo, idesc0 | ((uint32_t)((4 * COUT) >> 3) << 17), 1u);
+                  UmmaKind<ET>::mma(d0 + 4 * COUT, a_desc, ((uint64_t)b_hi << 32) | (uint64_t)(b_lo + 4 * COUT),
                             idesc0 | ((uint32_t)(COUT >> 3) << 17), 0u);
                 } else {
-                  umma_bf16(d0, a_desc, ((uint64_t)b_hi << 32) | (uint64_t)b_lo, idesc0 | ((uint32_t)((5 * COUT) >> 3) << 17), 1u);
+                  UmmaKind<ET>::mma(d0, a_desc, ((uint64_t)b_hi << 32) | (uint64_t)b_lo, idesc0 | ((uint32_t)((5 * COUT) >> 3) << 17), 1u);
                 }
               }
             }
@@ -670,13 +681,13 @@ conv5x5_rs_kernel(const __grid_constant__ CUtensorMap tm_act, const __nv_bfloat1
               const int nacc = acc_hi - jj_lo + 1;                          // may be <= 0
               const int n1 = min(nacc, (int)(RT - s0));
               if (n1 > 0)
-                umma_bf16(tmem_base + s0 * COUT, a_desc, ((uint64_t)b_hi << 32) | (uint64_t)(b_lo + jj_lo * COUT),
+                UmmaKind<ET>::mma(tmem_base + s0 * COUT, a_desc, ((uint64_t)b_hi << 32) | (uint64_t)(b_lo + jj_lo * COUT),
                           idesc0 | ((uint32_t)((n1 * COUT) >> 3) << 17), 1u);
               if (nacc > n1)
-                umma_bf16(tmem_base, a_desc, ((uint64_t)b_hi << 32) | (uint64_t)(b_lo + (jj_lo + n1) * COUT),
+                UmmaKind<ET>::mma(tmem_base, a_desc, ((uint64_t)b_hi << 32) | (uint64_t)(b_lo + (jj_lo + n1) * COUT),
                           idesc0 | ((uint32_t)(((nacc - n1) * COUT) >> 3) << 17), 1u);
               if (first && starts_row)
-                umma_bf16(tmem_base + ((qbase + (uint32_t)i) % RT) * COUT, a_desc,
+                UmmaKind<ET>::mma(tmem_base + ((qbase + (uint32_t)i) % RT) * COUT, a_desc,
                           ((uint64_t)b_hi << 32) | (uint64_t)(b_lo + 4 * COUT), idesc0 | ((uint32_t)(COUT >> 3) << 17), 0u);
             }
           }
@@ -720,11 +731,11 @@ conv5x5_rs_kernel(const __grid_constant__ CUtensorMap tm_act, const __nv_bfloat1
         const uint32_t stage = q % RT, use = q / RT;
         // STATS == 2: fetch this pixel's pooled activation now, so the load latency overlaps the wait for
         // the accumulator (it is read here, before the gradient written below overwrites it in place)
-        uint4 pvv[STATS == 2 ? COUT / 8 : 1];
+        uint4 pvv[STATS == 2 ? COUT / Cfg::kCPP : 1];
         if (STATS == 2 && valid) {
           const uint4* pp = reinterpret_cast<const uint4*>(pooled + (((size_t)b * g.H + (y0 + j)) * g.W + x) * COUT);
 #pragma unroll
-          for (int i = 0; i < COUT / 8; ++i) pvv[i] = pp[i];
+          for (int i = 0; i < COUT / Cfg::kCPP; ++i) pvv[i] = pp[i];
         }
         mbar_wait(&tfull[stage], use & 1);
         tc_fence_after();
@@ -735,6 +746,30 @@ conv5x5_rs_kernel(const __grid_constant__ CUtensorMap tm_act, const __nv_bfloat1
         tmem_ld_wait();
         tc_fence_before();
         mbar_arrive(&tempty[stage]);
+        if constexpr (kF32) {
+          // fp32 storage: the accumulator (+ bias) is stored as is; statistics are those of the stored values
+          if (!TRANSPOSED) {
+#pragma unroll
+            for (int c = 0; c < COUT; ++c) v[c] = __float_as_uint(__uint_as_float(v[c]) + s_bias[c]);
+          }
+          if (valid) {
+            ET* o = out + (((size_t)b * g.H + (y0 + j)) * g.W + x) * COUT;
+#pragma unroll
+            for (int c = 0; c < COUT; ++c) {
+              const float r0 = __uint_as_float(v[c]);
+              if (STATS == 1) { ssum[c] += r0; ssq[c] = fmaf(r0, r0, ssq[c]); }
+              if (STATS == 2) {
+                const float y = __uint_as_float((&pvv[c / 4].x)[c & 3]);
+                const float gg = y > 0.f ? r0 : 0.f;
+                ssum[c] += gg;
+                ssq[c] = fmaf(gg, fmaf(y, kA[c], kB[c]), ssq[c]);
+              }
+            }
+#pragma unroll
+            for (int i = 0; i < COUT / 8; ++i) st_global_v8(o + 8 * i, &v[8 * i]);
+          }
+          continue;
+        }
         uint32_t pk[COUT / 2];
 #pragma unroll
         for (int c = 0; c < COUT; c += 2) {
@@ -748,11 +783,11 @@ conv5x5_rs_kernel(const __grid_constant__ CUtensorMap tm_act, const __nv_bfloat1
           }
         }
         if (valid) {
-          __nv_bfloat16* o = out + (((size_t)b * g.H + (y0 + j)) * g.W + x) * COUT;
+          __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(out) + (((size_t)b * g.H + (y0 + j)) * g.W + x) * COUT;
           if (STATS == 2) {
 #pragma unroll
             for (int c = 0; c < COUT; ++c) {
-              const uint32_t pw = (&pvv[c / 8].x)[(c & 7) >> 1];
+              const uint32_t pw = (&pvv[(c / 8) % (COUT / Cfg::kCPP)].x)[(c & 7) >> 1];
               const float y = (c & 1) ? bf16_hi(pw) : bf16_lo(pw);
               const float gq = (c & 1) ? bf16_hi(pk[c / 2]) : bf16_lo(pk[c / 2]);
               const float gg = y > 0.f ? gq : 0.f;
@@ -976,6 +1011,350 @@ conv5x5_wgrad_rs_kernel(const __grid_constant__ CUtensorMap tm_act, const __grid
   if (warp == 1) { __syncwarp(); tmem_dealloc<kWgTmemCols>(tmem_base); }
 }
 
+
+// ===================================================== wgrad, dx-replicated A ===
+// The kernels above give the weight gradient only half-filled MMAs: with the dx shift expressed as the
+// M-stride of the act operand, one MMA covers one 8-channel plane, M = 64 with 40 useful rows, and a
+// plane pair needs two of them.  Here the feed writes the act row FIVE times, each copy shifted by one
+// pixel, as chunk rows [(dx, plane)][pixel][16 B].  The chunks of all (dx, ci) now sit at ONE constant
+// stride, so a single M = 128 MMA (80 useful rows: m = dx*16 + ci) contracts a K-step against the five
+// dx2 rows (N = 160): half the MMA count of the version above.  The extra copies cost cp.async wavefronts
+// in the L1 data pipe (one per 32-byte sector), which is what bounds this version: 0.52 vs 0.56 ms at
+// batch 5.  (The template also instantiates for float, but the hardware has no no-swizzle MN-major layout
+// for TF32 - such MMAs accumulate zeros - so fp32 storage uses conv5x5_wgrad_tf32_kernel below.)
+template <typename ET>
+struct WgRepCfg {
+  static constexpr int kEB = (int)sizeof(ET);
+  static constexpr int kCPP = 16 / kEB;                 // channels per 16-byte chunk
+  static constexpr int kSP = kEB == 2 ? 128 : 64;       // strip width in pixels
+  static constexpr int kChunkRow = kSP * 16;            // bytes of one chunk over the strip
+  static constexpr int kPlanesA = 16 / kCPP;            // act:  16 channels
+  static constexpr int kPlanesB = 32 / kCPP;            // dx2:  32 channels
+  static constexpr int kSlotA = 5 * kPlanesA * kChunkRow;   // 20 KB (both types)
+  static constexpr int kSlotB = kPlanesB * kChunkRow;       //  8 KB
+  static constexpr int kSlotsA = 4;
+  static constexpr int kSlotsB = 12, kPhysB = kSlotsB + 4;  // slots 12..15 mirror 0..3 (windows never wrap)
+  static constexpr int kKSteps = kSP / UmmaKind<ET>::kK;    // 8
+  static constexpr int kKAdv = UmmaKind<ET>::kK * 16;       // bytes per K-step along a chunk row
+  static constexpr int kTmemCols = 256;                     // one 128 x 160 fp32 accumulator
+  static constexpr int kSmemBytes = kSlotsA * kSlotA + kPhysB * kSlotB + 1024 + 128;
+  // an M = 128 operand spans 128 / kCPP chunk rows from the slot start; the rows past the 5 * kPlanesA real
+  // ones belong to accumulator lanes >= 80 that nobody reads, but the bytes must exist: they fall into the
+  // next A slots / the B ring, which follows the A ring in shared memory.
+  static_assert((128 / kCPP) * kChunkRow <= kSlotA + kPhysB * kSlotB, "A operand overrun must stay inside the B ring");
+};
+
+template <typename ET>
+__global__ void __launch_bounds__(kThreads, 1)
+conv5x5_wgrad_rep_kernel(const ET* __restrict__ act, const ET* __restrict__ dxo, float* __restrict__ partials,
+                         ConvGeom g) {
+  using Cfg = WgRepCfg<ET>;
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((128u - (smem_u32(smem_raw) & 127u)) & 127u);
+  uint8_t* s_a = smem;
+  uint8_t* s_b = smem + Cfg::kSlotsA * Cfg::kSlotA;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_b + Cfg::kPhysB * Cfg::kSlotB);
+  uint64_t* fullA = bars;
+  uint64_t* emptyA = fullA + Cfg::kSlotsA;
+  uint64_t* fullB = emptyA + Cfg::kSlotsA;
+  uint64_t* emptyB = fullB + Cfg::kSlotsB;
+  uint64_t* done = emptyB + Cfg::kSlotsB;
+  uint32_t* s_tmem = reinterpret_cast<uint32_t*>(done + 1);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < Cfg::kSlotsA; ++i) { mbar_init(&fullA[i], 32); mbar_init(&emptyA[i], 1); }
+    for (int i = 0; i < Cfg::kSlotsB; ++i) { mbar_init(&fullB[i], 32); mbar_init(&emptyB[i], 1); }
+    mbar_init(done, 1);
+    mbar_fence_init();
+  }
+  if (warp == 1) tmem_alloc<Cfg::kTmemCols>(s_tmem);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *s_tmem;
+
+  if (warp == 0) {
+    // ===== feed: whole warp, 16-byte cp.async, arrival on the row's barrier when the lane's copies land
+    uint32_t ga = 0, gb = 0;
+    for (int item = blockIdx.x; item < g.nitems; item += gridDim.x) {
+      const int seg = item % g.nseg;
+      const int strip = (item / g.nseg) % g.nstrips;
+      const int b = item / (g.nseg * g.nstrips);
+      const int r0 = seg * g.rseg;
+      const int rows = min(g.rseg, g.H - r0);
+      const int x0 = strip * Cfg::kSP;
+      RowPlan<32, Cfg::kSP, Cfg::kEB> planB;
+      planB.build(x0, Cfg::kChunkRow, g.W, lane);
+      RowPlan<16, Cfg::kSP, Cfg::kEB> planA[5];          // one per dx: same lane offsets, different edge masks
+#pragma unroll
+      for (int dx = 0; dx < 5; ++dx) planA[dx].build(x0 - 2 + dx, Cfg::kChunkRow, g.W, lane);
+      for (int i = 0; i < rows + 4; ++i) {
+        {
+          const uint32_t slot = gb % Cfg::kSlotsB, use = gb / Cfg::kSlotsB;
+          mbar_wait(&emptyB[slot], (use & 1) ^ 1);
+          planB.copy(s_b + slot * Cfg::kSlotB, dxo, b, r0 - 2 + i, g.H, g.W);
+          if (slot < 4) planB.copy(s_b + (Cfg::kSlotsB + slot) * Cfg::kSlotB, dxo, b, r0 - 2 + i, g.H, g.W);
+          cp_async_mbar_arrive_noinc(&fullB[slot]);
+          ++gb;
+        }
+        if (i >= 4) {
+          const uint32_t slot = ga % Cfg::kSlotsA, use = ga / Cfg::kSlotsA;
+          mbar_wait(&emptyA[slot], (use & 1) ^ 1);
+          uint8_t* dst = s_a + slot * Cfg::kSlotA;
+#pragma unroll
+          for (int dx = 0; dx < 5; ++dx)
+            planA[dx].copy(dst + dx * Cfg::kPlanesA * Cfg::kChunkRow, act, b, r0 + i - 4, g.H, g.W);
+          cp_async_mbar_arrive_noinc(&fullA[slot]);
+          ++ga;
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issue: warp-uniform loop, tcgen05 instructions on one elected lane
+    constexpr uint32_t idesc = umma_idesc(UmmaKind<ET>::kFormat, 128, 160, 1, 1);
+    const uint64_t tmpl = smem_desc_noswz(0, 128, Cfg::kChunkRow);     // MN-major: LBO = 8 k-rows, SBO = next chunk row
+    const uint32_t hi = (uint32_t)(tmpl >> 32);
+    const uint32_t a_base = (uint32_t)tmpl + (smem_u32(s_a) >> 4), b_base = (uint32_t)tmpl + (smem_u32(s_b) >> 4);
+    uint32_t ga = 0, gbase = 0;
+    uint32_t first = 1;
+    for (int item = blockIdx.x; item < g.nitems; item += gridDim.x) {
+      const int seg = item % g.nseg;
+      const int r0 = seg * g.rseg;
+      const int rows = min(g.rseg, g.H - r0);
+      for (int i = 0; i < rows; ++i, ++ga) {
+        for (int k = (i == 0 ? 0 : 4); k < 5; ++k) {          // dx2 local rows i..i+4 have landed
+          const uint32_t gc = gbase + i + k;
+          mbar_wait(&fullB[gc % Cfg::kSlotsB], (gc / Cfg::kSlotsB) & 1);
+        }
+        const uint32_t slotA = ga % Cfg::kSlotsA;
+        mbar_wait(&fullA[slotA], (ga / Cfg::kSlotsA) & 1);
+        tc_fence_after();
+        const uint32_t s0 = (gbase + i) % Cfg::kSlotsB;
+        const uint32_t arow = a_base + slotA * (Cfg::kSlotA >> 4);
+        const uint32_t brow = b_base + s0 * (Cfg::kSlotB >> 4);     // slots s0..s0+4 (<= 15: mirrors) are contiguous
+        const uint32_t acc0 = first ? 0u : 1u;
+        if (elect_one()) {
+#pragma unroll
+          for (int kb = 0; kb < Cfg::kKSteps; ++kb)
+            UmmaKind<ET>::mma(tmem_base, ((uint64_t)hi << 32) | (uint64_t)(arow + kb * (Cfg::kKAdv >> 4)),
+                              ((uint64_t)hi << 32) | (uint64_t)(brow + kb * (Cfg::kKAdv >> 4)), idesc,
+                              kb == 0 ? acc0 : 1u);
+          umma_commit(&emptyA[slotA]);
+          umma_commit(&emptyB[(gbase + i) % Cfg::kSlotsB]);
+        }
+        __syncwarp();
+        first = 0;
+      }
+      if (elect_one())
+        for (int k = 0; k < 4; ++k) umma_commit(&emptyB[(gbase + rows + k) % Cfg::kSlotsB]);
+      __syncwarp();
+      gbase += rows + 4;
+    }
+    if (elect_one()) umma_commit(done);
+    __syncwarp();
+  } else {
+    // ===== extraction: lane m = dx*16 + ci (m < 80), column n = jj*32 + co, dy = 4 - jj
+    const int quarter = warp & 3;
+    float* dst = partials + (size_t)blockIdx.x * (32 * 16 * kTaps);
+    mbar_wait(done, 0);
+    tc_fence_after();
+    const int m = quarter * 32 + lane;
+    const int dxs = m >> 4, ci = m & 15;
+#pragma unroll 1
+    for (int jj = 0; jj < 5; ++jj) {
+      const int dy = 4 - jj;
+      uint32_t v[32];
+      const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + jj * 32;
+      tmem_ld16(taddr, *reinterpret_cast<uint32_t(*)[16]>(&v[0]));
+      tmem_ld16(taddr + 16, *reinterpret_cast<uint32_t(*)[16]>(&v[16]));
+      tmem_ld_wait();
+      if (m < 80) {
+#pragma unroll
+        for (int co = 0; co < 32; ++co)
+          dst[((size_t)co * 16 + ci) * kTaps + dy * 5 + dxs] = __uint_as_float(v[co]);
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  if (warp == 1) { __syncwarp(); tmem_dealloc<Cfg::kTmemCols>(tmem_base); }
+}
+
+// =================================================== wgrad, fp32 storage, TF32 ===
+// MN-major TF32 operands exist in exactly one shared-memory layout: 128-byte rows (32 fp32 MN elements per
+// K row = pixel), 32-byte units XOR-swizzled by the row index (sw32_off, ptx.cuh).  That happens to be the
+// NHWC memory of a 32-channel fp32 tensor, so a dx2 row segment is copied pixel by pixel with only the unit
+// permutation applied, and five consecutive row slots are again one N = 160 operand (LBO = slot stride).
+// The act tensor has 16 channels (64 B per pixel): an A row pairs two neighbouring pixels, atom j holds
+// [p1[x+2j] | p1[x+2j+1]], three atoms cover dx = 0..5, M = 128 with m = 16*dx + ci (80 useful rows).
+namespace wt {
+constexpr int kSP = 64;                         // strip width in pixels
+constexpr int kAtom = kSP * 128;                // 8 KB: one 32-element MN atom over the strip
+constexpr int kSlotA = 3 * kAtom;               // 24 KB (the 4th atom an M = 128 operand spans is the next slot: unused lanes)
+constexpr int kSlotB = kAtom;                   //  8 KB
+constexpr int kSlotsA = 3;
+constexpr int kSlotsB = 12, kPhysB = kSlotsB + 4;
+constexpr int kKSteps = kSP / 8;
+constexpr int kTmemCols = 256;
+constexpr int kSmemBytes = kSlotsA * kSlotA + kPhysB * kSlotB + 1024 + 1024;
+}  // namespace wt
+
+__global__ void __launch_bounds__(kThreads, 1)
+conv5x5_wgrad_tf32_kernel(const float* __restrict__ act, const float* __restrict__ dxo, float* __restrict__ partials,
+                          ConvGeom g) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);     // swizzle atoms: 1 KB aligned
+  uint8_t* s_a = smem;
+  uint8_t* s_b = smem + wt::kSlotsA * wt::kSlotA;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_b + wt::kPhysB * wt::kSlotB);
+  uint64_t* fullA = bars;
+  uint64_t* emptyA = fullA + wt::kSlotsA;
+  uint64_t* fullB = emptyA + wt::kSlotsA;
+  uint64_t* emptyB = fullB + wt::kSlotsB;
+  uint64_t* done = emptyB + wt::kSlotsB;
+  uint32_t* s_tmem = reinterpret_cast<uint32_t*>(done + 1);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < wt::kSlotsA; ++i) { mbar_init(&fullA[i], 32); mbar_init(&emptyA[i], 1); }
+    for (int i = 0; i < wt::kSlotsB; ++i) { mbar_init(&fullB[i], 32); mbar_init(&emptyB[i], 1); }
+    mbar_init(done, 1);
+    mbar_fence_init();
+  }
+  if (warp == 1) tmem_alloc<wt::kTmemCols>(s_tmem);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *s_tmem;
+
+  if (warp == 0) {
+    // ===== feed.  dx2: one instruction = 4 pixels x 8 pieces (512 contiguous bytes of the row).
+    //              act: one instruction = 8 pixels x 4 pieces (512 contiguous bytes), written to half h of atom j.
+    const int bp = lane >> 3, bq = lane & 7;           // dx2: pixel-in-group, 16-byte piece (unit = bq >> 1)
+    const int ap = lane >> 2, aq = lane & 3;           // act: pixel-in-group, 16-byte piece of the 64-byte pixel
+    uint32_t ga = 0, gb = 0;
+    for (int item = blockIdx.x; item < g.nitems; item += gridDim.x) {
+      const int seg = item % g.nseg;
+      const int strip = (item / g.nseg) % g.nstrips;
+      const int b = item / (g.nseg * g.nstrips);
+      const int r0 = seg * g.rseg;
+      const int rows = min(g.rseg, g.H - r0);
+      const int x0 = strip * wt::kSP;
+      for (int i = 0; i < rows + 4; ++i) {
+        {
+          const uint32_t slot = gb % wt::kSlotsB, use = gb / wt::kSlotsB;
+          mbar_wait(&emptyB[slot], (use & 1) ^ 1);
+          const int y = r0 - 2 + i;
+          const bool row_ok = y >= 0 && y < g.H;
+          const char* row = reinterpret_cast<const char*>(dxo) + (((int64_t)b * g.H + (row_ok ? y : 0)) * g.W + x0) * 128;
+          uint8_t* dst = s_b + slot * wt::kSlotB;
+          uint8_t* dst2 = s_b + (wt::kSlotsB + slot) * wt::kSlotB;            // mirror of slots 0..3
+#pragma unroll
+          for (int k4 = 0; k4 < wt::kSP / 4; ++k4) {
+            const int k = k4 * 4 + bp;
+            const uint32_t nbytes = (row_ok && x0 + k < g.W) ? 16u : 0u;
+            const uint32_t off = sw32_off(k, bq >> 1) + (bq & 1) * 16;
+            cp_async16(dst + off, row + k * 128 + bq * 16, nbytes);
+            if (slot < 4) cp_async16(dst2 + off, row + k * 128 + bq * 16, nbytes);
+          }
+          cp_async_mbar_arrive_noinc(&fullB[slot]);
+          ++gb;
+        }
+        if (i >= 4) {
+          const uint32_t slot = ga % wt::kSlotsA, use = ga / wt::kSlotsA;
+          mbar_wait(&emptyA[slot], (use & 1) ^ 1);
+          const int y = r0 + i - 4;                                            // always inside the image
+          const char* row = reinterpret_cast<const char*>(act) + ((int64_t)b * g.H + y) * g.W * 64;
+          uint8_t* dst = s_a + slot * wt::kSlotA;
+#pragma unroll
+          for (int jh = 0; jh < 6; ++jh) {                                     // dx = jh: atom jh >> 1, half jh & 1
+#pragma unroll
+            for (int k8 = 0; k8 < wt::kSP / 8; ++k8) {
+              const int k = k8 * 8 + ap;
+              const int x = x0 - 2 + jh + k;
+              const uint32_t nbytes = (x >= 0 && x < g.W) ? 16u : 0u;
+              const uint32_t u = (uint32_t)((jh & 1) * 2 + (aq >> 1));
+              cp_async16(dst + (jh >> 1) * wt::kAtom + sw32_off(k, u) + (aq & 1) * 16,
+                         row + (int64_t)(nbytes ? x : 0) * 64 + aq * 16, nbytes);
+            }
+          }
+          cp_async_mbar_arrive_noinc(&fullA[slot]);
+          ++ga;
+        }
+      }
+    }
+  } else if (warp == 1) {
+    constexpr uint32_t idesc = umma_idesc(2, 128, 160, 1, 1);
+    // MN-major SW128_32B: LBO = distance between 32-element MN atoms, SBO = distance between 4-row K groups
+    const uint64_t a_tmpl = smem_desc(0, wt::kAtom, 512, 1), b_tmpl = smem_desc(0, wt::kSlotB, 512, 1);
+    const uint32_t a_hi = (uint32_t)(a_tmpl >> 32), b_hi = (uint32_t)(b_tmpl >> 32);
+    const uint32_t a_base = (uint32_t)a_tmpl + (smem_u32(s_a) >> 4), b_base = (uint32_t)b_tmpl + (smem_u32(s_b) >> 4);
+    uint32_t ga = 0, gbase = 0;
+    uint32_t first = 1;
+    for (int item = blockIdx.x; item < g.nitems; item += gridDim.x) {
+      const int seg = item % g.nseg;
+      const int r0 = seg * g.rseg;
+      const int rows = min(g.rseg, g.H - r0);
+      for (int i = 0; i < rows; ++i, ++ga) {
+        for (int k = (i == 0 ? 0 : 4); k < 5; ++k) {
+          const uint32_t gc = gbase + i + k;
+          mbar_wait(&fullB[gc % wt::kSlotsB], (gc / wt::kSlotsB) & 1);
+        }
+        const uint32_t slotA = ga % wt::kSlotsA;
+        mbar_wait(&fullA[slotA], (ga / wt::kSlotsA) & 1);
+        tc_fence_after();
+        const uint32_t s0 = (gbase + i) % wt::kSlotsB;
+        const uint32_t arow = a_base + slotA * (wt::kSlotA >> 4);
+        const uint32_t brow = b_base + s0 * (wt::kSlotB >> 4);
+        const uint32_t acc0 = first ? 0u : 1u;
+        if (elect_one()) {
+#pragma unroll
+          for (int kb = 0; kb < wt::kKSteps; ++kb)       // 8 pixels = 1 KB further down every atom
+            umma_tf32(tmem_base, ((uint64_t)a_hi << 32) | (uint64_t)(arow + kb * 64),
+                      ((uint64_t)b_hi << 32) | (uint64_t)(brow + kb * 64), idesc, kb == 0 ? acc0 : 1u);
+          umma_commit(&emptyA[slotA]);
+          umma_commit(&emptyB[(gbase + i) % wt::kSlotsB]);
+        }
+        __syncwarp();
+        first = 0;
+      }
+      if (elect_one())
+        for (int k = 0; k < 4; ++k) umma_commit(&emptyB[(gbase + rows + k) % wt::kSlotsB]);
+      __syncwarp();
+      gbase += rows + 4;
+    }
+    if (elect_one()) umma_commit(done);
+    __syncwarp();
+  } else {
+    const int quarter = warp & 3;
+    float* dst = partials + (size_t)blockIdx.x * (32 * 16 * kTaps);
+    mbar_wait(done, 0);
+    tc_fence_after();
+    const int m = quarter * 32 + lane;
+    const int dxs = m >> 4, ci = m & 15;
+#pragma unroll 1
+    for (int jj = 0; jj < 5; ++jj) {
+      const int dy = 4 - jj;
+      uint32_t v[32];
+      const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + jj * 32;
+      tmem_ld16(taddr, *reinterpret_cast<uint32_t(*)[16]>(&v[0]));
+      tmem_ld16(taddr + 16, *reinterpret_cast<uint32_t(*)[16]>(&v[16]));
+      tmem_ld_wait();
+      if (m < 80) {
+#pragma unroll
+        for (int co = 0; co < 32; ++co)
+          dst[((size_t)co * 16 + ci) * kTaps + dy * 5 + dxs] = __uint_as_float(v[co]);
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  if (warp == 1) { __syncwarp(); tmem_dealloc<wt::kTmemCols>(tmem_base); }
+}
+
 // ------------------------------------------------------------- host side ----
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
@@ -1030,28 +1409,28 @@ ConvGeom make_geom(int B, int H, int W, int nsm, int halo_rows) {
   return g;
 }
 
-// 1 = tap-stationary + TMA, 2 = row-stationary + TMA, 3 = row-stationary + cp.async feed (default)
-int g_conv_tc_version = 3;
+// 1 = tap-stationary + TMA, 2 = row-stationary + TMA, 3 = row-stationary + cp.async feed,
+// 4 = 3 with the dx-replicated weight-gradient kernel (M = 128) (default)
+int g_conv_tc_version = 4;
 
-template <int CIN, int COUT, bool TRANSPOSED, int STATS, bool LDGSTS>
+template <int CIN, int COUT, bool TRANSPOSED, int STATS, bool LDGSTS, typename ET = __nv_bfloat16>
 int launch_conv_rs(const void* act, const void* w, const void* bias, void* out, void* partials, int B, int H, int W,
                    cudaStream_t s, int* grid_out, const void* pooled = nullptr, const void* bnprev = nullptr) {
-  using Cfg = RsCfg<CIN, COUT>;
-  auto kern = conv5x5_rs_kernel<CIN, COUT, TRANSPOSED, STATS, LDGSTS>;
-  static std::once_flag once;
-  static cudaError_t attr_err = cudaSuccess;
-  std::call_once(once, [&] {
-    attr_err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes);
-  });
-  B200_CUDA(attr_err);
+  using Cfg = RsCfg<CIN, COUT, ET>;
+  auto kern = conv5x5_rs_kernel<CIN, COUT, TRANSPOSED, STATS, LDGSTS, ET>;
+  B200_CUDA(set_max_smem(kern, Cfg::kSmemBytes));
   CUtensorMap tm;
-  int rc = make_act_tmap(&tm, act, B, H, W, CIN, kPW);
-  if (rc) return rc;
+  if (!LDGSTS) {
+    int rc = make_act_tmap(&tm, act, B, H, W, CIN, kPW);
+    if (rc) return rc;
+  } else {
+    memset(&tm, 0, sizeof(tm));          // the cp.async feed never touches the tensor map
+  }
   const int nsm = b200_compute_sms();
   ConvGeom g = make_geom(B, H, W, nsm, 4);
   const int grid = g.nitems < nsm ? g.nitems : nsm;
-  kern<<<grid, kRsThreads, Cfg::kSmemBytes, s>>>(tm, (const __nv_bfloat16*)act, (const float*)w, (const float*)bias,
-                                                (__nv_bfloat16*)out, (float*)partials, (const __nv_bfloat16*)pooled,
+  kern<<<grid, kRsThreads, Cfg::kSmemBytes, s>>>(tm, (const ET*)act, (const float*)w, (const float*)bias,
+                                                (ET*)out, (float*)partials, (const ET*)pooled,
                                                 (const float*)bnprev, g);
   B200_LAUNCH_CHECK();
   if (grid_out) *grid_out = grid;
@@ -1061,18 +1440,13 @@ int launch_conv_rs(const void* act, const void* w, const void* bias, void* out, 
 template <int CIN, int COUT, bool TRANSPOSED, bool STATS>
 int launch_conv(const void* act, const void* w, const void* bias, void* out, void* partials, int B, int H, int W,
                 cudaStream_t s, int* grid_out) {
-  if (g_conv_tc_version == 3)
+  if (g_conv_tc_version >= 3)
     return launch_conv_rs<CIN, COUT, TRANSPOSED, STATS ? 1 : 0, true>(act, w, bias, out, partials, B, H, W, s, grid_out);
   if (g_conv_tc_version == 2)
     return launch_conv_rs<CIN, COUT, TRANSPOSED, STATS ? 1 : 0, false>(act, w, bias, out, partials, B, H, W, s, grid_out);
   using Cfg = ConvCfg<CIN, COUT>;
   auto kern = conv5x5_tc_kernel<CIN, COUT, TRANSPOSED, STATS>;
-  static std::once_flag once;
-  static cudaError_t attr_err = cudaSuccess;
-  std::call_once(once, [&] {
-    attr_err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes);
-  });
-  B200_CUDA(attr_err);
+  B200_CUDA(set_max_smem(kern, Cfg::kSmemBytes));
   CUtensorMap tm;
   int rc = make_act_tmap(&tm, act, B, H, W, CIN, kPW);
   if (rc) return rc;
@@ -1086,13 +1460,32 @@ int launch_conv(const void* act, const void* w, const void* bias, void* out, voi
   return 0;
 }
 
+ConvGeom make_geom_w(int B, int H, int W, int nsm, int halo_rows, int strip) {
+  ConvGeom g = make_geom(B, H, (W + strip - 1) / strip * kBM, nsm, halo_rows);   // make_geom counts 128-px strips
+  g.W = W;
+  return g;
+}
+
+template <typename ET>
+int launch_wgrad_rep(const void* p1, const void* dx2, void* partials, void* dw2, int B, int H, int W, float gscale,
+                     cudaStream_t s) {
+  using Cfg = WgRepCfg<ET>;
+  B200_CUDA(set_max_smem(conv5x5_wgrad_rep_kernel<ET>, Cfg::kSmemBytes));
+  const int nsm = b200_compute_sms();
+  ConvGeom g = make_geom_w(B, H, W, nsm, 4, Cfg::kSP);
+  const int grid = g.nitems < nsm ? g.nitems : nsm;
+  conv5x5_wgrad_rep_kernel<ET><<<grid, kThreads, Cfg::kSmemBytes, s>>>((const ET*)p1, (const ET*)dx2, (float*)partials, g);
+  B200_LAUNCH_CHECK();
+  return b200_reduce_partials(partials, grid, 32 * 16 * kTaps, dw2, gscale, (void*)s);
+}
+
 }  // namespace
 
 // Number of partial-stat rows conv2_fwd writes (= its grid size); callers size
 // the partials buffer with b200_conv_tc_max_grid() x 2*COUT floats.
 B200_API int b200_conv_tc_max_grid() { return b200_num_sms(); }
 B200_API int b200_conv_tc_set_version(int v) {
-  if (v < 1 || v > 3) return b200_fail(-2, "conv_tc version must be 1, 2 or 3");
+  if (v < 1 || v > 4) return b200_fail(-2, "conv_tc version must be 1..4");
   g_conv_tc_version = v;
   return 0;
 }
@@ -1128,16 +1521,11 @@ B200_API int b200_conv2_dgrad_stats_tc(const void* dx2_bf16, const void* w2, con
 B200_API int b200_conv2_wgrad_tc(const void* p1_bf16, const void* dx2_bf16, void* partials, void* dw2, int B,
                                  int H, int W, float gscale, void* stream) {
   cudaStream_t s = (cudaStream_t)stream;
-  static std::once_flag once;
-  static cudaError_t attr_err = cudaSuccess;
-  std::call_once(once, [&] {
-    attr_err = cudaFuncSetAttribute(conv5x5_wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kWgSmemBytes);
-    if (attr_err == cudaSuccess)
-      attr_err = cudaFuncSetAttribute(conv5x5_wgrad_rs_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kWg2SmemBytes);
-    if (attr_err == cudaSuccess)
-      attr_err = cudaFuncSetAttribute(conv5x5_wgrad_rs_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kWg2SmemBytes);
-  });
-  B200_CUDA(attr_err);
+  if (g_conv_tc_version >= 4)
+    return launch_wgrad_rep<__nv_bfloat16>(p1_bf16, dx2_bf16, partials, dw2, B, H, W, gscale, s);
+  if (g_conv_tc_version == 3) B200_CUDA(set_max_smem(conv5x5_wgrad_rs_kernel<true>, kWg2SmemBytes));
+  else if (g_conv_tc_version == 2) B200_CUDA(set_max_smem(conv5x5_wgrad_rs_kernel<false>, kWg2SmemBytes));
+  else B200_CUDA(set_max_smem(conv5x5_wgrad_tc_kernel, kWgSmemBytes));
   CUtensorMap tma, tmb;
   int rc = make_act_tmap(&tma, p1_bf16, B, H, W, 16, kPW);
   if (rc) return rc;
@@ -1154,6 +1542,36 @@ B200_API int b200_conv2_wgrad_tc(const void* p1_bf16, const void* dx2_bf16, void
                                                                          (const __nv_bfloat16*)dx2_bf16, (float*)partials, g);
   else
     conv5x5_wgrad_tc_kernel<<<grid, kThreads, kWgSmemBytes, s>>>(tma, tmb, (float*)partials, g);
+  B200_LAUNCH_CHECK();
+  return b200_reduce_partials(partials, grid, 32 * 16 * kTaps, dw2, gscale, stream);
+}
+
+// ---- fp32 storage + kind::tf32 (the reference's precision: fp32 tensors, TF32 convolution math) ------------
+// Same contracts as the bf16 entry points above with every activation / gradient tensor in fp32.
+B200_API int b200_conv2_fwd_tc_f32(const void* p1, const void* w2, const void* b2, void* x2, void* partials, int B,
+                                   int H, int W, int* nparts_out, void* stream) {
+  return launch_conv_rs<16, 32, false, 1, true, float>(p1, w2, b2, x2, partials, B, H, W, (cudaStream_t)stream,
+                                                       nparts_out);
+}
+B200_API int b200_conv2_dgrad_tc_f32(const void* dx2, const void* w2, void* dp1, int B, int H, int W, void* stream) {
+  return launch_conv_rs<32, 16, true, 0, true, float>(dx2, w2, nullptr, dp1, nullptr, B, H, W, (cudaStream_t)stream,
+                                                      nullptr);
+}
+B200_API int b200_conv2_dgrad_stats_tc_f32(const void* dx2, const void* w2, const void* pooled, const void* bn1,
+                                           void* dp1, void* partials, int B, int H, int W, int* nparts_out,
+                                           void* stream) {
+  return launch_conv_rs<32, 16, true, 2, true, float>(dx2, w2, nullptr, dp1, partials, B, H, W, (cudaStream_t)stream,
+                                                      nparts_out, pooled, bn1);
+}
+B200_API int b200_conv2_wgrad_tc_f32(const void* p1, const void* dx2, void* partials, void* dw2, int B, int H, int W,
+                                     float gscale, void* stream) {
+  cudaStream_t s = (cudaStream_t)stream;
+  B200_CUDA(set_max_smem(conv5x5_wgrad_tf32_kernel, wt::kSmemBytes));
+  const int nsm = b200_compute_sms();
+  ConvGeom g = make_geom_w(B, H, W, nsm, 4, wt::kSP);
+  const int grid = g.nitems < nsm ? g.nitems : nsm;
+  conv5x5_wgrad_tf32_kernel<<<grid, kThreads, wt::kSmemBytes, s>>>((const float*)p1, (const float*)dx2,
+                                                                   (float*)partials, g);
   B200_LAUNCH_CHECK();
   return b200_reduce_partials(partials, grid, 32 * 16 * kTaps, dw2, gscale, stream);
 }

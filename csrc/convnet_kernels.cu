@@ -40,6 +40,44 @@ __device__ __forceinline__ uint2 ldg_stream8(const void* p) {
   return r;
 }
 
+// Activation storage: bf16 (the fast mode) or fp32 (the reference's precision).  Kernels below are templated
+// on the storage type and move 16-byte pieces: 8 bf16 or 4 fp32 channels.
+template <typename T> struct Act;
+template <> struct Act<__nv_bfloat16> {
+  static constexpr int kN = 8;                         // channels per 16-byte piece
+  __device__ static __forceinline__ void unpack(const uint4& v, float (&f)[8]) {
+    f[0] = bf16_lo(v.x); f[1] = bf16_hi(v.x); f[2] = bf16_lo(v.y); f[3] = bf16_hi(v.y);
+    f[4] = bf16_lo(v.z); f[5] = bf16_hi(v.z); f[6] = bf16_lo(v.w); f[7] = bf16_hi(v.w);
+  }
+  __device__ static __forceinline__ uint4 pack(const float (&f)[8]) {
+    return make_uint4(pack_bf16x2(f[0], f[1]), pack_bf16x2(f[2], f[3]), pack_bf16x2(f[4], f[5]), pack_bf16x2(f[6], f[7]));
+  }
+  // four consecutive elements (8 bytes)
+  __device__ static __forceinline__ void load4(const __nv_bfloat16* p, float (&f)[4]) {
+    const uint2 v = ldg_stream8(p);
+    f[0] = bf16_lo(v.x); f[1] = bf16_hi(v.x); f[2] = bf16_lo(v.y); f[3] = bf16_hi(v.y);
+  }
+  // stores four elements and returns them as stored (rounded) in f
+  __device__ static __forceinline__ void store4(__nv_bfloat16* p, float (&f)[4]) {
+    const uint2 o = make_uint2(pack_bf16x2(f[0], f[1]), pack_bf16x2(f[2], f[3]));
+    *reinterpret_cast<uint2*>(p) = o;
+    f[0] = bf16_lo(o.x); f[1] = bf16_hi(o.x); f[2] = bf16_lo(o.y); f[3] = bf16_hi(o.y);
+  }
+};
+template <> struct Act<float> {
+  static constexpr int kN = 4;
+  __device__ static __forceinline__ void unpack(const uint4& v, float (&f)[4]) {
+    f[0] = __uint_as_float(v.x); f[1] = __uint_as_float(v.y); f[2] = __uint_as_float(v.z); f[3] = __uint_as_float(v.w);
+  }
+  __device__ static __forceinline__ uint4 pack(const float (&f)[4]) {
+    return make_uint4(__float_as_uint(f[0]), __float_as_uint(f[1]), __float_as_uint(f[2]), __float_as_uint(f[3]));
+  }
+  __device__ static __forceinline__ void load4(const float* p, float (&f)[4]) { unpack(ldg_stream16(p), f); }
+  __device__ static __forceinline__ void store4(float* p, float (&f)[4]) {
+    *reinterpret_cast<float4*>(p) = make_float4(f[0], f[1], f[2], f[3]);
+  }
+};
+
 // ----------------------------------------------------------------- resize ---
 // K1/K2: the reference resizes 28x28 -> 3000x3000 on the CPU
 // with PIL (0.176 s/image) and ships 36 MB/image over PCIe.  Here the raw
@@ -246,14 +284,13 @@ __global__ void bn_finalize_kernel(const float* __restrict__ partials, int npart
 // K5/K7: one pass, bf16 NHWC in -> bf16 NHWC out at quarter size; no argmax
 // tensor is written (the reference's ATen max-pool stores int64 indices, 8 B
 // per output element).  One thread = one pooled pixel x 8 channels (16 B).
-template <int C>
+template <int C, typename T>
 __global__ void __launch_bounds__(256)
-bn_relu_pool_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ bn,
-                    __nv_bfloat16* __restrict__ p, int B, int H, int W) {
+bn_relu_pool_kernel(const T* __restrict__ x, const float* __restrict__ bn, T* __restrict__ p, int B, int H, int W) {
   __shared__ float s_sc[C], s_sh[C];
   if (threadIdx.x < C) { s_sc[threadIdx.x] = bn[threadIdx.x]; s_sh[threadIdx.x] = bn[C + threadIdx.x]; }
   __syncthreads();
-  constexpr int CH = C / 8;
+  constexpr int V = Act<T>::kN, CH = C / V;
   const int Ho = H / 2, Wo = W / 2;
   const size_t total = (size_t)B * Ho * Wo * CH;
   for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
@@ -263,26 +300,23 @@ bn_relu_pool_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict
     const int xo = (int)(pix % Wo); pix /= Wo;
     const int yo = (int)(pix % Ho);
     const int b = (int)(pix / Ho);
-    const __nv_bfloat16* base = x + (((size_t)b * H + 2 * yo) * W + 2 * xo) * C + ch * 8;
+    const T* base = x + (((size_t)b * H + 2 * yo) * W + 2 * xo) * C + ch * V;
     uint4 v[4];
     v[0] = ldg_stream16(base);
     v[1] = ldg_stream16(base + C);
     v[2] = ldg_stream16(base + (size_t)W * C);
     v[3] = ldg_stream16(base + (size_t)W * C + C);
-    uint32_t o[4];
+    float f[4][V], o[V];
 #pragma unroll
-    for (int e = 0; e < 4; ++e) {
-      float m0 = 0.f, m1 = 0.f;   // ReLU folded into the max: start from 0
+    for (int i = 0; i < 4; ++i) Act<T>::unpack(v[i], f[i]);
 #pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        uint32_t w = (&v[i].x)[e];
-        m0 = fmaxf(m0, fmaf(bf16_lo(w), s_sc[ch * 8 + 2 * e], s_sh[ch * 8 + 2 * e]));
-        m1 = fmaxf(m1, fmaf(bf16_hi(w), s_sc[ch * 8 + 2 * e + 1], s_sh[ch * 8 + 2 * e + 1]));
-      }
-      o[e] = pack_bf16x2(m0, m1);
+    for (int e = 0; e < V; ++e) {
+      float m = 0.f;   // ReLU folded into the max: start from 0
+#pragma unroll
+      for (int i = 0; i < 4; ++i) m = fmaxf(m, fmaf(f[i][e], s_sc[ch * V + e], s_sh[ch * V + e]));
+      o[e] = m;
     }
-    *reinterpret_cast<uint4*>(p + (((size_t)b * Ho + yo) * Wo + xo) * C + ch * 8) =
-        make_uint4(o[0], o[1], o[2], o[3]);
+    *reinterpret_cast<uint4*>(p + (((size_t)b * Ho + yo) * Wo + xo) * C + ch * V) = Act<T>::pack(o);
   }
 }
 
@@ -293,12 +327,12 @@ bn_relu_pool_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict
 //   MODE 0 (stats): per-channel  sum(dy), sum(dy * xhat)  -> partials
 //   MODE 1 (apply): dx = scale * (dy - mean(dy) - xhat * mean(dy*xhat)) -> bf16
 // bn = [scale | shift | mean | rstd]; red = [mean(dy) | mean(dy*xhat)].
-template <int C, int MODE>
+template <int C, int MODE, typename T>
 __global__ void __launch_bounds__(256)
-pool_bn_bwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dp,
+pool_bn_bwd_kernel(const T* __restrict__ x, const T* __restrict__ dp,
                    const float* __restrict__ bn, const float* __restrict__ red,
-                   float* __restrict__ partials, __nv_bfloat16* __restrict__ dx, int B, int H, int W) {
-  constexpr int CH = C / 8;
+                   float* __restrict__ partials, T* __restrict__ dx, int B, int H, int W) {
+  constexpr int V = Act<T>::kN, CH = C / V;
   __shared__ float s_bn[4 * C];
   __shared__ float s_red[2 * C];
   __shared__ float s_part[8][2 * C];
@@ -308,9 +342,9 @@ pool_bn_bwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __r
   const int Ho = H / 2, Wo = W / 2;
   const size_t total = (size_t)B * Ho * Wo * CH;
   const int ch = threadIdx.x % CH;   // blockDim (256) is a multiple of CH: fixed per thread
-  float a_dy[8], a_dyx[8];
+  float a_dy[V], a_dyx[V];
 #pragma unroll
-  for (int e = 0; e < 8; ++e) { a_dy[e] = 0.f; a_dyx[e] = 0.f; }
+  for (int e = 0; e < V; ++e) { a_dy[e] = 0.f; a_dyx[e] = 0.f; }
 
   for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
        idx += (size_t)gridDim.x * blockDim.x) {
@@ -318,23 +352,23 @@ pool_bn_bwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __r
     const int xo = (int)(pix % Wo); pix /= Wo;
     const int yo = (int)(pix % Ho);
     const int b = (int)(pix / Ho);
-    const size_t off0 = (((size_t)b * H + 2 * yo) * W + 2 * xo) * C + ch * 8;
+    const size_t off0 = (((size_t)b * H + 2 * yo) * W + 2 * xo) * C + ch * V;
     const size_t offs[4] = {off0, off0 + C, off0 + (size_t)W * C, off0 + (size_t)W * C + C};
     uint4 v[4];
 #pragma unroll
     for (int i = 0; i < 4; ++i) v[i] = ldg_stream16(x + offs[i]);
-    const uint4 g4 = ldg_stream16(dp + (((size_t)b * Ho + yo) * Wo + xo) * C + ch * 8);
-    uint32_t o[4][4];
+    const uint4 g4 = ldg_stream16(dp + (((size_t)b * Ho + yo) * Wo + xo) * C + ch * V);
+    float xf[4][V], gf[V], o[4][V];
 #pragma unroll
-    for (int e = 0; e < 8; ++e) {
-      const int c = ch * 8 + e;
+    for (int i = 0; i < 4; ++i) Act<T>::unpack(v[i], xf[i]);
+    Act<T>::unpack(g4, gf);
+#pragma unroll
+    for (int e = 0; e < V; ++e) {
+      const int c = ch * V + e;
       const float sc = s_bn[c], sh = s_bn[C + c], mu = s_bn[2 * C + c], rs = s_bn[3 * C + c];
       float xv[4];
 #pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        uint32_t w = (&v[i].x)[e >> 1];
-        xv[i] = (e & 1) ? bf16_hi(w) : bf16_lo(w);
-      }
+      for (int i = 0; i < 4; ++i) xv[i] = xf[i][e];
       int am = 0;
       float best = fmaf(xv[0], sc, sh);
 #pragma unroll
@@ -342,9 +376,7 @@ pool_bn_bwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __r
         float y = fmaf(xv[i], sc, sh);
         if (y > best) { best = y; am = i; }
       }
-      uint32_t gw = (&g4.x)[e >> 1];
-      float g = (e & 1) ? bf16_hi(gw) : bf16_lo(gw);
-      g = best > 0.f ? g : 0.f;
+      const float g = best > 0.f ? gf[e] : 0.f;
       if (MODE == 0) {
         float xa = xv[0];
 #pragma unroll
@@ -355,18 +387,14 @@ pool_bn_bwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __r
         const float mdy = s_red[c], mdyx = s_red[C + c];
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
-          float xh = (xv[i] - mu) * rs;
-          float d = sc * (((am == i) ? g : 0.f) - mdy - xh * mdyx);
-          // pack: even e -> low half, odd e -> high half
-          uint32_t bits = (uint32_t)__bfloat16_as_ushort(__float2bfloat16_rn(d));
-          if (e & 1) o[i][e >> 1] |= bits << 16; else o[i][e >> 1] = bits;
+          const float xh = (xv[i] - mu) * rs;
+          o[i][e] = sc * (((am == i) ? g : 0.f) - mdy - xh * mdyx);
         }
       }
     }
     if (MODE == 1) {
 #pragma unroll
-      for (int i = 0; i < 4; ++i)
-        *reinterpret_cast<uint4*>(dx + offs[i]) = make_uint4(o[i][0], o[i][1], o[i][2], o[i][3]);
+      for (int i = 0; i < 4; ++i) *reinterpret_cast<uint4*>(dx + offs[i]) = Act<T>::pack(o[i]);
     }
   }
   if (MODE == 0) {
@@ -374,14 +402,14 @@ pool_bn_bwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __r
     // over lanes that share (lane % CH), then across warps through smem.
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 #pragma unroll
-    for (int e = 0; e < 8; ++e) {
+    for (int e = 0; e < V; ++e) {
       float a = a_dy[e], q = a_dyx[e];
 #pragma unroll
       for (int o2 = 16; o2 >= CH; o2 >>= 1) {
         a += __shfl_xor_sync(0xffffffffu, a, o2);
         q += __shfl_xor_sync(0xffffffffu, q, o2);
       }
-      if (lane < CH) { s_part[warp][lane * 8 + e] = a; s_part[warp][C + lane * 8 + e] = q; }
+      if (lane < CH) { s_part[warp][lane * V + e] = a; s_part[warp][C + lane * V + e] = q; }
     }
     __syncthreads();
     if (threadIdx.x < 2 * C) {
@@ -424,9 +452,10 @@ __global__ void bn_bwd_finalize_kernel(const float* __restrict__ partials, int n
 // partials[block][c*25 + tap].
 constexpr int kWgT = 32;   // full-res tile edge
 
+template <typename T>
 __global__ void __launch_bounds__(256, 1)
-conv1_wgrad_kernel(const float* __restrict__ in, const __nv_bfloat16* __restrict__ x1,
-                   const __nv_bfloat16* __restrict__ dp1, const float* __restrict__ bn,
+conv1_wgrad_kernel(const float* __restrict__ in, const T* __restrict__ x1,
+                   const T* __restrict__ dp1, const float* __restrict__ bn,
                    const float* __restrict__ red, float* __restrict__ partials,
                    int B, int H, int W, int tilesX, int tilesY) {
   __shared__ float s_in[kWgT + 4][kWgT + 5];
@@ -468,21 +497,18 @@ conv1_wgrad_kernel(const float* __restrict__ in, const __nv_bfloat16* __restrict
       if (gy >= H || gx >= W) continue;       // H, W even: windows are all-or-nothing
       float dxv[4][4];                        // [pixel][channel]
       {
-        uint2 xr[4];
-        const __nv_bfloat16* xb = x1 + (((size_t)b * H + gy) * W + gx) * kC1 + cg * 4;
-        xr[0] = ldg_stream8(xb);
-        xr[1] = ldg_stream8(xb + kC1);
-        xr[2] = ldg_stream8(xb + (size_t)W * kC1);
-        xr[3] = ldg_stream8(xb + (size_t)W * kC1 + kC1);
-        const uint2 gr = ldg_stream8(dp1 + (((size_t)b * Ho + (gy >> 1)) * Wo + (gx >> 1)) * kC1 + cg * 4);
+        float xr[4][4], gr[4];
+        const T* xb = x1 + (((size_t)b * H + gy) * W + gx) * kC1 + cg * 4;
+        Act<T>::load4(xb, xr[0]);
+        Act<T>::load4(xb + kC1, xr[1]);
+        Act<T>::load4(xb + (size_t)W * kC1, xr[2]);
+        Act<T>::load4(xb + (size_t)W * kC1 + kC1, xr[3]);
+        Act<T>::load4(dp1 + (((size_t)b * Ho + (gy >> 1)) * Wo + (gx >> 1)) * kC1 + cg * 4, gr);
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
           float xv[4];
 #pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            uint32_t w = (c < 2) ? xr[i].x : xr[i].y;
-            xv[i] = (c & 1) ? bf16_hi(w) : bf16_lo(w);
-          }
+          for (int i = 0; i < 4; ++i) xv[i] = xr[i][c];
           int am = 0;
           float best = fmaf(xv[0], sc[c], sh[c]);
 #pragma unroll
@@ -490,9 +516,7 @@ conv1_wgrad_kernel(const float* __restrict__ in, const __nv_bfloat16* __restrict
             float y = fmaf(xv[i], sc[c], sh[c]);
             if (y > best) { best = y; am = i; }
           }
-          uint32_t gw = (c < 2) ? gr.x : gr.y;
-          float g = (c & 1) ? bf16_hi(gw) : bf16_lo(gw);
-          g = best > 0.f ? g : 0.f;
+          const float g = best > 0.f ? gr[c] : 0.f;
 #pragma unroll
           for (int i = 0; i < 4; ++i) {
             float xh = (xv[i] - mu[c]) * rs[c];
@@ -558,9 +582,9 @@ __global__ void reduce_partials_kernel(const float* __restrict__ partials, int n
 // grid; partial logits are reduced by fc_reduce_kernel.
 constexpr int kNC = 10;   // classes
 
-template <int BT>
+template <int BT, typename T>
 __global__ void __launch_bounds__(256)
-fc_fwd_kernel(const __nv_bfloat16* __restrict__ p2, const float* __restrict__ W,
+fc_fwd_kernel(const T* __restrict__ p2, const float* __restrict__ W,
               float* __restrict__ partials, size_t F) {
   float acc[BT][kNC];
 #pragma unroll
@@ -570,14 +594,14 @@ fc_fwd_kernel(const __nv_bfloat16* __restrict__ p2, const float* __restrict__ W,
   const size_t n4 = F / 4;
   for (size_t j = (size_t)blockIdx.x * 256 + threadIdx.x; j < n4; j += (size_t)gridDim.x * 256) {
     uint4 w[kNC];
-    uint2 a[BT];
+    float a[BT][4];
 #pragma unroll
     for (int k = 0; k < kNC; ++k) w[k] = ldg_stream16(W + (size_t)k * F + 4 * j);
 #pragma unroll
-    for (int b = 0; b < BT; ++b) a[b] = ldg_stream8(p2 + (size_t)b * F + 4 * j);
+    for (int b = 0; b < BT; ++b) Act<T>::load4(p2 + (size_t)b * F + 4 * j, a[b]);
 #pragma unroll
     for (int b = 0; b < BT; ++b) {
-      const float a0 = bf16_lo(a[b].x), a1 = bf16_hi(a[b].x), a2 = bf16_lo(a[b].y), a3 = bf16_hi(a[b].y);
+      const float a0 = a[b][0], a1 = a[b][1], a2 = a[b][2], a3 = a[b][3];
 #pragma unroll
       for (int k = 0; k < kNC; ++k) {
         float s = acc[b][k];
@@ -663,10 +687,10 @@ __global__ void ce_kernel(const float* __restrict__ logits, const long long* __r
 // sum(dy) and sum(dy * xhat) only involve the arg-max element of each pooling window, and its xhat follows
 // from the pooled value itself: y = p2 = scale*x + shift  =>  xhat = ((p2 - shift)/scale - mean) * rstd.
 // bn2 = [scale | shift | mean | rstd] (32 channels; channel = j % 32 in the HWC flatten order).
-template <int BT>
+template <int BT, typename T>
 __global__ void __launch_bounds__(256)
-fc_bwd_kernel(const float* __restrict__ dl, const __nv_bfloat16* __restrict__ p2, float* W,
-              float* dW, __nv_bfloat16* __restrict__ dp2, size_t F, float lr, int accumulate, float gscale,
+fc_bwd_kernel(const float* __restrict__ dl, const T* __restrict__ p2, float* W,
+              float* dW, T* __restrict__ dp2, size_t F, float lr, int accumulate, float gscale,
               const float* __restrict__ bn2, float* __restrict__ bwd_partials) {
   __shared__ float s_dl[BT * kNC];
   __shared__ float s_bp[8][64];
@@ -692,17 +716,11 @@ fc_bwd_kernel(const float* __restrict__ dl, const __nv_bfloat16* __restrict__ p2
   const size_t n4 = F / 4;
   for (size_t j = (size_t)blockIdx.x * 256 + threadIdx.x; j < n4; j += (size_t)gridDim.x * 256) {
     float4 w[kNC];
-    uint2 a[BT];
 #pragma unroll
     for (int k = 0; k < kNC; ++k) w[k] = *reinterpret_cast<const float4*>(W + (size_t)k * F + 4 * j);
-#pragma unroll
-    for (int b = 0; b < BT; ++b) a[b] = ldg_stream8(p2 + (size_t)b * F + 4 * j);
     float av[BT][4];
 #pragma unroll
-    for (int b = 0; b < BT; ++b) {
-      av[b][0] = bf16_lo(a[b].x); av[b][1] = bf16_hi(a[b].x);
-      av[b][2] = bf16_lo(a[b].y); av[b][3] = bf16_hi(a[b].y);
-    }
+    for (int b = 0; b < BT; ++b) Act<T>::load4(p2 + (size_t)b * F + 4 * j, av[b]);
     // dp2
 #pragma unroll
     for (int b = 0; b < BT; ++b) {
@@ -712,10 +730,9 @@ fc_bwd_kernel(const float* __restrict__ dl, const __nv_bfloat16* __restrict__ p2
         s.x = fmaf(d[b][k], w[k].x, s.x); s.y = fmaf(d[b][k], w[k].y, s.y);
         s.z = fmaf(d[b][k], w[k].z, s.z); s.w = fmaf(d[b][k], w[k].w, s.w);
       }
-      const uint2 o = make_uint2(pack_bf16x2(s.x, s.y), pack_bf16x2(s.z, s.w));
-      *reinterpret_cast<uint2*>(dp2 + (size_t)b * F + 4 * j) = o;
-      if (bn2) {     // BN2 backward reductions from the ROUNDED gradient (what the apply pass will read)
-        const float gq[4] = {bf16_lo(o.x), bf16_hi(o.x), bf16_lo(o.y), bf16_hi(o.y)};
+      float gq[4] = {s.x, s.y, s.z, s.w};
+      Act<T>::store4(dp2 + (size_t)b * F + 4 * j, gq);
+      if (bn2) {     // BN2 backward reductions from the STORED (rounded) gradient: what the apply pass will read
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
           const float y = av[b][i];
@@ -878,30 +895,38 @@ B200_API int b200_bn_finalize(const void* partials, int nparts, int C, double co
   return 0;
 }
 
-B200_API int b200_bn_relu_pool(const void* x, const void* bn, void* p, int B, int H, int W, int C, void* stream) {
+template <typename T>
+static int bn_relu_pool_t(const void* x, const void* bn, void* p, int B, int H, int W, int C, void* stream) {
   B200_CHECK(H % 2 == 0 && W % 2 == 0, "bn_relu_pool: H and W must be even");
-  const size_t work = (size_t)B * (H / 2) * (W / 2) * (C / 8);
+  const size_t work = (size_t)B * (H / 2) * (W / 2) * (C / Act<T>::kN);
   const int grid = grid_for(work, 256, b200_num_sms() * 16);
   cudaStream_t s = (cudaStream_t)stream;
-  if (C == 16) bn_relu_pool_kernel<16><<<grid, 256, 0, s>>>((const __nv_bfloat16*)x, (const float*)bn, (__nv_bfloat16*)p, B, H, W);
-  else if (C == 32) bn_relu_pool_kernel<32><<<grid, 256, 0, s>>>((const __nv_bfloat16*)x, (const float*)bn, (__nv_bfloat16*)p, B, H, W);
+  if (C == 16) bn_relu_pool_kernel<16, T><<<grid, 256, 0, s>>>((const T*)x, (const float*)bn, (T*)p, B, H, W);
+  else if (C == 32) bn_relu_pool_kernel<32, T><<<grid, 256, 0, s>>>((const T*)x, (const float*)bn, (T*)p, B, H, W);
   else return b200_fail(-2, "bn_relu_pool: C must be 16 or 32");
   B200_LAUNCH_CHECK();
   return 0;
+}
+B200_API int b200_bn_relu_pool(const void* x, const void* bn, void* p, int B, int H, int W, int C, void* stream) {
+  return bn_relu_pool_t<__nv_bfloat16>(x, bn, p, B, H, W, C, stream);
+}
+B200_API int b200_bn_relu_pool_f32(const void* x, const void* bn, void* p, int B, int H, int W, int C, void* stream) {
+  return bn_relu_pool_t<float>(x, bn, p, B, H, W, C, stream);
 }
 
 B200_API int b200_pool_bn_bwd_grid() { return b200_num_sms() * 8; }
 
 // mode 0: stats -> partials [grid][2C];  mode 1: apply -> dx
-B200_API int b200_pool_bn_bwd(const void* x, const void* dp, const void* bn, const void* red, void* partials,
-                              void* dx, int B, int H, int W, int C, int mode, void* stream) {
+template <typename T>
+static int pool_bn_bwd_t(const void* x, const void* dp, const void* bn, const void* red, void* partials,
+                         void* dx, int B, int H, int W, int C, int mode, void* stream) {
   B200_CHECK(H % 2 == 0 && W % 2 == 0, "pool_bn_bwd: H and W must be even");
   const int grid = b200_pool_bn_bwd_grid();
   cudaStream_t s = (cudaStream_t)stream;
 #define B200_PBB(CC, MM)                                                                              \
-  pool_bn_bwd_kernel<CC, MM><<<grid, 256, 0, s>>>((const __nv_bfloat16*)x, (const __nv_bfloat16*)dp,  \
+  pool_bn_bwd_kernel<CC, MM, T><<<grid, 256, 0, s>>>((const T*)x, (const T*)dp,  \
                                                   (const float*)bn, (const float*)red, (float*)partials, \
-                                                  (__nv_bfloat16*)dx, B, H, W)
+                                                  (T*)dx, B, H, W)
   if (C == 16 && mode == 0) B200_PBB(16, 0);
   else if (C == 16 && mode == 1) B200_PBB(16, 1);
   else if (C == 32 && mode == 0) B200_PBB(32, 0);
@@ -910,6 +935,14 @@ B200_API int b200_pool_bn_bwd(const void* x, const void* dp, const void* bn, con
 #undef B200_PBB
   B200_LAUNCH_CHECK();
   return 0;
+}
+B200_API int b200_pool_bn_bwd(const void* x, const void* dp, const void* bn, const void* red, void* partials,
+                              void* dx, int B, int H, int W, int C, int mode, void* stream) {
+  return pool_bn_bwd_t<__nv_bfloat16>(x, dp, bn, red, partials, dx, B, H, W, C, mode, stream);
+}
+B200_API int b200_pool_bn_bwd_f32(const void* x, const void* dp, const void* bn, const void* red, void* partials,
+                                  void* dx, int B, int H, int W, int C, int mode, void* stream) {
+  return pool_bn_bwd_t<float>(x, dp, bn, red, partials, dx, B, H, W, C, mode, stream);
 }
 
 B200_API int b200_bn_bwd_finalize(const void* partials, int nparts, int C, double count, void* red,
@@ -923,20 +956,30 @@ B200_API int b200_bn_bwd_finalize(const void* partials, int nparts, int C, doubl
 
 B200_API int b200_conv1_wgrad_grid() { return b200_num_sms(); }
 
-B200_API int b200_conv1_wgrad(const void* in_f32, const void* x1, const void* dp1, const void* bn,
-                              const void* red, void* partials, void* dw1, int B, int H, int W,
-                              float gscale, void* stream) {
+template <typename T>
+static int conv1_wgrad_t(const void* in_f32, const void* x1, const void* dp1, const void* bn,
+                         const void* red, void* partials, void* dw1, int B, int H, int W,
+                         float gscale, void* stream) {
   B200_CHECK(H % 2 == 0 && W % 2 == 0, "conv1_wgrad: H and W must be even");
   cudaStream_t s = (cudaStream_t)stream;
   const int tilesX = (W + kWgT - 1) / kWgT, tilesY = (H + kWgT - 1) / kWgT;
   const int grid = b200_conv1_wgrad_grid();
-  conv1_wgrad_kernel<<<grid, 256, 0, s>>>((const float*)in_f32, (const __nv_bfloat16*)x1,
-                                          (const __nv_bfloat16*)dp1, (const float*)bn, (const float*)red,
-                                          (float*)partials, B, H, W, tilesX, tilesY);
+  conv1_wgrad_kernel<T><<<grid, 256, 0, s>>>((const float*)in_f32, (const T*)x1, (const T*)dp1, (const float*)bn,
+                                             (const float*)red, (float*)partials, B, H, W, tilesX, tilesY);
   B200_LAUNCH_CHECK();
   reduce_partials_kernel<<<(400 + 127) / 128, 128, 0, s>>>((const float*)partials, grid, 400, (float*)dw1, gscale);
   B200_LAUNCH_CHECK();
   return 0;
+}
+B200_API int b200_conv1_wgrad(const void* in_f32, const void* x1, const void* dp1, const void* bn,
+                              const void* red, void* partials, void* dw1, int B, int H, int W,
+                              float gscale, void* stream) {
+  return conv1_wgrad_t<__nv_bfloat16>(in_f32, x1, dp1, bn, red, partials, dw1, B, H, W, gscale, stream);
+}
+B200_API int b200_conv1_wgrad_f32(const void* in_f32, const void* x1, const void* dp1, const void* bn,
+                                  const void* red, void* partials, void* dw1, int B, int H, int W,
+                                  float gscale, void* stream) {
+  return conv1_wgrad_t<float>(in_f32, x1, dp1, bn, red, partials, dw1, B, H, W, gscale, stream);
 }
 
 // ---------------------------------------------------------------------------------------
@@ -997,8 +1040,9 @@ B200_API int b200_conv1_wgrad_noalloc(const void* in_f32, const void* x1, const 
   }
   cudaStream_t s = (cudaStream_t)stream;
   const int tilesX = (W + kWgT - 1) / kWgT, tilesY = (H + kWgT - 1) / kWgT;
-  conv1_wgrad_kernel<<<grid, 256, 0, s>>>((const float*)in_f32, (const __nv_bfloat16*)x1, (const __nv_bfloat16*)dp1,
-                                          (const float*)bn, (const float*)red, scratch, B, H, W, tilesX, tilesY);
+  conv1_wgrad_kernel<__nv_bfloat16><<<grid, 256, 0, s>>>((const float*)in_f32, (const __nv_bfloat16*)x1,
+                                                         (const __nv_bfloat16*)dp1, (const float*)bn, (const float*)red,
+                                                         scratch, B, H, W, tilesX, tilesY);
   B200_LAUNCH_CHECK();
   reduce_partials_kernel<<<(400 + 127) / 128, 128, 0, s>>>(scratch, grid, 400, (float*)dw1, gscale);
   B200_LAUNCH_CHECK();
@@ -1015,14 +1059,15 @@ B200_API int b200_reduce_partials(const void* partials, int nparts, int len, voi
 B200_API int b200_fc_grid() { return b200_num_sms() * 4; }
 
 // logits[bt][10] for a batch chunk of bt <= 8 rows.
-B200_API int b200_fc_fwd(const void* p2, const void* W, const void* bias, void* partials, void* logits,
-                         int bt, size_t F, void* stream) {
+template <typename T>
+static int fc_fwd_t(const void* p2, const void* W, const void* bias, void* partials, void* logits,
+                    int bt, size_t F, void* stream) {
   B200_CHECK(bt >= 1 && bt <= 8, "fc_fwd: batch chunk must be 1..8 (got %d)", bt);
   B200_CHECK(F % 4 == 0, "fc_fwd: F must be a multiple of 4");
   cudaStream_t s = (cudaStream_t)stream;
   const int grid = b200_fc_grid();
   switch (bt) {
-#define B200_FCF(N) case N: fc_fwd_kernel<N><<<grid, 256, 0, s>>>((const __nv_bfloat16*)p2, (const float*)W, (float*)partials, F); break;
+#define B200_FCF(N) case N: fc_fwd_kernel<N, T><<<grid, 256, 0, s>>>((const T*)p2, (const float*)W, (float*)partials, F); break;
     B200_FCF(1) B200_FCF(2) B200_FCF(3) B200_FCF(4) B200_FCF(5) B200_FCF(6) B200_FCF(7) B200_FCF(8)
 #undef B200_FCF
   }
@@ -1030,6 +1075,14 @@ B200_API int b200_fc_fwd(const void* p2, const void* W, const void* bias, void* 
   fc_reduce_kernel<<<1, 128, 0, s>>>((const float*)partials, grid, bt * kNC, (const float*)bias, (float*)logits);
   B200_LAUNCH_CHECK();
   return 0;
+}
+B200_API int b200_fc_fwd(const void* p2, const void* W, const void* bias, void* partials, void* logits,
+                         int bt, size_t F, void* stream) {
+  return fc_fwd_t<__nv_bfloat16>(p2, W, bias, partials, logits, bt, F, stream);
+}
+B200_API int b200_fc_fwd_f32(const void* p2, const void* W, const void* bias, void* partials, void* logits,
+                             int bt, size_t F, void* stream) {
+  return fc_fwd_t<float>(p2, W, bias, partials, logits, bt, F, stream);
 }
 
 B200_API int b200_cross_entropy(const void* logits, const void* labels_i64, int B, void* loss, void* dlogits,
@@ -1041,20 +1094,29 @@ B200_API int b200_cross_entropy(const void* logits, const void* labels_i64, int 
 }
 
 // bn2 / bwd_partials (both nullable): fused BatchNorm-2 backward reductions, partials [b200_fc_grid()][64].
-B200_API int b200_fc_bwd(const void* dlogits, const void* p2, void* W, void* dW, void* dp2, int bt, size_t F,
-                         float lr, int accumulate, float gscale, const void* bn2, void* bwd_partials, void* stream) {
+template <typename T>
+static int fc_bwd_t(const void* dlogits, const void* p2, void* W, void* dW, void* dp2, int bt, size_t F,
+                    float lr, int accumulate, float gscale, const void* bn2, void* bwd_partials, void* stream) {
   B200_CHECK(bt >= 1 && bt <= 8, "fc_bwd: batch chunk must be 1..8 (got %d)", bt);
   B200_CHECK(F % 4 == 0, "fc_bwd: F must be a multiple of 4");
   B200_CHECK(!bn2 || (F % 32 == 0 && bwd_partials), "fc_bwd: fused BN statistics need F %% 32 == 0 and a partials buffer");
   cudaStream_t s = (cudaStream_t)stream;
   const int grid = b200_fc_grid();
   switch (bt) {
-#define B200_FCB(N) case N: fc_bwd_kernel<N><<<grid, 256, 0, s>>>((const float*)dlogits, (const __nv_bfloat16*)p2, (float*)W, (float*)dW, (__nv_bfloat16*)dp2, F, lr, accumulate, gscale, (const float*)bn2, (float*)bwd_partials); break;
+#define B200_FCB(N) case N: fc_bwd_kernel<N, T><<<grid, 256, 0, s>>>((const float*)dlogits, (const T*)p2, (float*)W, (float*)dW, (T*)dp2, F, lr, accumulate, gscale, (const float*)bn2, (float*)bwd_partials); break;
     B200_FCB(1) B200_FCB(2) B200_FCB(3) B200_FCB(4) B200_FCB(5) B200_FCB(6) B200_FCB(7) B200_FCB(8)
 #undef B200_FCB
   }
   B200_LAUNCH_CHECK();
   return 0;
+}
+B200_API int b200_fc_bwd(const void* dlogits, const void* p2, void* W, void* dW, void* dp2, int bt, size_t F,
+                         float lr, int accumulate, float gscale, const void* bn2, void* bwd_partials, void* stream) {
+  return fc_bwd_t<__nv_bfloat16>(dlogits, p2, W, dW, dp2, bt, F, lr, accumulate, gscale, bn2, bwd_partials, stream);
+}
+B200_API int b200_fc_bwd_f32(const void* dlogits, const void* p2, void* W, void* dW, void* dp2, int bt, size_t F,
+                             float lr, int accumulate, float gscale, const void* bn2, void* bwd_partials, void* stream) {
+  return fc_bwd_t<float>(dlogits, p2, W, dW, dp2, bt, F, lr, accumulate, gscale, bn2, bwd_partials, stream);
 }
 
 B200_API int b200_sgd(void* p, const void* g, size_t n, float lr, void* stream) {

@@ -129,6 +129,33 @@ __device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t a_desc, uint
       ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+// Same with fp32 data read as TF32 (the low 13 mantissa bits of each operand word are ignored), K = 8 per
+// instruction: the precision of the reference's cuDNN convolutions (torch.backends.cudnn.allow_tf32 = True).
+__device__ __forceinline__ void umma_tf32(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc,
+                                          uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// Element-type dispatch used by the kernels templated on the activation storage type.
+template <typename ET> struct UmmaKind;
+template <> struct UmmaKind<__nv_bfloat16> {
+  static constexpr uint32_t kFormat = 1;       // BF16
+  static constexpr int kK = 16;                // K per instruction (32 bytes)
+  __device__ static __forceinline__ void mma(uint32_t d, uint64_t a, uint64_t b, uint32_t idesc, uint32_t acc) {
+    umma_bf16(d, a, b, idesc, acc);
+  }
+};
+template <> struct UmmaKind<float> {
+  static constexpr uint32_t kFormat = 2;       // TF32
+  static constexpr int kK = 8;
+  __device__ static __forceinline__ void mma(uint32_t d, uint64_t a, uint64_t b, uint32_t idesc, uint32_t acc) {
+    umma_tf32(d, a, b, idesc, acc);
+  }
+};
 // Arrive on an mbarrier once every previously issued tcgen05.mma has retired.
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
@@ -163,6 +190,17 @@ __device__ __forceinline__ uint64_t smem_desc_noswz(uint32_t saddr, uint32_t lbo
   d |= static_cast<uint64_t>(1) << 46;
   return d;
 }
+// Same with an explicit layout type in bits [61,64): 0 = no swizzle, 1 = 128-byte swizzle with 32-byte
+// atomicity (the ONLY layout the hardware accepts for MN-major TF32 operands; CUTLASS sm100_common.inl:92 -
+// with the no-swizzle MN-major layout a kind::tf32 MMA silently accumulates zeros), 2 = 128B, 4 = 64B, 6 = 32B.
+__device__ __forceinline__ uint64_t smem_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes, uint32_t layout) {
+  return smem_desc_noswz(saddr, lbo_bytes, sbo_bytes) | (static_cast<uint64_t>(layout) << 61);
+}
+// MN-major TF32 operand tile ("SW128_32B"): a K row (one pixel) is 128 contiguous bytes = 32 fp32 MN elements,
+// rows 128 B apart, four rows per swizzle atom; the four 32-byte units of row k are permuted by XOR with (k & 3).
+// Byte offset of 32-byte unit `u` of row `k` inside a tile that starts 512-byte aligned:
+__device__ __forceinline__ uint32_t sw32_off(uint32_t k, uint32_t u) { return k * 128u + ((u ^ (k & 3u)) << 5); }
+
 // Instruction descriptor for kind::f16 with bf16 A/B and fp32 D
 // (CUTLASS InstrDescriptor): c_format[4,6)=1 (F32), a_format[7,10)=1 (BF16),
 // b_format[10,13)=1, a_major bit15, b_major bit16 (0 = K-major, 1 = MN-major),
@@ -170,6 +208,19 @@ __device__ __forceinline__ uint64_t smem_desc_noswz(uint32_t saddr, uint32_t lbo
 __host__ __device__ constexpr uint32_t umma_idesc_bf16(uint32_t M, uint32_t N, uint32_t a_mn_major, uint32_t b_mn_major) {
   return (1u << 4) | (1u << 7) | (1u << 10) | (a_mn_major << 15) | (b_mn_major << 16) |
          ((N >> 3) << 17) | ((M >> 4) << 24);
+}
+
+// Same for any F16/F32-family operand format (0 = F16, 1 = BF16, 2 = TF32), fp32 accumulate.
+__host__ __device__ constexpr uint32_t umma_idesc(uint32_t fmt, uint32_t M, uint32_t N, uint32_t a_mn_major, uint32_t b_mn_major) {
+  return (1u << 4) | (fmt << 7) | (fmt << 10) | (a_mn_major << 15) | (b_mn_major << 16) |
+         ((N >> 3) << 17) | ((M >> 4) << 24);
+}
+// fp32 -> tf32, round to nearest (ties away): used where WE choose the rounding (weights); operands fed
+// straight from memory are truncated by the tensor core.
+__device__ __forceinline__ float to_tf32_rna(float v) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(v));
+  return __uint_as_float(r);
 }
 
 // ------------------------------------------------------------ misc helpers --

@@ -71,6 +71,7 @@ class FusedConvNet:
     def __init__(self, image_shape: Sequence[int] = (3000, 3000), batch_size: int = 5,
                  device: Optional[torch.device] = None, lr: float = 1e-4, seed: int = 0,
                  init: str = "reference", conv_backend: str = "tc", fuse_fc_sgd: bool = True,
+                 precision: Optional[str] = None,
                  fc_weight_storage: Optional[torch.Tensor] = None,
                  fc_grad_storage: Optional[torch.Tensor] = None):
         if not torch.cuda.is_available():
@@ -83,6 +84,16 @@ class FusedConvNet:
         self.image_shape = (H, W)
         self.lr = float(lr)
         self.conv_backend = conv_backend
+        # "tf32": fp32 activation / gradient storage, kind::tf32 tensor-core math in conv2, hi/lo-split (fp32-level)
+        #         products in conv1, fp32 everywhere else - the reference's own numerics (fp32 tensors, cuDNN with
+        #         allow_tf32, fp32 cuBLAS fc; mnist_distributed.py:28-38 has no autocast).
+        # "bf16": bf16 activation / gradient storage and tensor-core operands, fp32 accumulation: the fast mode.
+        self.precision = (precision or os.environ.get("B200DP_PRECISION", "bf16")).lower()
+        if self.precision in ("fp32", "float32"):
+            self.precision = "tf32"
+        if self.precision not in ("bf16", "tf32"):
+            raise ValueError(f"precision must be 'bf16' or 'tf32', got {precision!r}")
+        self.act_dtype = torch.float32 if self.precision == "tf32" else torch.bfloat16
         self.conv1_backend = os.environ.get("B200DP_CONV1", "tc")      # "tc" (tcgen05) | "ffma"
         # BN-backward reductions fused into fc_bwd / the conv2-dgrad epilogue (0: separate passes over x2 / x1)
         self.fuse_bwd_stats = os.environ.get("B200DP_FUSE_BWD_STATS", "1") == "1"
@@ -96,7 +107,7 @@ class FusedConvNet:
         self.grad_scale = 1.0      # 1/world_size under DDP (fused into the producing kernels)
         dev, B = self.device, self.B
         f32 = dict(device=dev, dtype=torch.float32)
-        bf = dict(device=dev, dtype=torch.bfloat16)
+        bf = dict(device=dev, dtype=self.act_dtype)
 
         with torch.cuda.device(dev):
             # ---- parameters / buffers --------------------------------------
@@ -277,7 +288,7 @@ class FusedConvNet:
         if images is not None:
             self.set_input(images)
         P, B, H, W = self.params, self.B, self.H, self.W
-        if self.conv1_backend == "tc":
+        if self.conv1_backend == "tc" or self.precision == "tf32":
             n1 = ops.conv1_fwd_tc(self.x, P["layer1.0.weight"], P["layer1.0.bias"], self.x1, self.part_c1)
         else:
             ops.conv1_fwd(self.x, P["layer1.0.weight"], P["layer1.0.bias"], self.x1, self.part_c1)

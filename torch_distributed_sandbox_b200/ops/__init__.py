@@ -5,9 +5,11 @@ returns nothing (outputs are pre-allocated by the caller: the engine owns all
 activation memory so a training step allocates nothing).  ``LAUNCHES`` counts
 kernels launched by this module; ``bench.py`` reports it as ``gpu_launches``.
 
-Layouts: activations are bf16 **NHWC**, weights/grads fp32 in the reference's
-``state_dict`` layouts except ``fc.weight`` which is kept in HWC-flatten order
-internally (``fcw_permute`` converts for checkpoints).
+Layouts: activations are **NHWC**, bf16 (fast mode) or fp32 (the reference's precision:
+fp32 tensors, TF32 tensor-core math in the convolutions); the storage dtype of the
+activation argument selects the kernel variant (``*_f32`` entry points).  Weights/grads
+are fp32 in the reference's ``state_dict`` layouts except ``fc.weight`` which is kept in
+HWC-flatten order internally (``fcw_permute`` converts for checkpoints).
 """
 from __future__ import annotations
 
@@ -32,6 +34,16 @@ def _p(t) -> c_void_p:
 
 def _stream() -> c_void_p:
     return c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _fn(name: str, act):
+    """Entry point `name` for the storage dtype of activation tensor `act` (bf16 -> name, fp32 -> name_f32)."""
+    lib = _lib()
+    if act.dtype == torch.float32:
+        return getattr(lib, name + "_f32")
+    if act.dtype != torch.bfloat16:
+        raise TypeError(f"{name}: activations must be bfloat16 or float32, got {act.dtype}")
+    return getattr(lib, name)
 
 
 def _lib():
@@ -61,6 +73,9 @@ def _lib():
                                            c_void_p]
         lib.b200_reduce_partials.argtypes = [c_void_p, c_int, c_int, c_void_p, c_float, c_void_p]
         lib.b200_l2_flush.argtypes = [c_void_p, c_size_t, c_void_p]
+        for name in ("fc_fwd", "fc_bwd", "conv2_dgrad_stats_tc", "conv1_wgrad", "conv1_wgrad_tc", "conv1_fwd_tc", "conv2_wgrad_tc",
+                     "conv2_fwd_tc", "conv2_dgrad_tc"):
+            getattr(lib, f"b200_{name}_f32").argtypes = getattr(lib, f"b200_{name}").argtypes
         lib._b200_ops_bound = True
     return lib
 
@@ -96,7 +111,8 @@ def fc_grid() -> int:
 
 
 def conv_tc_set_version(v: int) -> None:
-    """tcgen05 conv variant: 1 = tap-stationary + TMA, 2 = row-stationary + TMA, 3 = row-stationary + cp.async (default)."""
+    """tcgen05 conv variant (bf16 kernels): 1 = tap-stationary + TMA, 2 = row-stationary + TMA, 3 = row-stationary +
+    cp.async, 4 = 3 with the dx-replicated M=128 weight-gradient kernel (default)."""
     _native.check(_lib().b200_conv_tc_set_version(int(v)), "conv_tc_set_version")
 
 
@@ -127,8 +143,8 @@ def conv1_fwd_tc(x_f32, w1, b1, x1_bf16, partials) -> int:
     Returns the number of BN-stat partial rows written (partials: [sm_count()][32])."""
     B, H, W = x_f32.shape
     n = c_int(0)
-    _native.check(_lib().b200_conv1_fwd_tc(_p(x_f32), _p(w1), _p(b1), _p(x1_bf16), _p(partials), B, H, W,
-                                           ctypes.byref(n), _stream()), "conv1_fwd_tc")
+    _native.check(_fn("b200_conv1_fwd_tc", x1_bf16)(_p(x_f32), _p(w1), _p(b1), _p(x1_bf16), _p(partials), B, H, W,
+                                                    ctypes.byref(n), _stream()), "conv1_fwd_tc")
     _count(1)
     return n.value
 
@@ -145,15 +161,18 @@ def bn_finalize(partials, nparts, C, count, gamma, beta, running_mean, running_v
 def bn_relu_pool(x_bf16, bn, p_bf16):
     """K5/K7: BN-apply + ReLU + 2x2 max-pool, bf16 NHWC -> bf16 NHWC."""
     B, H, W, C = x_bf16.shape
-    _native.check(_lib().b200_bn_relu_pool(_p(x_bf16), _p(bn), _p(p_bf16), B, H, W, C, _stream()), "bn_relu_pool")
+    assert x_bf16.dtype == p_bf16.dtype
+    _native.check(_fn("b200_bn_relu_pool", x_bf16)(_p(x_bf16), _p(bn), _p(p_bf16), B, H, W, C, _stream()),
+                  "bn_relu_pool")
     _count(1)
 
 
 def pool_bn_bwd(x_bf16, dp_bf16, bn, red, partials, dx_bf16, mode):
     """K11/K13: mode 0 = reduction partials, mode 1 = dense dx (may alias x)."""
     B, H, W, C = x_bf16.shape
-    _native.check(_lib().b200_pool_bn_bwd(_p(x_bf16), _p(dp_bf16), _p(bn), _p(red), _p(partials), _p(dx_bf16), B, H,
-                                          W, C, mode, _stream()), "pool_bn_bwd")
+    assert x_bf16.dtype == dp_bf16.dtype and (dx_bf16 is None or dx_bf16.dtype == x_bf16.dtype)
+    _native.check(_fn("b200_pool_bn_bwd", x_bf16)(_p(x_bf16), _p(dp_bf16), _p(bn), _p(red), _p(partials),
+                                                  _p(dx_bf16), B, H, W, C, mode, _stream()), "pool_bn_bwd")
     _count(1)
 
 
@@ -166,8 +185,9 @@ def bn_bwd_finalize(partials, nparts, C, count, red, dgamma, dbeta, gscale=1.0):
 def conv1_wgrad(x_f32, x1_bf16, dp1_bf16, bn, red, partials, dw1, gscale=1.0):
     """K13: fused pool1/ReLU1/BN1 backward + conv1 weight gradient."""
     B, H, W = x_f32.shape
-    _native.check(_lib().b200_conv1_wgrad(_p(x_f32), _p(x1_bf16), _p(dp1_bf16), _p(bn), _p(red), _p(partials),
-                                          _p(dw1), B, H, W, gscale, _stream()), "conv1_wgrad")
+    assert x1_bf16.dtype == dp1_bf16.dtype
+    _native.check(_fn("b200_conv1_wgrad", x1_bf16)(_p(x_f32), _p(x1_bf16), _p(dp1_bf16), _p(bn), _p(red),
+                                                   _p(partials), _p(dw1), B, H, W, gscale, _stream()), "conv1_wgrad")
     _count(2)
 
 
@@ -175,8 +195,10 @@ def conv1_wgrad_tc(x_f32, x1_bf16, dp1_bf16, bn, red, partials, dw1, gscale=1.0)
     """K13 on tcgen05: same contract as conv1_wgrad; pixels are the GEMM K dimension, the conv1-output
     gradient is produced into shared memory by CUDA-core warps and never touches HBM."""
     B, H, W = x_f32.shape
-    _native.check(_lib().b200_conv1_wgrad_tc(_p(x_f32), _p(x1_bf16), _p(dp1_bf16), _p(bn), _p(red), _p(partials),
-                                             _p(dw1), B, H, W, gscale, _stream()), "conv1_wgrad_tc")
+    assert x1_bf16.dtype == dp1_bf16.dtype
+    _native.check(_fn("b200_conv1_wgrad_tc", x1_bf16)(_p(x_f32), _p(x1_bf16), _p(dp1_bf16), _p(bn), _p(red),
+                                                      _p(partials), _p(dw1), B, H, W, gscale, _stream()),
+                  "conv1_wgrad_tc")
     _count(2)
 
 
@@ -184,8 +206,9 @@ def conv2_fwd_tc(p1_bf16, w2, b2, x2_bf16, partials) -> int:
     """K6 (tcgen05): conv(16->32) + BN-stat partials. Returns the number of partial rows."""
     B, H, W, _ = p1_bf16.shape
     n = c_int(0)
-    _native.check(_lib().b200_conv2_fwd_tc(_p(p1_bf16), _p(w2), _p(b2), _p(x2_bf16), _p(partials), B, H, W,
-                                           ctypes.byref(n), _stream()), "conv2_fwd_tc")
+    assert p1_bf16.dtype == x2_bf16.dtype
+    _native.check(_fn("b200_conv2_fwd_tc", p1_bf16)(_p(p1_bf16), _p(w2), _p(b2), _p(x2_bf16), _p(partials), B, H, W,
+                                                    ctypes.byref(n), _stream()), "conv2_fwd_tc")
     _count(1)
     return n.value
 
@@ -193,7 +216,8 @@ def conv2_fwd_tc(p1_bf16, w2, b2, x2_bf16, partials) -> int:
 def conv2_dgrad_tc(dx2_bf16, w2, dp1_bf16):
     """K12a (tcgen05): data gradient of conv2, [B,H,W,32] -> [B,H,W,16]."""
     B, H, W, _ = dx2_bf16.shape
-    _native.check(_lib().b200_conv2_dgrad_tc(_p(dx2_bf16), _p(w2), _p(dp1_bf16), B, H, W, _stream()),
+    assert dx2_bf16.dtype == dp1_bf16.dtype
+    _native.check(_fn("b200_conv2_dgrad_tc", dx2_bf16)(_p(dx2_bf16), _p(w2), _p(dp1_bf16), B, H, W, _stream()),
                   "conv2_dgrad_tc")
     _count(1)
 
@@ -201,16 +225,17 @@ def conv2_dgrad_tc(dx2_bf16, w2, dp1_bf16):
 def conv2_wgrad_tc(p1_bf16, dx2_bf16, partials, dw2, gscale=1.0):
     """K12b (tcgen05): weight gradient of conv2 -> [32,16,5,5] fp32."""
     B, H, W, _ = p1_bf16.shape
-    _native.check(_lib().b200_conv2_wgrad_tc(_p(p1_bf16), _p(dx2_bf16), _p(partials), _p(dw2), B, H, W, gscale,
-                                             _stream()), "conv2_wgrad_tc")
+    assert p1_bf16.dtype == dx2_bf16.dtype
+    _native.check(_fn("b200_conv2_wgrad_tc", p1_bf16)(_p(p1_bf16), _p(dx2_bf16), _p(partials), _p(dw2), B, H, W,
+                                                      gscale, _stream()), "conv2_wgrad_tc")
     _count(2)
 
 
 def fc_fwd(p2_bf16, W, bias, partials, logits):
     """K8: logits for a batch chunk of <= 8 rows. p2 [bt,F] bf16, W [10,F] fp32."""
     bt, F = p2_bf16.shape[0], p2_bf16[0].numel()
-    _native.check(_lib().b200_fc_fwd(_p(p2_bf16), _p(W), _p(bias), _p(partials), _p(logits), bt, F, _stream()),
-                  "fc_fwd")
+    _native.check(_fn("b200_fc_fwd", p2_bf16)(_p(p2_bf16), _p(W), _p(bias), _p(partials), _p(logits), bt, F,
+                                              _stream()), "fc_fwd")
     _count(2)
 
 
@@ -225,8 +250,10 @@ def fc_bwd(dlogits, p2_bf16, W, dW, dp2_bf16, lr=0.0, accumulate=False, gscale=1
     """K10(+K14): dW (optional), dp2 and optional in-place SGD on W, one streaming pass.  With ``bn2`` the
     BatchNorm-2 backward reductions are produced too (partials [fc_grid()][64]), replacing a pass over x2."""
     bt, F = p2_bf16.shape[0], p2_bf16[0].numel()
-    _native.check(_lib().b200_fc_bwd(_p(dlogits), _p(p2_bf16), _p(W), _p(dW), _p(dp2_bf16), bt, F, lr,
-                                     1 if accumulate else 0, gscale, _p(bn2), _p(bwd_partials), _stream()), "fc_bwd")
+    assert p2_bf16.dtype == dp2_bf16.dtype
+    _native.check(_fn("b200_fc_bwd", p2_bf16)(_p(dlogits), _p(p2_bf16), _p(W), _p(dW), _p(dp2_bf16), bt, F, lr,
+                                              1 if accumulate else 0, gscale, _p(bn2), _p(bwd_partials), _stream()),
+                  "fc_bwd")
     _count(1)
 
 
@@ -235,9 +262,10 @@ def conv2_dgrad_stats_tc(dx2_bf16, w2, pooled_p1, bn1, dp1_bf16, partials) -> in
     (``pooled_p1`` may alias ``dp1_bf16``).  Returns the number of partial rows ([rows][32])."""
     B, H, W, _ = dx2_bf16.shape
     n = c_int(0)
-    _native.check(_lib().b200_conv2_dgrad_stats_tc(_p(dx2_bf16), _p(w2), _p(pooled_p1), _p(bn1), _p(dp1_bf16),
-                                                   _p(partials), B, H, W, ctypes.byref(n), _stream()),
-                  "conv2_dgrad_stats_tc")
+    assert dx2_bf16.dtype == dp1_bf16.dtype == pooled_p1.dtype
+    _native.check(_fn("b200_conv2_dgrad_stats_tc", dx2_bf16)(_p(dx2_bf16), _p(w2), _p(pooled_p1), _p(bn1),
+                                                             _p(dp1_bf16), _p(partials), B, H, W, ctypes.byref(n),
+                                                             _stream()), "conv2_dgrad_stats_tc")
     _count(1)
     return n.value
 
