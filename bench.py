@@ -33,6 +33,11 @@ def parse():
     ap.add_argument("--impl", default="b200dp", choices=["b200dp", "reference"])
     ap.add_argument("--batch", type=int, default=5, help="per-GPU batch (reference: 5)")
     ap.add_argument("--image", type=int, default=3000, help="image edge (reference: 3000)")
+    ap.add_argument("--precision", default="both", choices=["both", "tf32", "bf16"],
+                    help="tf32 = the reference's numerics (fp32 tensors, TF32 conv math): the headline `value`; "
+                         "bf16 = the fast mode, reported under `bf16_mode`; both (default) measures the two")
+    ap.add_argument("--sustained-seconds", type=float, default=3.0,
+                    help="extra untimed-by-the-driver run of this many seconds with clock sampling (0 disables)")
     ap.add_argument("--stock-loader-steps", type=int, default=4,
                     help="reference arm: steps of the stock train() (CPU PIL resize) to time; 0 disables")
     return ap.parse_args()
@@ -88,7 +93,6 @@ def _physical_gpu_index(local_rank):
 # =============================================================== our framework ==
 def run_b200dp(a):
     import torch
-    import torch_distributed_sandbox_b200 as b2
     from torch_distributed_sandbox_b200 import distributed as dist, ops
     from torch_distributed_sandbox_b200.data.mnist import synthetic_digits
     from torch_distributed_sandbox_b200.models.module import FusedModule
@@ -99,22 +103,9 @@ def run_b200dp(a):
         raise SystemExit(f"--gpus {a.gpus} but WORLD_SIZE={world}: launch with torch.distributed.run --nproc-per-node {a.gpus}")
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
-    B, S = a.batch, a.image
-    notes = {}
+    B, S, K, W = a.batch, a.image, a.steps, a.warmup
     if world > 1:
-        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
-    model = FusedModule((S, S), batch_size=B, device=dev, lr=1e-4, seed=0)
-    if world > 1:
-        model = DistributedDataParallel(model, device_ids=[local_rank])
-        notes["allreduce"] = model._engine_sync.describe()
-    eng = (model.module if world > 1 else model).engine
-
-    nb = 8                                                    # distinct batches, cycled
-    imgs_np, labs_np = synthetic_digits(nb * B, seed=100 + rank)
-    host_imgs = torch.from_numpy(imgs_np).view(nb, B, 28, 28).pin_memory()
-    host_labs = torch.from_numpy(labs_np.astype("int64")).view(nb, B).pin_memory()
-    dev_imgs, dev_labs = host_imgs.to(dev), host_labs.to(dev)
-    loss_host = torch.zeros((), dtype=torch.float32).pin_memory()
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev, timeout=180)
 
     def sync_all():
         torch.cuda.synchronize()
@@ -129,50 +120,119 @@ def run_b200dp(a):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
-    step = model.train_step
+    # every step of every loop sees a batch it has not seen before (no cycling: final_loss means something)
+    W2 = max(3, W // 2)
+    nb = W + K + W2 + K
+    imgs_np, labs_np = synthetic_digits(nb * B, seed=100 + rank)
+    host_imgs = torch.from_numpy(imgs_np).view(nb, B, 28, 28).pin_memory()
+    host_labs = torch.from_numpy(labs_np.astype("int64")).view(nb, B).pin_memory()
+    dev_imgs, dev_labs = host_imgs.to(dev), host_labs.to(dev)
+    loss_host = torch.zeros((), dtype=torch.float32).pin_memory()
 
-    def dev_step(i):                                          # inputs already on the device
-        step(dev_imgs[i % nb], dev_labs[i % nb])
+    def measure(precision, sustained_s):
+        """Build the model at `precision`, time K device-resident steps and K end-to-end steps."""
+        model = FusedModule((S, S), batch_size=B, device=dev, lr=1e-4, seed=0, precision=precision)
+        notes = {}
+        if world > 1:
+            model = DistributedDataParallel(model, device_ids=[local_rank])
+            notes["allreduce"] = model._engine_sync.describe()
+        eng = (model.module if world > 1 else model).engine
+        step = model.train_step
+        losses = []
 
-    def e2e_step(i):                                          # H2D of this step's batch + D2H of its loss
-        x = host_imgs[i % nb].to(dev, non_blocking=True)
-        y = host_labs[i % nb].to(dev, non_blocking=True)
-        loss = step(x, y)
-        loss_host.copy_(loss, non_blocking=True)
-        torch.cuda.current_stream().synchronize()
+        traj = []
 
-    launches0 = ops.LAUNCHES
-    ms, clocks = timed_loop(dev_step, a.steps, a.warmup, sync_all, max_over_ranks, local_rank, drain=eng._sync_fc)
-    launches = (ops.LAUNCHES - launches0) * a.steps // (a.steps + a.warmup)
-    ms_e2e, _ = timed_loop(e2e_step, a.steps, max(3, a.warmup // 2), sync_all, max_over_ranks, local_rank,
-                           sample_clocks=False, drain=eng._sync_fc)
-    loss_val = float(loss_host)
-    peak = torch.cuda.max_memory_allocated(dev) / 2 ** 30
+        def dev_step(i):                                      # inputs already on the device
+            loss = step(dev_imgs[i], dev_labs[i])
+            if i < W:                                         # warm-up steps only: the start of the loss curve
+                traj.append(loss.clone())
+
+        def e2e_step(i):                                      # H2D of this step's batch + D2H of its loss
+            j = W + K + i
+            x = host_imgs[j].to(dev, non_blocking=True)
+            y = host_labs[j].to(dev, non_blocking=True)
+            loss = step(x, y)
+            loss_host.copy_(loss, non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+            losses.append(float(loss_host))
+
+        launches0 = ops.LAUNCHES
+        ms, clocks = timed_loop(dev_step, K, W, sync_all, max_over_ranks, local_rank, drain=eng._sync_fc)
+        launches = (ops.LAUNCHES - launches0) // (K + W)
+        ms_e2e, _ = timed_loop(e2e_step, K, W2, sync_all, max_over_ranks, local_rank, sample_clocks=False,
+                               drain=eng._sync_fc)
+        out = {"ms_per_step": ms, "ms_e2e": ms_e2e, "clocks": clocks, "launches_per_step": int(launches),
+               "loss_first_steps": [round(float(t), 4) for t in traj], "final_loss": losses[-1], "notes": notes,
+               "peak_mem_gib": round(torch.cuda.max_memory_allocated(dev) / 2 ** 30, 2)}
+        if sustained_s > 0:
+            # >= sustained_s seconds of back-to-back steps: the short timed region above is a burst number;
+            # this one shows clocks / power behaviour under sustained load (same step, batches re-used)
+            n = max(K, int(sustained_s * 1e3 / ms) + 1)
+            ms_s, clk_s = timed_loop(lambda i: step(dev_imgs[i % nb], dev_labs[i % nb]), n, 0, sync_all, max_over_ranks,
+                                     local_rank, drain=eng._sync_fc)
+            out["sustained"] = {"steps": n, "seconds": round(n * ms_s / 1e3, 2), "ms_per_step": ms_s,
+                                "value": B * world / ms_s * 1e3, "unit": "img/s",
+                                "clocks": {"sm_mhz": clk_s["sm_mhz"], "sm_max_mhz": clk_s["sm_max_mhz"],
+                                           "reasons": clk_s["reasons"], "samples": clk_s.get("samples"),
+                                           "power_w_max": clk_s.get("power_w_max")}}
+        if world > 1:
+            # replicas must hold bit-identical parameters after training (checked, not assumed)
+            eng._sync_fc()
+            torch.cuda.synchronize()
+            sums = torch.stack([eng.fcw.view(torch.int32).sum(dtype=torch.int64),
+                                eng.small.view(torch.int32).sum(dtype=torch.int64)])
+            gathered = [torch.zeros_like(sums) for _ in range(world)]
+            dist.all_gather(gathered, sums)
+            same = all(torch.equal(g, gathered[0]) for g in gathered)
+            out["replicas_bit_identical"] = bool(same)
+            if not same:
+                raise RuntimeError(f"rank parameter checksums differ after training: {[g.tolist() for g in gathered]}")
+        del model, eng, step
+        torch.cuda.empty_cache()
+        return out
+
+    want = ["tf32", "bf16"] if a.precision == "both" else [a.precision]
+    res = {}
+    for i, prec in enumerate(want):
+        res[prec] = measure(prec, a.sustained_seconds if i == 0 else 0.0)
     if world > 1:
         dist.destroy_process_group()
     if rank != 0:
         return
     gb = B * world
+    main = res[want[0]]
+    dtype = {"tf32": "fp32 storage, TF32 tensor-core conv math, fp32 fc/BN/loss/optimizer (the reference's numerics)",
+             "bf16": "bf16"}[want[0]]
     out = {
-        "metric": "images_per_sec", "value": gb / ms * 1e3, "unit": "img/s", "n_gpus": world, "steps": a.steps,
-        "warmup": a.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "bf16", "data": "synthetic", "impl": "b200dp",
+        "metric": "images_per_sec", "value": gb / main["ms_per_step"] * 1e3, "unit": "img/s", "n_gpus": world,
+        "steps": K, "warmup": W, "ms_per_step": main["ms_per_step"], "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": dtype, "precision": want[0], "data": "synthetic", "impl": "b200dp",
         "config": {"model": "sandbox ConvNet (conv5x5 1-16-32 + BN + ReLU + pool, fc 18M->10), SGD lr 1e-4",
                    "global_batch": gb, "seq_len": None, "image": [S, S], "per_gpu_batch": B,
                    "parallelism": f"dp{world}",
-                   "l2": "working set per step (2.7 GB activations + 1.4 GB weights) >> 126 MB L2; no flush needed",
-                   "precision": "bf16 activations/gradients, bf16 tensor-core operands, fp32 accumulate, "
-                                "fp32 master weights/statistics/optimizer"},
-        "clocks": {"sm_mhz": clocks["sm_mhz"], "sm_max_mhz": clocks["sm_max_mhz"], "reasons": clocks["reasons"]},
-        "e2e": {"value": gb / ms_e2e * 1e3, "unit": "img/s", "ms_per_step": ms_e2e,
+                   "l2": "working set per step (>= 2.7 GB activations + 1.4 GB weights) >> 126 MB L2; no flush needed",
+                   "batches": "synthetic digits, a fresh batch every step (nothing cycled inside the timed regions)"},
+        "clocks": {"sm_mhz": main["clocks"]["sm_mhz"], "sm_max_mhz": main["clocks"]["sm_max_mhz"],
+                   "reasons": main["clocks"]["reasons"]},
+        "e2e": {"value": gb / main["ms_e2e"] * 1e3, "unit": "img/s", "ms_per_step": main["ms_e2e"],
                 "h2d_bytes_per_step": int(host_imgs[0].numel() + host_labs[0].numel() * 8),
                 "d2h_bytes_per_step": 4,
                 "note": "input = raw uint8 digits in pinned host memory; resize 28->3000 runs on the GPU inside the step"},
-        "gpu_launches": int(launches // max(a.steps, 1)) * a.steps,
-        "gpu_launches_per_step": int(launches // max(a.steps, 1)),
-        "final_loss": loss_val, "peak_mem_gib": round(peak, 2),
+        "gpu_launches": main["launches_per_step"] * K, "gpu_launches_per_step": main["launches_per_step"],
+        "loss_first_steps": main["loss_first_steps"], "final_loss": main["final_loss"],
+        "peak_mem_gib": main["peak_mem_gib"],
     }
-    out.update(notes)
+    for k in ("sustained", "replicas_bit_identical"):
+        if k in main:
+            out[k] = main[k]
+    out.update(main["notes"])
+    if "bf16" in res and want[0] != "bf16":
+        r = res["bf16"]
+        out["bf16_mode"] = {"value": gb / r["ms_per_step"] * 1e3, "unit": "img/s", "ms_per_step": r["ms_per_step"],
+                            "e2e_value": gb / r["ms_e2e"] * 1e3, "e2e_ms_per_step": r["ms_e2e"],
+                            "final_loss": r["final_loss"], "gpu_launches_per_step": r["launches_per_step"],
+                            "note": "bf16 activation/gradient storage and tensor-core operands, fp32 accumulate and "
+                                    "master weights: lower precision than the reference, NOT the headline"}
     print(json.dumps(out))
 
 

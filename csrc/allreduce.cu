@@ -71,6 +71,11 @@ __device__ __forceinline__ void mc_st_b32x4(void* p, uint4 v) {
   asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
 
+// How long an in-kernel wait for a peer may last before it is declared dead.  Set from the process group's
+// timeout (init_process_group(timeout=), default 600 s like ProcessGroupNCCL) by b200_ar_set_timeout_ms: rank skew
+// of minutes is legitimate (rank 0 writing a 720 MB checkpoint, a first-step build, an eval phase before a barrier).
+__device__ unsigned long long g_wait_timeout_ns = 600ull * 1000000000ull;
+
 // Barrier across the same-index CTA of every rank.  Slot layout: flag[(block*kMaxRanks)+src].
 __device__ __forceinline__ void sys_barrier(const Peers& P, uint32_t epoch) {
   __threadfence_system();            // every thread publishes its own prior writes at system scope
@@ -80,12 +85,17 @@ __device__ __forceinline__ void sys_barrier(const Peers& P, uint32_t epoch) {
     st_release_sys(P.flag[t] + (size_t)blockIdx.x * kMaxRanks + P.rank, epoch);
     const uint32_t* mine = P.flag[P.rank] + (size_t)blockIdx.x * kMaxRanks + t;
     const uint64_t t0 = b2::globaltimer_ns();
+    const uint64_t limit = g_wait_timeout_ns;
     uint32_t spins = 0;
     // epochs are compared with wrap-safe signed distance
     while ((int32_t)(ld_acquire_sys(mine) - epoch) < 0) {
-      if ((++spins & 0x3FF) == 0 && b2::globaltimer_ns() - t0 > 20000000000ull) {
-        printf("b200dp: rank %d block %d timed out waiting for rank %d (epoch %u)\n", P.rank, blockIdx.x, t, epoch);
-        __trap();
+      if ((++spins & 0x3FF) == 0) {
+        if (b2::globaltimer_ns() - t0 > limit) {
+          printf("b200dp: rank %d block %d timed out after %llu ms waiting for rank %d (epoch %u)\n", P.rank,
+                 blockIdx.x, (unsigned long long)(limit / 1000000ull), t, epoch);
+          __trap();
+        }
+        __nanosleep(spins > 0x10000 ? 2000 : 100);      // a long wait should not hammer the peer's memory
       }
     }
   }
@@ -342,6 +352,14 @@ Peers make_peers(void* const* ptrs, void* const* flags, void* mc, int rank, int 
 }  // namespace
 
 // Bytes one channel's flag page needs on every rank.
+// Per device (the symbol lives in each device's copy of the module): call with the communicator's device current.
+B200_API int b200_ar_set_timeout_ms(long long ms) {
+  if (ms < 1) return b200_fail(-2, "collective timeout must be >= 1 ms");
+  const unsigned long long ns = (unsigned long long)ms * 1000000ull;
+  B200_CUDA(cudaMemcpyToSymbol(g_wait_timeout_ns, &ns, sizeof(ns)));
+  return 0;
+}
+
 B200_API size_t b200_ar_flag_bytes() { return (size_t)kMaxBlocks * kMaxRanks * sizeof(uint32_t); }
 B200_API int b200_ar_max_blocks() { return kMaxBlocks; }
 

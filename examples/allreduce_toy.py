@@ -39,8 +39,8 @@ def run(world_size, rank, steps):
 def setup(rank, world_size, backend="nccl", steps=10, init_method=None):
     if rank == -1:   # serial code
         return
-    if backend == "nccl" and torch.cuda.is_available():
-        torch.cuda.set_device(rank % torch.cuda.device_count())
+    # as in the reference (allreduce_toy.py:41-48) no torch.cuda.set_device: the group binds to the device of the
+    # first collective's tensor (cuda:rank), like ProcessGroupNCCL
     dist.init_process_group(backend, init_method=init_method, rank=rank, world_size=world_size)
     print(f"--> done setting up rank={rank}")
     run(world_size, rank, steps)

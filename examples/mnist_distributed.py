@@ -19,7 +19,7 @@ from torch import nn
 
 import torch_distributed_sandbox_b200 as b2
 from torch_distributed_sandbox_b200 import distributed as dist
-from torch_distributed_sandbox_b200.data.mnist import MNIST, DataLoader
+from torch_distributed_sandbox_b200.data.mnist import DataLoader, open_dataset
 from torch_distributed_sandbox_b200.data.resize import resize_u8_reference
 from torch_distributed_sandbox_b200.parallel import DistributedDataParallel, DistributedSampler
 
@@ -29,10 +29,10 @@ IMAGE_SHAPE = [3000, 3000]
 def train(gpu, args):
     rank = args.nr * args.gpus + gpu
     on_gpu = args.backend == "nccl"
-    if on_gpu:
-        torch.cuda.set_device(gpu)
-    dist.init_process_group(backend=args.backend, world_size=args.world_size, rank=rank)
+    dist.init_process_group(backend=args.backend, world_size=args.world_size, rank=rank)   # mnist_distributed.py:50
     torch.manual_seed(0)
+    if on_gpu:
+        torch.cuda.set_device(gpu)                  # after init, as in the reference (:57): the group binds lazily
     batch_size = args.batch_size                    # per GPU: effective batch = batch_size * world_size
     if args.model == "fused":
         from torch_distributed_sandbox_b200.models.module import FusedModule
@@ -47,10 +47,9 @@ def train(gpu, args):
         criterion = nn.CrossEntropyLoss()
         optimizer = torch.optim.SGD(model.parameters(), 1e-4)
         model = DistributedDataParallel(model, device_ids=[gpu] if on_gpu else None)
-    dataset = MNIST(args.data, train=True, synthetic=args.synthetic)
+    dataset = open_dataset(args.data, synthetic=args.synthetic, quiet=(gpu != 0))
     sampler = DistributedSampler(dataset, num_replicas=args.world_size, rank=rank)
-    loader = DataLoader(dataset, batch_size=batch_size, shuffle=False, pin_memory=on_gpu, sampler=sampler,
-                        drop_last=True)
+    loader = DataLoader(dataset, batch_size=batch_size, shuffle=False, pin_memory=on_gpu, sampler=sampler)
     start = datetime.now()
     total_step = len(loader) if args.max_steps is None else min(len(loader), args.max_steps)
     for epoch in range(args.epochs):
@@ -92,13 +91,14 @@ def parse(argv=None):
     parser.add_argument("--backend", default="nccl", choices=["nccl", "gloo"])
     parser.add_argument("--model", default=None, choices=["fused", "eager"])
     parser.add_argument("--data", default="./data")
-    parser.add_argument("--synthetic", default=60000, type=int)
+    parser.add_argument("--synthetic", default=None, type=int,
+                        help="train on N generated digits (default: the idx files under --data when present, "
+                             "else 60000 generated digits)")
     parser.add_argument("--max-steps", default=None, type=int)
     parser.add_argument("--log-every", default=100, type=int)
     parser.add_argument("--save", default=None)
     args = parser.parse_args(argv)
     args.world_size = args.gpus * args.nodes
-    args.synthetic = args.synthetic or None
     if args.backend == "nccl" and not torch.cuda.is_available():
         print("no CUDA device: using --backend gloo --model eager")
         args.backend = "gloo"

@@ -15,7 +15,7 @@ from datetime import datetime
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 
-from torch_distributed_sandbox_b200.data.mnist import MNIST, DataLoader
+from torch_distributed_sandbox_b200.data.mnist import DataLoader, open_dataset
 
 IMAGE_SHAPE = [3000, 3000]
 
@@ -26,8 +26,8 @@ def train(gpu, args):
     torch.cuda.set_device(gpu)
     batch_size = args.batch_size            # 5 in the reference (10 OOMs a 24 GB card: mnist_onegpu.py:44-45)
     model = FusedModule(args.image_shape, batch_size=batch_size, device=torch.device("cuda", gpu), lr=1e-4, seed=0)
-    dataset = MNIST(args.data, train=True, synthetic=args.synthetic)
-    loader = DataLoader(dataset, batch_size=batch_size, shuffle=True, pin_memory=True, drop_last=True)
+    dataset = open_dataset(args.data, synthetic=args.synthetic, quiet=(gpu != 0))
+    loader = DataLoader(dataset, batch_size=batch_size, shuffle=True, pin_memory=True)
     start = datetime.now()
     total_step = len(loader) if args.max_steps is None else min(len(loader), args.max_steps)
     for epoch in range(args.epochs):
@@ -53,12 +53,13 @@ def parse(argv=None):
     parser.add_argument("--image-shape", default=IMAGE_SHAPE, type=int, nargs=2)
     parser.add_argument("--batch-size", default=5, type=int)
     parser.add_argument("--data", default="./data")
-    parser.add_argument("--synthetic", default=60000, type=int, help="generate N synthetic digits (0: read --data)")
+    parser.add_argument("--synthetic", default=None, type=int,
+                        help="train on N generated digits (default: the idx files under --data when present, "
+                             "else 60000 generated digits)")
     parser.add_argument("--max-steps", default=None, type=int)
     parser.add_argument("--log-every", default=100, type=int)
     parser.add_argument("--save", default=None, help="write a torch state_dict checkpoint here")
     args = parser.parse_args(argv)
-    args.synthetic = args.synthetic or None
     return args
 
 

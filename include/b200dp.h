@@ -62,7 +62,9 @@ int b200_conv1_wgrad(const void* in_f32, const void* x1_bf16, const void* dp1_bf
  * until exit) instead of a caller buffer.  nblocks = thread blocks / partial rows (0: the SM count);
  * more than b200_conv1_wgrad_noalloc_max_blocks() (160) is rejected.  The first call on each device
  * resolves the array's address - make it outside stream capture.  All calls on a device share the
- * array: serialise calls that could overlap on the GPU.  Never calls cudaMalloc/cudaFree. */
+ * array: serialise calls that could overlap on the GPU.  Never calls cudaMalloc/cudaFree.
+ * It launches the CUDA-core (FFMA) kernel of b200_conv1_wgrad - about 2 ms at batch 5, 3000x3000 - not the
+ * 0.7 ms tcgen05 kernel of b200_conv1_wgrad_tc, and takes bf16 x1 / dp1 only. */
 int b200_conv1_wgrad_noalloc_max_blocks(void);
 int b200_conv1_wgrad_noalloc(const void* in_f32, const void* x1_bf16, const void* dp1_bf16, const void* bn,
                              const void* red, void* dw1, int B, int H, int W, float gscale, int nblocks,
@@ -79,7 +81,8 @@ int b200_conv1_wgrad_tc(const void* in_f32, const void* x1_bf16, const void* dp1
  * mnist_distributed.py:34,96.  partials (fwd): [b200_conv_tc_max_grid()][64];
  * partials (wgrad): [b200_conv_tc_max_grid()][12800] scratch. */
 int b200_conv_tc_max_grid(void);
-int b200_conv_tc_set_version(int v);   /* 1 tap-stationary+TMA, 2 row-stationary+TMA, 3 row-stationary+cp.async (default) */
+int b200_conv_tc_set_version(int v);   /* 1 tap-stationary+TMA, 2 row-stationary+TMA, 3 row-stationary+cp.async,
+                                          4 = 3 + dx-replicated M=128 weight-gradient kernel (default) */
 int b200_conv_tc_get_version(void);
 int b200_set_reserved_sms(int n);      /* SM partition for an overlapped collective (DDP); 0 = none, at most SM count - 1 */
 int b200_get_reserved_sms(void);
@@ -102,6 +105,33 @@ int b200_cross_entropy(const void* logits, const void* labels_i64, int B, void* 
 int b200_fc_bwd(const void* dlogits, const void* p2_bf16, void* W, void* dW_or_null, void* dp2_bf16, int bt, size_t F,
                 float lr_fused_sgd, int accumulate, float gscale, const void* bn2_or_null, void* bwd_partials_or_null,
                 void* stream);
+
+/* ------------------------------- fp32 storage / TF32 math ("tf32" mode) --- */
+/* ref: the reference's own numerics - fp32 tensors everywhere, cuDNN convolutions with allow_tf32 (the default),
+ * fp32 cuBLAS fc (mnist_distributed.py:28-38, no autocast).  Same contracts as the entry points above with every
+ * activation / gradient tensor in fp32 (NHWC); conv2 runs tcgen05.mma.kind::tf32, conv1 forward keeps its bf16
+ * hi/lo split (fp32-level products), conv1 weight gradient is kind::tf32 (tc) or exact fp32 FFMA. */
+int b200_conv1_fwd_tc_f32(const void* in_f32, const void* w1, const void* b1, void* x1_f32, void* partials, int B,
+                          int H, int W, int* nparts_out, void* stream);
+int b200_bn_relu_pool_f32(const void* x, const void* bn, void* p, int B, int H, int W, int C, void* stream);
+int b200_pool_bn_bwd_f32(const void* x, const void* dp, const void* bn, const void* red, void* partials, void* dx,
+                         int B, int H, int W, int C, int mode, void* stream);
+int b200_conv1_wgrad_f32(const void* in_f32, const void* x1, const void* dp1, const void* bn, const void* red,
+                         void* partials, void* dw1, int B, int H, int W, float gscale, void* stream);
+int b200_conv1_wgrad_tc_f32(const void* in_f32, const void* x1, const void* dp1, const void* bn, const void* red,
+                            void* partials, void* dw1, int B, int H, int W, float gscale, void* stream);
+int b200_conv2_fwd_tc_f32(const void* p1, const void* w2, const void* b2, void* x2, void* partials, int B, int H,
+                          int W, int* nparts_out, void* stream);
+int b200_conv2_dgrad_tc_f32(const void* dx2, const void* w2, void* dp1, int B, int H, int W, void* stream);
+int b200_conv2_dgrad_stats_tc_f32(const void* dx2, const void* w2, const void* pooled_p1, const void* bn1, void* dp1,
+                                  void* partials, int B, int H, int W, int* nparts_out, void* stream);
+int b200_conv2_wgrad_tc_f32(const void* p1, const void* dx2, void* partials, void* dw2, int B, int H, int W,
+                            float gscale, void* stream);
+int b200_fc_fwd_f32(const void* p2, const void* W, const void* bias, void* partials, void* logits, int bt, size_t F,
+                    void* stream);
+int b200_fc_bwd_f32(const void* dlogits, const void* p2, void* W, void* dW_or_null, void* dp2, int bt, size_t F,
+                    float lr_fused_sgd, int accumulate, float gscale, const void* bn2_or_null,
+                    void* bwd_partials_or_null, void* stream);
 
 /* ------------------------------------------------------ optimizer (K14) --- */
 /* ref: torch.optim.SGD(model.parameters(), 1e-4).step(), mnist_distributed.py:65,97. */
@@ -133,6 +163,8 @@ int b200_ar_max_blocks(void);
 int b200_ar_barrier(void* const* flags, int rank, int world, uint32_t epoch, void* stream);
 int b200_ar_oneshot(void* const* ptrs, void* const* flags, int rank, int world, void* out, size_t n, int dtype, int op,
                     float scale, int blocks, uint32_t epoch, void* stream);
+/* in-kernel waits for a peer give up (diagnostic + trap) after this long; set from init_process_group(timeout=) */
+int b200_ar_set_timeout_ms(long long ms);
 int b200_ar_oneshot_f32x4(void* const* ptrs, void* const* flags, int rank, int world, void* out, void* param, size_t n,
                           float scale, float lr, int blocks, uint32_t epoch, void* stream);
 int b200_ar_large_f32(void* const* ptrs, void* mc, void* const* flags, void* const* wptrs, void* wmc, int rank,

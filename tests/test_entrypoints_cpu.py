@@ -92,7 +92,7 @@ def test_mnist_distributed_cpu_eager_two_ranks(tmp_path):
                           "gloo", "--model", "eager", "--image-shape", "32", "32", "--synthetic", "64", "--epochs", "1",
                           "--log-every", "2", "--save", ck], capture_output=True, text=True, timeout=600)
     assert out.returncode == 0, out.stderr[-3000:]
-    assert re.search(r"Rank \[0\], Epoch \[1/1\], Step \[2/6\], Loss: \d+\.\d{4}", out.stdout), out.stdout
+    assert re.search(r"Rank \[0\], Epoch \[1/1\], Step \[2/7\], Loss: \d+\.\d{4}", out.stdout), out.stdout
     assert "Training complete in: " in out.stdout
     sd = torch.load(ck)
     assert list(sd.keys())[0] == "module.layer1.0.weight" and sd["module.fc.weight"].shape == (10, 32 * 8 * 8)

@@ -144,8 +144,11 @@ def test_tf32_engine_matches_pure_fp32_model():
             errs[k] = rel(grads[k], gref)
             print(f"[engine/tf32]   grad {k}: rel-L2 {errs[k]:.3e}")
         for k, e in errs.items():
-            # layer 1 sits behind two BatchNorm backward cancellations and both pooling arg-max choices
-            assert e < (2e-2 if k.startswith("layer1") else 5e-3), f"grad {k}: {e}"
+            # Parameters whose gradient is a BatchNorm-backward sum with heavy cancellation (conv weights, BN-1, BN-2
+            # beta) amplify the 2^-11 TF32 operand rounding to ~1e-2: torch's own cuDNN TF32 path shows 1e-2 .. 6e-2
+            # on the same quantities at this shape (profiles/precision_error_vs_cudnn_tf32.txt); the rest is tight.
+            loose = k.startswith("layer1") or k in ("layer2.0.weight", "layer2.1.bias")
+            assert e < (3e-2 if loose else 2e-3), f"grad {k}: {e}"
     sd, sd_ref = eng.state_dict(), ref.state_dict()
     for k in sd_ref:
         if k.endswith("num_batches_tracked"):
@@ -213,3 +216,23 @@ def test_uint8_input_path_and_batch_gt_8():
         l1 = float(eng.train_step(imgs.to(DEV), labels.to(DEV)))
     print(f"[engine] overfit one batch: {l0:.4f} -> {l1:.4f}")
     assert l1 < l0
+
+
+@pytest.mark.parametrize("precision", ["bf16", "tf32"])
+def test_short_last_batch_equals_an_engine_of_that_size(precision):
+    """drop_last=False (mnist_onegpu.py:55-59): a batch smaller than the engine's capacity runs on leading-dimension
+    views of the same buffers and must give exactly what an engine built for that batch size gives."""
+    from torch_distributed_sandbox_b200.models.engine import FusedConvNet
+    shape = (64, 96)
+    big = FusedConvNet(shape, batch_size=5, device=DEV, lr=1e-2, precision=precision)
+    small = FusedConvNet(shape, batch_size=3, device=DEV, lr=1e-2, precision=precision)
+    g = torch.Generator().manual_seed(3)
+    full = torch.randint(0, 256, (5, 28, 28), dtype=torch.uint8, generator=g).to(DEV)
+    lab = torch.randint(0, 10, (5,), generator=g).to(DEV)
+    big.train_step(full, lab)                      # leaves stale rows 3..4 in every activation buffer
+    small.load_state_dict(big.state_dict())
+    l_big = float(big.train_step(full[:3], lab[:3]))
+    l_small = float(small.train_step(full[:3], lab[:3]))
+    assert l_big == l_small
+    assert torch.equal(big.fcw, small.fcw) and torch.equal(big.small, small.small)
+    assert torch.equal(big.bn_flat, small.bn_flat)

@@ -11,6 +11,7 @@ Checked here, calling both entry points with ctypes exactly as a C program would
   * the result equals the caller-scratch entry point's (same grid: the same bits; a different
     grid: within the band the other kernel tests use), on two calls in a row with different
     inputs - the second call sees the first call's leftovers in the shared scratch;
+  * it also equals a plain PyTorch fp32 computation of the same gradient;
   * a grid larger than the built-in scratch is refused with a message, nothing is launched.
 The file name sorts last on purpose: a run that stops at the first failure has then already
 run every other test.  It passes alone in a fresh process and after the rest of the suite.
@@ -52,6 +53,25 @@ def rel(a, b):
     return float((a.double() - b.double()).norm() / (b.double().norm() + 1e-12))
 
 
+def _torch_oracle(xin, x1, dp1, bn, red):
+    """Plain PyTorch fp32 statement of what the kernel computes: the pool / ReLU / BatchNorm backward of dp1 through
+    the stored conv output x1 (first maximum of each 2x2 window, as ATen picks it), then the conv1 weight gradient."""
+    import torch.nn.functional as F
+    x = x1.float().permute(0, 3, 1, 2)                      # [B,16,H,W]
+    g = dp1.float().permute(0, 3, 1, 2)
+    sc, sh, mu, rs = (bn[i].view(1, 16, 1, 1) for i in range(4))
+    mdy, mdyx = red[0].view(1, 16, 1, 1), red[1].view(1, 16, 1, 1)
+    y = x * sc + sh
+    B, C, H, W = y.shape
+    win = y.view(B, C, H // 2, 2, W // 2, 2).permute(0, 1, 2, 4, 3, 5).reshape(B, C, H // 2, W // 2, 4)
+    best, am = win.max(dim=-1)                              # torch.max returns the first maximum on ties
+    routed = torch.where(best > 0, g, torch.zeros_like(g))
+    onehot = F.one_hot(am, 4).to(routed.dtype) * routed.unsqueeze(-1)
+    dense = onehot.view(B, C, H // 2, W // 2, 2, 2).permute(0, 1, 2, 4, 3, 5).reshape(B, C, H, W)
+    dx = sc * (dense - mdy - (x - mu) * rs * mdyx)
+    return torch.nn.grad.conv2d_weight(xin[:, None], (16, 1, 5, 5), dx, padding=2)
+
+
 def test_noalloc_matches_caller_scratch_entry_point_twice_and_rejects_oversize():
     lib = _lib()
     stream = c_void_p(torch.cuda.current_stream().cuda_stream)
@@ -76,6 +96,9 @@ def test_noalloc_matches_caller_scratch_entry_point_twice_and_rejects_oversize()
         torch.cuda.synchronize()
         assert torch.isfinite(got).all()
         assert torch.equal(got, want), f"call {call}: rel-L2 {rel(got, want):.3e}"
+        # ... and both agree with an independent fp32 PyTorch computation of the same quantity
+        oracle = _torch_oracle(xin, x1, dp1, bn, red)
+        assert rel(got, oracle) < 2e-3, f"call {call}: rel-L2 vs torch {rel(got, oracle):.3e}"
         # a different grid re-partitions the sum: equal within the kernel tests' tolerance
         got2 = torch.zeros(16, 1, 5, 5, device=DEV)
         rc = lib.b200_conv1_wgrad_noalloc(ptr(xin), ptr(x1), ptr(dp1), ptr(bn), ptr(red), ptr(got2), B, H, W, 1.0,

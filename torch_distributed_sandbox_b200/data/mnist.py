@@ -78,6 +78,26 @@ def write_synthetic_idx(root: str = "./data", n_train: int = 60000, n_test: int 
     return raw
 
 
+def raw_files_present(root: str = "./data", train: bool = True) -> bool:
+    """True when ``root/MNIST/raw`` holds the idx files (plain or .gz) - the presence-only check torchvision does."""
+    raw = os.path.join(root, "MNIST", "raw")
+    return all(os.path.exists(os.path.join(raw, f)) or os.path.exists(os.path.join(raw, f) + ".gz")
+               for f in _FILES[train])
+
+
+def open_dataset(root: str = "./data", synthetic: Optional[int] = None, train: bool = True, quiet: bool = False):
+    """What the entrypoints train on.  ``synthetic=None`` (the default) reads the real idx files under ``root`` when
+    they are there - as the reference does after its download (mnist_onegpu.py:51-54) - and only otherwise falls back
+    to 60,000 synthetic digits, saying so; ``synthetic=N`` forces N generated digits."""
+    if synthetic is None and raw_files_present(root, train):
+        return MNIST(root, train=train)
+    n = 60000 if synthetic is None else int(synthetic)
+    if synthetic is None and not quiet:
+        print(f"note: no MNIST idx files under {os.path.join(root, 'MNIST', 'raw')} (and no network to download "
+              f"them): training on {n} synthetic MNIST-shaped digits")
+    return MNIST(root, train=train, synthetic=n)
+
+
 class MNIST:
     """uint8 digits + int64 labels held as CPU tensors.  ``synthetic=N`` skips the disk."""
 

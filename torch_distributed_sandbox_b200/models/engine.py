@@ -100,6 +100,7 @@ class FusedConvNet:
         self.fuse_fc_sgd = bool(fuse_fc_sgd)
         self.F = rn.feature_size((H, W))
         self.comm = None           # set by parallel.ddp for data-parallel runs
+        self._b = int(batch_size)  # size of the batch currently in the buffers (<= B: short last batch)
         self._fc_fused_done = False
         self._fc_pending = False
         self._publish_grads = lambda: None
@@ -265,75 +266,90 @@ class FusedConvNet:
         if images.dtype == torch.uint8:
             if images.dim() == 4:
                 images = images[:, 0]
-            assert images.shape[0] == self.B, f"batch {images.shape[0]} != engine batch {self.B}"
+            b = int(images.shape[0])
+            assert 1 <= b <= self.B, f"batch {b} exceeds the engine's batch capacity {self.B}"
+            self._b = b
             sh, sw = int(images.shape[-2]), int(images.shape[-1])
             key = (sh, sw)
             if key not in self._tabs:
                 self._tabs[key] = (torch.from_numpy(pil_bilinear_table(sw, self.W)).to(self.device),
                                    torch.from_numpy(pil_bilinear_table(sh, self.H)).to(self.device))
-            if self._u8 is None or self._u8.shape != images.shape:
-                self._u8 = torch.empty(images.shape, device=self.device, dtype=torch.uint8)
-            self._u8.copy_(images, non_blocking=True)
+            if self._u8 is None or self._u8.shape[1:] != images.shape[1:]:
+                self._u8 = torch.empty((self.B,) + tuple(images.shape[1:]), device=self.device, dtype=torch.uint8)
+            self._u8[:b].copy_(images, non_blocking=True)
             xt, yt = self._tabs[key]
-            ops.resize_pil_bilinear(self._u8, xt, yt, self.x)
+            ops.resize_pil_bilinear(self._u8[:b], xt, yt, self.x[:b])
         else:
             if images.dim() == 4:
                 images = images[:, 0]
-            assert tuple(images.shape) == (self.B, self.H, self.W), f"bad input shape {tuple(images.shape)}"
-            self.x.copy_(images, non_blocking=True)
+            b = int(images.shape[0])
+            assert 1 <= b <= self.B and tuple(images.shape[1:]) == (self.H, self.W), \
+                f"bad input shape {tuple(images.shape)} (capacity {self.B} x {self.H} x {self.W})"
+            self._b = b
+            self.x[:b].copy_(images, non_blocking=True)
 
     # ---------------------------------------------------------------- forward --
     def forward(self, images: Optional[torch.Tensor] = None) -> torch.Tensor:
         """Train-mode forward (batch statistics, running stats updated). Returns logits [B,10]."""
         if images is not None:
             self.set_input(images)
-        P, B, H, W = self.params, self.B, self.H, self.W
+        # B = size of THIS batch: a short last batch (the reference's loaders are drop_last=False,
+        # mnist_onegpu.py:55-59) runs on leading-dimension views of the same buffers
+        P, B, H, W = self.params, self._b, self.H, self.W
+        x, x1, p1, x2, p2t = self.x[:B], self.x1[:B], self.p1[:B], self.x2[:B], self.p2[:B]
         if self.conv1_backend == "tc" or self.precision == "tf32":
-            n1 = ops.conv1_fwd_tc(self.x, P["layer1.0.weight"], P["layer1.0.bias"], self.x1, self.part_c1)
+            n1 = ops.conv1_fwd_tc(x, P["layer1.0.weight"], P["layer1.0.bias"], x1, self.part_c1)
         else:
-            ops.conv1_fwd(self.x, P["layer1.0.weight"], P["layer1.0.bias"], self.x1, self.part_c1)
+            ops.conv1_fwd(x, P["layer1.0.weight"], P["layer1.0.bias"], x1, self.part_c1)
             n1 = self.g_c1
         ops.bn_finalize(self.part_c1, n1, 16, B * H * W, P["layer1.1.weight"], P["layer1.1.bias"],
                         self.bn_buf[1]["mean"], self.bn_buf[1]["var"], self.bn_buf[1]["nbt"], self.bn1)
-        ops.bn_relu_pool(self.x1, self.bn1, self.p1)
+        ops.bn_relu_pool(x1, self.bn1, p1)
         if self.conv_backend == "tc":
-            nparts = ops.conv2_fwd_tc(self.p1, P["layer2.0.weight"], P["layer2.0.bias"], self.x2, self.part_c2)
+            nparts = ops.conv2_fwd_tc(p1, P["layer2.0.weight"], P["layer2.0.bias"], x2, self.part_c2)
         else:
             nparts = self._conv2_fwd_torch()
         ops.bn_finalize(self.part_c2, nparts, 32, B * (H // 2) * (W // 2), P["layer2.1.weight"],
                         P["layer2.1.bias"], self.bn_buf[2]["mean"], self.bn_buf[2]["var"], self.bn_buf[2]["nbt"],
                         self.bn2)
-        ops.bn_relu_pool(self.x2, self.bn2, self.p2)
-        p2 = self.p2.view(B, self.F)
+        ops.bn_relu_pool(x2, self.bn2, p2t)
+        p2 = p2t.view(B, self.F)
         self._sync_fc()
         for b0 in range(0, B, 8):
             b1 = min(B, b0 + 8)
             ops.fc_fwd(p2[b0:b1], self.fcw, P["fc.bias"], self.part_fc, self.logits[b0:b1])
-        return self.logits
+        return self.logits[:B]
 
     # --------------------------------------------------------------- backward --
     def loss_backward(self, labels: torch.Tensor) -> torch.Tensor:
         """Cross-entropy (mean) + full backward.  Leaves gradients in ``self.grads`` /
         ``self.fcw_grad``; with ``fuse_fc_sgd`` and no comm, fc.weight is updated in place here."""
-        self._labels.copy_(labels, non_blocking=True)
-        ops.cross_entropy(self.logits, self._labels, self.loss, self.dlogits, self.grads["fc.bias"], self.grad_scale)
+        B = self._b
+        assert labels.shape[0] == B, f"{labels.shape[0]} labels for a batch of {B}"
+        self._labels[:B].copy_(labels, non_blocking=True)
+        ops.cross_entropy(self.logits[:B], self._labels[:B], self.loss, self.dlogits[:B], self.grads["fc.bias"],
+                          self.grad_scale)
         self._backward(allow_fused_sgd=True)
         return self.loss
 
     def backward_from_dlogits(self, dlogits: torch.Tensor) -> None:
         """Backward for an externally computed loss (autograd front-end, models/module.py)."""
-        self.dlogits.copy_(dlogits)
-        self.grads["fc.bias"].copy_(self.dlogits.sum(0) * self.grad_scale)
+        B = self._b
+        self.dlogits[:B].copy_(dlogits)
+        self.grads["fc.bias"].copy_(self.dlogits[:B].sum(0) * self.grad_scale)
         self._backward(allow_fused_sgd=False)
 
     def _backward(self, allow_fused_sgd: bool) -> None:
-        P, G, B, H, W = self.params, self.grads, self.B, self.H, self.W
+        P, G, B, H, W = self.params, self.grads, self._b, self.H, self.W
+        x, x1, p1, x2 = self.x[:B], self.x1[:B], self.p1[:B], self.x2[:B]
+        dx2, dp1 = x2, p1                  # in-place gradients (dp2 over p2, dx2 over x2, dp1 over p1)
         gs = self.grad_scale
         fused = allow_fused_sgd and self.fuse_fc_sgd and self.comm is None and B <= 8
         if not fused and self.fcw_grad is None:
             self.fcw_grad = torch.empty_like(self.fcw)
-        p2 = self.p2.view(B, self.F)
-        dp2 = self.dp2.view(B, self.F)
+        p2 = self.p2[:B].view(B, self.F)
+        dp2 = p2
+        dp2t = self.p2[:B]
         fuse_stats = self.fuse_bwd_stats and self.conv_backend == "tc"
         for b0 in range(0, B, 8):
             b1 = min(B, b0 + 8)
@@ -353,18 +369,18 @@ class FusedConvNet:
             ops.bn_bwd_finalize(self.part_fcb, self.g_fc, 32, B * H2 * W2, self.red2, G["layer2.1.weight"],
                                 G["layer2.1.bias"], gs)
         else:
-            ops.pool_bn_bwd(self.x2, self.dp2, self.bn2, self.red2, self.part_bwd, None, mode=0)
+            ops.pool_bn_bwd(x2, dp2t, self.bn2, self.red2, self.part_bwd, None, mode=0)
             ops.bn_bwd_finalize(self.part_bwd, self.g_pbb, 32, B * H2 * W2, self.red2, G["layer2.1.weight"],
                                 G["layer2.1.bias"], gs)
-        ops.pool_bn_bwd(self.x2, self.dp2, self.bn2, self.red2, None, self.dx2, mode=1)
+        ops.pool_bn_bwd(x2, dp2t, self.bn2, self.red2, None, dx2, mode=1)
         if defer_ar:
             self.comm.fc_grad_ready(self)
         if self.conv_backend == "tc":
-            ops.conv2_wgrad_tc(self.p1, self.dx2, self.part_wg2, G["layer2.0.weight"], gs)
+            ops.conv2_wgrad_tc(p1, dx2, self.part_wg2, G["layer2.0.weight"], gs)
             if fuse_stats:   # dgrad epilogue also reduces BN1's backward sums (reads p1 before dp1 overwrites it)
-                n1 = ops.conv2_dgrad_stats_tc(self.dx2, P["layer2.0.weight"], self.p1, self.bn1, self.dp1, self.part_bwd)
+                n1 = ops.conv2_dgrad_stats_tc(dx2, P["layer2.0.weight"], p1, self.bn1, dp1, self.part_bwd)
             else:
-                ops.conv2_dgrad_tc(self.dx2, P["layer2.0.weight"], self.dp1)
+                ops.conv2_dgrad_tc(dx2, P["layer2.0.weight"], dp1)
         else:
             self._conv2_bwd_torch(gs)
         G["layer2.0.bias"].zero_()      # a bias feeding BatchNorm has an analytically zero gradient
@@ -373,11 +389,11 @@ class FusedConvNet:
             ops.bn_bwd_finalize(self.part_bwd, n1, 16, B * H * W, self.red1, G["layer1.1.weight"],
                                 G["layer1.1.bias"], gs)
         else:
-            ops.pool_bn_bwd(self.x1, self.dp1, self.bn1, self.red1, self.part_bwd, None, mode=0)
+            ops.pool_bn_bwd(x1, dp1, self.bn1, self.red1, self.part_bwd, None, mode=0)
             ops.bn_bwd_finalize(self.part_bwd, self.g_pbb, 16, B * H * W, self.red1, G["layer1.1.weight"],
                                 G["layer1.1.bias"], gs)
         wg1 = ops.conv1_wgrad_tc if self.conv1_backend == "tc" else ops.conv1_wgrad
-        wg1(self.x, self.x1, self.dp1, self.bn1, self.red1, self.part_wg1, G["layer1.0.weight"], gs)
+        wg1(x, x1, dp1, self.bn1, self.red1, self.part_wg1, G["layer1.0.weight"], gs)
         G["layer1.0.bias"].zero_()
 
     def step(self) -> None:
@@ -420,11 +436,12 @@ class FusedConvNet:
     # ------------------------------------------------ torch fallbacks (debug) --
     def _conv2_fwd_torch(self) -> int:
         P = self.params
-        x = self.p1.permute(0, 3, 1, 2).float()
+        B = self._b
+        x = self.p1[:B].permute(0, 3, 1, 2).float()
         w = P["layer2.0.weight"].to(torch.bfloat16).float()
         y = F.conv2d(x, w, P["layer2.0.bias"], padding=2)
-        self.x2.copy_(y.permute(0, 2, 3, 1))
-        r = self.x2.float()
+        self.x2[:B].copy_(y.permute(0, 2, 3, 1))
+        r = self.x2[:B].float()
         self.part_c2.zero_()
         self.part_c2[0, :32] = r.sum(dim=(0, 1, 2))
         self.part_c2[0, 32:] = (r * r).sum(dim=(0, 1, 2))
@@ -432,12 +449,13 @@ class FusedConvNet:
 
     def _conv2_bwd_torch(self, gs: float) -> None:
         P, G = self.params, self.grads
-        dy = self.dx2.permute(0, 3, 1, 2).float()
-        x = self.p1.permute(0, 3, 1, 2).float()
+        B = self._b
+        dy = self.dx2[:B].permute(0, 3, 1, 2).float()
+        x = self.p1[:B].permute(0, 3, 1, 2).float()
         w = P["layer2.0.weight"].to(torch.bfloat16).float()
         G["layer2.0.weight"].copy_(torch.nn.grad.conv2d_weight(x, w.shape, dy, padding=2) * gs)
         dxin = torch.nn.grad.conv2d_input(x.shape, w, dy, padding=2)
-        self.dp1.copy_(dxin.permute(0, 2, 3, 1))
+        self.dp1[:B].copy_(dxin.permute(0, 2, 3, 1))
 
     def activation_bytes(self) -> int:
         ts = (self.x, self.x1, self.p1, self.x2, self.p2)

@@ -129,6 +129,14 @@ class DistributedDataParallel(nn.Module):
     # -------------------------------------------------------------- buckets --
     def _build_buckets(self, ordered: List[nn.Parameter], limits) -> None:
         plan = plan_buckets([p.data for p in ordered], limits)
+        # the iteration-1 bucket spans the whole model (720 MB for the 3000x3000 net): give its symmetric memory
+        # back before the rebuilt buckets are allocated instead of holding both until the group is destroyed
+        free = getattr(self.process_group.backend, "free_symmetric", None)
+        old, self._buckets, self._where = getattr(self, "_buckets", []), [], {}
+        for b in old:
+            flat, b.flat, b.views = b.flat, None, []
+            if free is not None and flat is not None and flat.is_cuda:
+                free(flat)
         self._buckets = [_Bucket([ordered[i] for i in idx], self.process_group.backend, self.world_size)
                          for idx in plan]
         self._where = {}

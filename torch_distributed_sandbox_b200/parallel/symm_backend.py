@@ -57,6 +57,23 @@ def _lib():
     return lib
 
 
+def _on_device(fn):
+    """Run a collective with the group's device current (so `current_stream()` is that device's stream) -
+    a no-op in the usual one-GPU-per-process set-up where it already is."""
+    import functools
+
+    @functools.wraps(fn)
+    def wrapper(self, *a, **k):
+        if self.size > 1 and (self._comm is None or self.device is None):
+            self._ensure(next((x for x in a if isinstance(x, torch.Tensor) and x.is_cuda), None))
+        dev = self.device
+        if dev is None or self.size == 1 or torch.cuda.current_device() == dev.index:
+            return fn(self, *a, **k)
+        with torch.cuda.device(dev):
+            return fn(self, *a, **k)
+    return wrapper
+
+
 class _CudaView:
     """Minimal ``__cuda_array_interface__`` carrier so torch can wrap raw symmetric memory."""
 
@@ -104,22 +121,55 @@ class SymmBackend:
 
     def __init__(self, store, job: str, gid: int, ranks: Tuple[int, ...], my_global_rank: int,
                  device: Optional[torch.device], timeout: float):
-        lib = _lib()
         self.ranks, self.size = tuple(ranks), len(ranks)
         self.rank = self.ranks.index(my_global_rank)
-        self.device = torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
         self.timeout = timeout
         self._buffers: List[SymmBuffer] = []
         self._comm = None
         self.epoch = [4, 4]
-        if self.size == 1:
-            self.multicast = False
+        self.multicast = False
+        self._tag = f"b200dp_{job}_{gid}".encode()
+        # Like ProcessGroupNCCL, the communicator is bound to a device LAZILY: the reference calls
+        # init_process_group before torch.cuda.set_device (mnist_distributed.py:50,57) and allreduce_toy.py never
+        # calls set_device at all, so the device is only known at the first collective (from its tensor, or the
+        # then-current device).  With an explicit device_id the bring-up happens right away.
+        self.device: Optional[torch.device] = torch.device(device) if device is not None else None
+        if self.size > 1 and self.device is not None:
+            self._bring_up()
+
+    def _ensure(self, t: Optional[torch.Tensor] = None) -> None:
+        """COLLECTIVE on first use: bind to the tensor's device (else the current device) and map the peers."""
+        if self._comm is not None or self.size == 1:
+            if self.device is None:
+                self.device = t.device if (t is not None and t.is_cuda) else torch.device("cuda", torch.cuda.current_device())
+            if t is not None and t.is_cuda and t.device != self.device:
+                raise RuntimeError(f"collective on a tensor of {t.device}, but this process group is bound to "
+                                   f"{self.device} (one process drives one GPU; pass device_id= or call "
+                                   f"torch.cuda.set_device before the first collective)")
             return
+        if self.device is None:
+            self.device = t.device if (t is not None and t.is_cuda) else torch.device("cuda", torch.cuda.current_device())
+        self._bring_up()
+
+    def _bring_up(self) -> None:
+        lib = _lib()
+        timeout = self.timeout
+        with torch.cuda.device(self.device):
+            torch.zeros(1, device=self.device)          # make sure the primary context exists
+        prev = torch.cuda.current_device()
         torch.cuda.set_device(self.device)
-        tag = f"b200dp_{job}_{gid}".encode()
+        try:
+            self._bring_up_locked(lib, timeout)
+        finally:
+            torch.cuda.set_device(prev)
+
+    def _bring_up_locked(self, lib, timeout) -> None:
+        tag = self._tag
         self._comm = lib.b200_symm_comm_create(tag, self.rank, self.size, self.device.index, int(timeout * 1000))
         if not self._comm:
             raise RuntimeError("symmetric-memory bring-up failed: " + _native.cuda().b200_last_error().decode())
+        lib.b200_ar_set_timeout_ms.argtypes = [ctypes.c_longlong]
+        _native.check(lib.b200_ar_set_timeout_ms(max(1, int(timeout * 1000))), "set collective timeout")
         fb = int(lib.b200_ar_flag_bytes())
         self._flags = SymmBuffer(self, 2 * fb, multicast=False)
         self._flag_arr = [self._flags.ptr_array(0), self._flags.ptr_array(fb)]
@@ -151,11 +201,25 @@ class SymmBackend:
     def alloc_symmetric(self, numel: int, dtype: torch.dtype = torch.float32, multicast: bool = True) -> torch.Tensor:
         """COLLECTIVE.  A zero-initialised tensor in symmetric (peer-mapped, multicast-bound) memory."""
         es = torch.empty((), dtype=dtype).element_size()
+        self._ensure()
         if self.size == 1:
             return torch.zeros(numel, dtype=dtype, device=self.device)
-        buf = SymmBuffer(self, max(numel * es, 16), multicast=multicast)
+        with torch.cuda.device(self.device):
+            buf = SymmBuffer(self, max(numel * es, 16), multicast=multicast)
         self._buffers.append(buf)
         return buf.tensor(numel, dtype)
+
+    def free_symmetric(self, t: torch.Tensor) -> bool:
+        """COLLECTIVE.  Release the symmetric buffer `t` was allocated from (peer mappings, multicast binding and the
+        physical memory); every rank must call it for the same buffer.  The tensor must not be used afterwards."""
+        hit = self.lookup(t) if (self.size > 1 and t.is_cuda) else None
+        if hit is None or hit[0] in (getattr(self, "_flags", None), getattr(self, "_staging", None)):
+            return False
+        torch.cuda.synchronize(self.device)
+        self.barrier()                       # no peer kernel may still be reading the buffer
+        self._buffers.remove(hit[0])
+        hit[0].free()
+        return True
 
     def lookup(self, t: torch.Tensor) -> Optional[Tuple[SymmBuffer, int]]:
         p = t.data_ptr()
@@ -168,6 +232,7 @@ class SymmBackend:
         return max(1, min(64, (nbytes + (1 << 16) - 1) >> 16))
 
     # --------------------------------------------------------- collectives --
+    @_on_device
     def all_reduce(self, t: torch.Tensor, op, channel: int = 0, sgd: Optional[Tuple[torch.Tensor, float]] = None,
                    scale: Optional[float] = None, algo: Optional[str] = None, blocks: Optional[int] = None):
         """In-place all-reduce.  ``sgd=(weights, lr)`` fuses ``weights -= lr * result`` into the
@@ -181,6 +246,7 @@ class SymmBackend:
             raise RuntimeError(f"all_reduce: dtype {t.dtype} not supported by the native backend")
         if not t.is_cuda:
             raise RuntimeError("all_reduce on the native backend needs a CUDA tensor (use backend='gloo' for CPU)")
+        self._ensure(t)
         if scale is None:
             scale = 1.0 / self.size if op == 1 else 1.0
         if op == 1:
@@ -237,6 +303,7 @@ class SymmBackend:
         ev.record()
         return Work(ev)
 
+    @_on_device
     def all_reduce_small_symmetric(self, t: torch.Tensor, scale: float, out: Optional[torch.Tensor] = None,
                                    sgd: Optional[Tuple[torch.Tensor, float]] = None, channel: int = 0):
         """One-shot fp32 all-reduce reading a SYMMETRIC tensor on every rank directly (no staging copy):
@@ -248,6 +315,7 @@ class SymmBackend:
             if sgd is not None:
                 sgd[0].view(-1)[:n].add_(t.view(-1), alpha=-float(sgd[1]) * scale)
             return
+        self._ensure(t)
         sym = self.lookup(t)
         assert sym is not None and sym[1] % 16 == 0 and n % 4 == 0 and t.dtype == torch.float32
         buf, off = sym
@@ -258,6 +326,7 @@ class SymmBackend:
                                           max(1, min(32, (n // 4 + 511) // 512)), self._next_epoch(channel), self._stream())
         _native.check(rc, "all_reduce(one-shot f32x4)")
 
+    @_on_device
     def broadcast_symmetric_inplace(self, t: torch.Tensor, src: int, channel: int = 0):
         """Every rank overwrites its copy of the symmetric tensor ``t`` with rank ``src``'s (one tiny kernel)."""
         if self.size == 1:
@@ -280,9 +349,13 @@ class SymmBackend:
         pad[:flat.numel()].copy_(flat)
         return pad, True
 
+    @_on_device
     def broadcast(self, t: torch.Tensor, src: int, channel: int = 0):
         if self.size == 1:
             return None
+        if not t.is_cuda:
+            raise RuntimeError("broadcast on the native backend needs a CUDA tensor (use backend='gloo' for CPU)")
+        self._ensure(t)
         io, copy_back = self._padded_io(t)
         lib, st = _lib(), self._staging
         for s in range(0, io.numel(), STAGING_BYTES):
@@ -297,10 +370,14 @@ class SymmBackend:
             t.copy_(io[:t.numel() * t.element_size()].view(t.dtype).view(t.shape))
         return None
 
+    @_on_device
     def all_gather(self, out: torch.Tensor, t: torch.Tensor, channel: int = 0):
         if self.size == 1:
             out.view(-1).copy_(t.view(-1))
             return None
+        if not t.is_cuda:
+            raise RuntimeError("all_gather on the native backend needs CUDA tensors (use backend='gloo' for CPU)")
+        self._ensure(t)
         nb = t.numel() * t.element_size()
         if nb > STAGING_BYTES:
             raise RuntimeError("all_gather: per-rank tensor exceeds the 32 MiB staging buffer")
@@ -316,13 +393,15 @@ class SymmBackend:
         return None
 
     def barrier(self, channel: int = 0):
+        self._ensure()
         if self.size == 1:
             torch.cuda.synchronize(self.device)
             return
-        rc = _lib().b200_ar_barrier(self._flag_arr[channel], self.rank, self.size, self._next_epoch(channel),
-                                    self._stream())
-        _native.check(rc, "barrier")
-        torch.cuda.current_stream().synchronize()
+        with torch.cuda.device(self.device):
+            rc = _lib().b200_ar_barrier(self._flag_arr[channel], self.rank, self.size, self._next_epoch(channel),
+                                        self._stream())
+            _native.check(rc, "barrier")
+            torch.cuda.current_stream().synchronize()
 
     def close(self):
         if self._comm:
