@@ -62,17 +62,39 @@ def _collectives(rank, world, port):
     m = 6_000_000
     sym = be.alloc_symmetric(m, torch.float32)
     basem = (torch.arange(m, device=dev, dtype=torch.float32) % 509) * 0.5
-    for algo in (["nvls"] if be.multicast else []) + ["p2p"]:
-        for it in range(6):
+    import random
+    rng = random.Random(1000 + rank)                     # per-rank skew pattern
+    for algo in (["nvls", "nvls_excl"] if be.multicast else []) + ["p2p"]:
+        for it in range(40):
             if it % world == rank:
                 torch.cuda._sleep(20_000_000)            # one late rank per iteration
+            elif rng.random() < 0.3:
+                torch.cuda._sleep(rng.randrange(1, 4_000_000))
             sym.copy_(basem * (rank + 1 + it))
             be.all_reduce(sym, dist.ReduceOp.SUM, scale=1.0 / world, algo=algo)
             want = basem * ((tri + it * world) / world)
             assert torch.allclose(sym, want, rtol=1e-6, atol=1e-6), (algo, it, float((sym - want).abs().max()))
+    # 1000 back-to-back small collectives with randomised per-rank delays before each: the epoch flags are
+    # monotonic and never reset, so a stale or skipped epoch shows up as a wrong sum or a hang (bounded: 120 s)
+    small = be.alloc_symmetric(1024, torch.float32, multicast=False)
+    outv = torch.zeros(1024, device=dev)
+    for it in range(1000):
+        if rng.random() < 0.25:
+            torch.cuda._sleep(rng.randrange(1, 400_000))
+        if it % 3 == 0:
+            t = torch.tensor(rank + 1 + it, dtype=torch.int32, device=dev)
+            dist.all_reduce(t)
+            assert int(t) == tri + it * world, (it, int(t))
+        elif it % 3 == 1:
+            small.fill_(float(rank + it))
+            be.all_reduce_small_symmetric(small, 1.0, out=outv)
+            if it % 50 == 1:
+                assert float(outv[17]) == float(sum(r + it for r in range(world))), it
+        else:
+            dist.barrier()
     # fused SGD epilogue: W -= lr * mean(g)
     w = be.alloc_symmetric(m, torch.float32)
-    for algo in (["nvls"] if be.multicast else []) + ["p2p"]:
+    for algo in (["nvls", "nvls_excl"] if be.multicast else []) + ["p2p"]:
         w.fill_(1.0)
         sym.copy_(basem * (rank + 1))
         torch.cuda.synchronize()
@@ -160,3 +182,40 @@ def test_ddp_engine_matches_manual_gradient_averaging(tmp_path):
     out = str(tmp_path / "ok")
     b2.spawn(_ddp_engine, args=(world, b2.find_free_port(), out), nprocs=world)
     assert os.path.exists(out)
+
+
+def _missing_peer(rank, world, port, out_dir):
+    """Rank 1 never enters the collective: rank 0's kernel must give up after the group's timeout with a diagnostic
+    naming the missing rank (a trapped kernel, surfaced as a CUDA error), not spin for ever."""
+    import time
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", port
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank), timeout=3)
+    dev = torch.device("cuda", rank)
+    t = torch.ones(1 << 20, device=dev)
+    dist.all_reduce(t)                                   # both ranks: bring-up and one good collective
+    torch.cuda.synchronize()
+    if rank == 1:
+        time.sleep(12)                                   # "dead" peer: alive, but never calls the next collective
+        os._exit(0)
+    t0 = time.time()
+    try:
+        dist.all_reduce(t)
+        torch.cuda.synchronize()
+        outcome = "returned"
+    except Exception as e:                               # noqa: BLE001 - whatever CUDA reports for the trap
+        outcome = f"error after {time.time() - t0:.1f}s: {type(e).__name__}"
+    open(os.path.join(out_dir, "outcome"), "w").write(outcome)
+    os._exit(0)                                          # the context is gone after a trap: no orderly teardown
+
+
+@needs2
+def test_missing_peer_trips_the_bounded_wait(tmp_path, capfd):
+    b2.spawn(_missing_peer, args=(2, b2.find_free_port(), str(tmp_path)), nprocs=2)
+    outcome = open(tmp_path / "outcome").read()
+    print("[multi] missing peer:", outcome)
+    assert outcome.startswith("error after"), outcome
+    secs = float(outcome.split()[2].rstrip("s:"))
+    assert 2.0 <= secs <= 10.0, outcome                  # the 3 s group timeout reached the kernel
+    out = capfd.readouterr().out
+    assert "timed out after 3000 ms waiting for rank 1" in out, out[-500:]

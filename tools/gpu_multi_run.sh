@@ -1,21 +1,19 @@
 #!/bin/bash
-# Multi-GPU run (gpurun --gpus N): native collectives tests, bench at N (and N/2), reference arm.
+# Multi-GPU run (gpurun --gpus N): native collectives tests, bench at N (both arms).
 N=${1:-2}
 mkdir -p gpurun_out
 L=gpurun_out/multi_run_${N}.log
 : > $L
 run() { echo "=== $*" >> $L; timeout ${TMO:-300} "$@" >> $L 2>&1; echo "=== rc=$?" >> $L; }
 TR="python -m torch.distributed.run --nnodes=1 --master-addr 127.0.0.1"
-run python -m pytest -q -s -p no:cacheprovider -m gpu tests/test_gpu_multi.py
-run $TR --nproc-per-node $N --master-port 29511 bench.py --gpus $N --steps 30 --warmup 5
-run env B200DP_RESERVED_SMS=8 $TR --nproc-per-node $N --master-port 29521 bench.py --gpus $N --steps 30 --warmup 5
-run env B200DP_RESERVED_SMS=12 $TR --nproc-per-node $N --master-port 29522 bench.py --gpus $N --steps 30 --warmup 5
-if [ $N -ge 4 ]; then
-  H=$((N/2))
-  run $TR --nproc-per-node $H --master-port 29514 bench.py --gpus $H --steps 30 --warmup 5
-fi
+[ -z "$SKIP_TESTS" ] && run python -m pytest -q -s -p no:cacheprovider -m gpu tests/test_gpu_multi.py
+run $TR --nproc-per-node $N --master-port 29511 bench.py --gpus $N --steps 20 --warmup 5 $BENCH_ARGS
+[ -n "$REF" ] && TMO=400 run $TR --nproc-per-node $N --master-port 29531 bench.py --impl reference --gpus $N --steps 20 --warmup 5
 grep -E "passed|failed|rc=|rror|\[multi\] DDP" $L | cut -c1-300 | tail -20
-grep -E "^\{\"metric" $L | python -c "
+grep -E "^\{" $L | python -c "
 import sys, json
 for l in sys.stdin:
-    d = json.loads(l); print('N=%d ms_per_step %.3f  img/s %.1f  e2e %.1f  %s' % (d['n_gpus'], d['ms_per_step'], d['value'], d['e2e']['value'], {k: d.get('allreduce',{}).get(k) for k in ('fc_bucket_algo','comm_blocks','sm_partition')}))"
+    d = json.loads(l)
+    if d.get('impl') == 'reference':
+        print('REF N=%d ms_per_step %.3f img/s %.2f e2e %.2f' % (d['n_gpus'], d['ms_per_step'], d['value'], d['e2e']['value'])); continue
+    print('N=%d ms_per_step %.3f  img/s %.1f  e2e %.1f  sustained %.1f  bf16 %.3f ms  %s  identical=%s' % (d['n_gpus'], d['ms_per_step'], d['value'], d['e2e']['value'], d.get('sustained',{}).get('value',0), d.get('bf16_mode',{}).get('ms_per_step',0), {k: d.get('allreduce',{}).get(k) for k in ('fc_bucket_algo','comm_blocks','sm_partition')}, d.get('replicas_bit_identical')))"
