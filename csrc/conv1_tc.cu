@@ -293,8 +293,23 @@ constexpr int kABytes = 4 * kAtom;                    // 32 KB
 constexpr int kEBytes = 3 * kAtom;                    // 24 KB
 constexpr int kStageBytes = kABytes + kEBytes;
 constexpr int kInW = kXW + 8;                         // staged fp32 input row: x0-2 .. x0+69
-constexpr int kSmemBytes = kStages * kStageBytes + kStages * kERows * kInW * 4 + 1024 + 1024;
+// 16 producer warps: one thread = one 2x2 window x 4 channels.  Its five 16-byte pieces (4 pixels of x1, 1 of dp1)
+// reach it through a private two-slot cp.async ring, refilled for item n+2 as soon as item n has been read into
+// registers, so two items of HBM latency are covered without holding a second item in registers.  (The first
+// version prefetched one item ahead into registers: ncu showed 28 % of the stall samples on the first use of
+// those registers - 148 SMs bursting 45 KB each at the same moment see ~2 us of latency, one item time.)
+constexpr int kProdWarps = 16;
+constexpr int kProd = 32 * kProdWarps;                // 512
+constexpr int kThreads = 32 + kProd;
+constexpr int kRawBytes = 5 * kProd * 16;             // one slot of the x1 / dp1 ring: 40 KB
+constexpr int kInRing = 4;                            // input-row ring (shared by all producers; see the kernel)
+constexpr int kInBytes = kERows * kInW * 4;           // 3456 B
+constexpr int kSmemBytes = kStages * kStageBytes + 2 * kRawBytes + kInRing * kInBytes + 1024 + 1024;
 }  // namespace tf
+
+__device__ __forceinline__ void cp_async4(void* smem_dst, const void* gsrc, uint32_t src_bytes) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(smem_u32(smem_dst)), "l"(gsrc), "r"(src_bytes) : "memory");
+}
 
 __device__ __forceinline__ void ldg32f(const float* p, float (&v)[8]) {
   uint32_t u[8];
@@ -304,15 +319,16 @@ __device__ __forceinline__ void ldg32f(const float* p, float (&v)[8]) {
   for (int i = 0; i < 8; ++i) v[i] = __uint_as_float(u[i]);
 }
 
-__global__ void __launch_bounds__(kWgThreads, 1)
+__global__ void __launch_bounds__(tf::kThreads, 1)
 conv1_wgrad_tf32_kernel(const float* __restrict__ in, const float* __restrict__ x1,
                         const float* __restrict__ dp1, const float* __restrict__ bn,
                         const float* __restrict__ red, float* __restrict__ partials, WgGeom g) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);    // swizzle atoms: 1 KB aligned
   uint8_t* s_stage = smem;                                                          // [kStages][A | E]
-  float* s_in = reinterpret_cast<float*>(smem + kStages * tf::kStageBytes);         // [kStages][12][72]
-  float4* s_const = reinterpret_cast<float4*>(s_in + kStages * kERows * tf::kInW);  // [16] (sc, sh, ca, cb)
+  uint8_t* s_rawx = smem + kStages * tf::kStageBytes;                               // [2][5 pieces][512 threads][16 B]
+  float* s_in = reinterpret_cast<float*>(s_rawx + 2 * tf::kRawBytes);               // [kInRing][12][72]
+  float4* s_const = reinterpret_cast<float4*>(s_in + tf::kInRing * kERows * tf::kInW);  // [16] (sc, sh, ca, cb)
   uint64_t* bars = reinterpret_cast<uint64_t*>(s_const + kC1);
   uint64_t* full = bars;
   uint64_t* empty = bars + kStages;
@@ -321,7 +337,7 @@ conv1_wgrad_tf32_kernel(const float* __restrict__ in, const float* __restrict__ 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
   if (threadIdx.x == 0) {
-    for (int i = 0; i < kStages; ++i) { mbar_init(&full[i], kProducerWarps); mbar_init(&empty[i], 1); }
+    for (int i = 0; i < kStages; ++i) { mbar_init(&full[i], tf::kProdWarps); mbar_init(&empty[i], 1); }
     mbar_init(done, 1);
     mbar_fence_init();
   }
@@ -356,101 +372,129 @@ conv1_wgrad_tf32_kernel(const float* __restrict__ in, const float* __restrict__ 
     if (elect_one()) umma_commit(done);
     __syncwarp();
   } else {
-    const int pt = threadIdx.x - 32;                 // 0..255
-    const int half = pt & 1, w = pt >> 1;            // 8 channels (half) of window w
+    const int pt = threadIdx.x - 32;                 // 0..511
+    const int q = pt & 3, w = pt >> 2;               // channels 4q..4q+3 of window w
     const int wr = w >> 5, wc = w & 31;              // window row 0..3, window col 0..31
-    for (int c = pt; c < kC1; c += kProducers) {
+    for (int c = pt; c < kC1; c += tf::kProd) {
       const float s_ = bn[c], mu = bn[2 * kC1 + c], rs = bn[3 * kC1 + c];
       const float mdy = red[c], mdyx = red[kC1 + c];
       s_const[c] = make_float4(s_, bn[kC1 + c], s_ * (rs * mdyx * mu - mdy), -s_ * rs * mdyx);
     }
-    named_bar_sync(1, kProducers);
     constexpr int kInTot = kERows * tf::kInW;                               // 864
-    constexpr int kInPer = (kInTot + kProducers - 1) / kProducers;          // 4 staged floats per thread
-
-    struct Regs { float xr[4][8], gr[8], pin[kInPer]; bool wvalid; };
-    Regs nx;
-    nx.wvalid = false;
-    auto issue_loads = [&](int item) {
-      const int strip = item % g.nstrips;
-      const int grp = (item / g.nstrips) % g.ngroups;
-      const int b = item / (g.nstrips * g.ngroups);
-      const int y0 = grp * kRows, x0 = strip * tf::kXW;
+    constexpr int kInPer = (kInTot + tf::kProd - 1) / tf::kProd;            // 2 staged floats per thread
+    const int stride = (int)gridDim.x;
+    // cp.async fetch of the n-th item of this CTA: own window pieces -> private slot n & 1, own share of the
+    // input rows -> ring slot n & 3.  Always commits a group (possibly empty) so that wait_group counts items.
+    // (strip, group, image) of the next item to fetch, advanced by `stride` items without divisions
+    int f_strip = (int)blockIdx.x % g.nstrips, f_grp = ((int)blockIdx.x / g.nstrips) % g.ngroups,
+        f_b = (int)blockIdx.x / (g.nstrips * g.ngroups);
+    const int d_strip = stride % g.nstrips, d_grp = (stride / g.nstrips) % g.ngroups,
+              d_b = stride / (g.nstrips * g.ngroups);
+    uint32_t vq = 0;                                 // bit j: this thread's window is inside the image for item n+j
+    auto fetch = [&](int item, uint32_t n, int ahead) {
+      if (item < g.nitems) {
+        const int strip = f_strip, grp = f_grp, b = f_b;
+        f_strip += d_strip; f_grp += d_grp; f_b += d_b;
+        if (f_strip >= g.nstrips) { f_strip -= g.nstrips; ++f_grp; }
+        if (f_grp >= g.ngroups) { f_grp -= g.ngroups; ++f_b; }
+        const int y0 = grp * kRows, x0 = strip * tf::kXW;
+        float* sI = s_in + (n & (tf::kInRing - 1)) * kInTot;
 #pragma unroll
-      for (int j = 0; j < kInPer; ++j) {
-        const int i = pt + j * kProducers;
-        const int rr = i / tf::kInW, cc = i - rr * tf::kInW;
-        const int gy = y0 - 2 + rr, gx = x0 - 2 + cc;
-        nx.pin[j] = (i < kInTot && gy >= 0 && gy < g.H && gx >= 0 && gx < g.W)
-                        ? __ldg(in + ((size_t)b * g.H + gy) * g.W + gx) : 0.f;
+        for (int j = 0; j < kInPer; ++j) {
+          const int i = pt + j * tf::kProd;
+          if (i < kInTot) {
+            const int rr = i / tf::kInW, cc = i - rr * tf::kInW;
+            const int gy = y0 - 2 + rr, gx = x0 - 2 + cc;
+            const bool ok = gy >= 0 && gy < g.H && gx >= 0 && gx < g.W;
+            cp_async4(sI + i, in + (ok ? ((size_t)b * g.H + gy) * g.W + gx : 0), ok ? 4u : 0u);
+          }
+        }
+        const int gy = y0 + 2 * wr, gx = x0 + 2 * wc;
+        const uint32_t nb = (gy < g.H && gx < g.W) ? 16u : 0u;
+        vq |= (nb ? 1u : 0u) << ahead;
+        const float* xb = x1 + (nb ? (((size_t)b * g.H + gy) * g.W + gx) * kC1 : 0) + q * 4;
+        uint8_t* slot = s_rawx + (n & 1) * tf::kRawBytes + pt * 16;
+        cp_async16(slot, xb, nb);
+        cp_async16(slot + tf::kProd * 16, xb + kC1, nb);
+        cp_async16(slot + 2 * tf::kProd * 16, xb + (size_t)g.W * kC1, nb);
+        cp_async16(slot + 3 * tf::kProd * 16, xb + (size_t)g.W * kC1 + kC1, nb);
+        cp_async16(slot + 4 * tf::kProd * 16,
+                   dp1 + (nb ? (((size_t)b * Ho + (gy >> 1)) * Wo + (gx >> 1)) * kC1 : 0) + q * 4, nb);
       }
-      const int gy = y0 + 2 * wr, gx = x0 + 2 * wc;
-      nx.wvalid = gy < g.H && gx < g.W;
-      if (nx.wvalid) {
-        const float* xb = x1 + (((size_t)b * g.H + gy) * g.W + gx) * kC1 + half * 8;
-        ldg32f(xb, nx.xr[0]);
-        ldg32f(xb + kC1, nx.xr[1]);
-        ldg32f(xb + (size_t)g.W * kC1, nx.xr[2]);
-        ldg32f(xb + (size_t)g.W * kC1 + kC1, nx.xr[3]);
-        ldg32f(dp1 + (((size_t)b * Ho + (gy >> 1)) * Wo + (gx >> 1)) * kC1 + half * 8, nx.gr);
-      }
+      cp_async_commit();
     };
-    if ((int)blockIdx.x < g.nitems) issue_loads(blockIdx.x);
+    fetch(blockIdx.x, 0, 0);
+    fetch(blockIdx.x + stride, 1, 1);
+    named_bar_sync(1, tf::kProd);                    // s_const visible
     uint32_t n = 0;
-    for (int item = blockIdx.x; item < g.nitems; item += gridDim.x, ++n) {
+    for (int item = blockIdx.x; item < g.nitems; item += stride, ++n) {
       const uint32_t s = n % kStages;
       uint8_t* sA = s_stage + s * tf::kStageBytes;
       uint8_t* sE = sA + tf::kABytes;
-      float* sI = s_in + s * kInTot;
-      const Regs cur = nx;
-      if (item + (int)gridDim.x < g.nitems) issue_loads(item + gridDim.x);
-      mbar_wait(&empty[s], ((n / kStages) & 1) ^ 1);
-#pragma unroll
-      for (int j = 0; j < kInPer; ++j) {
-        const int i = pt + j * kProducers;
-        if (i < kInTot) sI[i] = cur.pin[j];
-      }
+      const float* sI = s_in + (n & (tf::kInRing - 1)) * kInTot;
+      cp_async_wait<1>();                            // this thread's pieces of item n have landed
+      float4 xr[4], gr;
       {
-        float o[4][8];
+        const uint8_t* slot = s_rawx + (n & 1) * tf::kRawBytes + pt * 16;
 #pragma unroll
-        for (int cc = 0; cc < 8; ++cc) {
-          const float4 k = s_const[half * 8 + cc];                // (sc, sh, ca, cb)
-          float best = fmaf(cur.xr[0][cc], k.x, k.y);
+        for (int i = 0; i < 4; ++i) xr[i] = *reinterpret_cast<const float4*>(slot + i * tf::kProd * 16);
+        gr = *reinterpret_cast<const float4*>(slot + 4 * tf::kProd * 16);
+      }
+      // refill the slot just read with item n+2.  Its input rows go to ring slot (n+2) & 3, last read in the E build
+      // of item n-2: every thread is past that, because this thread has passed item n-1's barrier below.
+      fetch(item + 2 * stride, n + 2, 2);
+      const bool wvalid = vq & 1u;
+      vq >>= 1;
+      mbar_wait(&empty[s], ((n / kStages) & 1) ^ 1);
+      {
+        float o[4][4];
+#pragma unroll
+        for (int cc = 0; cc < 4; ++cc) {
+          const float4 k = s_const[q * 4 + cc];                   // (sc, sh, ca, cb)
+          const float xv[4] = {(&xr[0].x)[cc], (&xr[1].x)[cc], (&xr[2].x)[cc], (&xr[3].x)[cc]};
+          float best = fmaf(xv[0], k.x, k.y);
           int am = 0;
 #pragma unroll
           for (int i = 1; i < 4; ++i) {
-            const float y = fmaf(cur.xr[i][cc], k.x, k.y);
+            const float y = fmaf(xv[i], k.x, k.y);
             if (y > best) { best = y; am = i; }
           }
-          const float gq = best > 0.f ? cur.gr[cc] * k.x : 0.f;   // ReLU mask, dy * scale, routed to the arg-max
+          const float gq = best > 0.f ? (&gr.x)[cc] * k.x : 0.f;  // ReLU mask, dy * scale, routed to the arg-max
+          // stored as fp32; the tensor core reads the top 19 bits (cvt.rna.tf32 is a 5-instruction emulation here)
 #pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            const float v = fmaf(k.w, cur.xr[i][cc], k.z) + (am == i ? gq : 0.f);
-            o[i][cc] = cur.wvalid ? to_tf32_rna(v) : 0.f;
-          }
+          for (int i = 0; i < 4; ++i) o[i][cc] = fmaf(k.w, xv[i], k.z);
+#pragma unroll
+          for (int i = 0; i < 4; ++i)
+            if (am == i) o[i][cc] += gq;
+        }
+        if (!wvalid) {
+#pragma unroll
+          for (int i = 0; i < 4; ++i)
+#pragma unroll
+            for (int cc = 0; cc < 4; ++cc) o[i][cc] = 0.f;
         }
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
-          const int kx = 2 * wc + (i & 1);                       // image row r = 2*wr + (i >> 1): atom wr
-          uint8_t* dst = sA + wr * tf::kAtom + sw32_off(kx, 2 * (i >> 1) + half);
-          *reinterpret_cast<float4*>(dst) = make_float4(o[i][0], o[i][1], o[i][2], o[i][3]);
-          *reinterpret_cast<float4*>(dst + 16) = make_float4(o[i][4], o[i][5], o[i][6], o[i][7]);
+          const int kx = 2 * wc + (i & 1);                        // image row r = 2*wr + (i >> 1): atom wr
+          *reinterpret_cast<float4*>(sA + wr * tf::kAtom + sw32_off(kx, 2 * (i >> 1) + (q >> 1)) + 16 * (q & 1)) =
+              make_float4(o[i][0], o[i][1], o[i][2], o[i][3]);
         }
       }
-      named_bar_sync(1, kProducers);                 // staged input complete
-      // expanded input E[r'][k][dxs]: 12 rows x 64 pixels x 2 pieces of 16 B, 6 per thread
+      named_bar_sync(1, tf::kProd);                  // everyone's input-row pieces of item n have landed
+      // expanded input E[r'][k][dxs]: 12 rows x 64 pixels x 2 pieces of 16 B, 3 per thread
 #pragma unroll
-      for (int j = 0; j < (2 * kERows * tf::kXW) / kProducers; ++j) {
-        const int idx = pt + j * kProducers;
+      for (int j = 0; j < (2 * kERows * tf::kXW) / tf::kProd; ++j) {
+        const int idx = pt + j * tf::kProd;
         const int kx = idx & (tf::kXW - 1), c2 = idx >> 6, rr = c2 >> 1;
         const float* src = sI + rr * tf::kInW + kx + 4 * (c2 & 1);          // in[.., x0 + kx - 2 + dxs]
         *reinterpret_cast<float4*>(sE + (rr >> 2) * tf::kAtom + sw32_off(kx, rr & 3) + 16 * (c2 & 1)) =
-            make_float4(to_tf32_rna(src[0]), to_tf32_rna(src[1]), to_tf32_rna(src[2]), to_tf32_rna(src[3]));
+            make_float4(src[0], src[1], src[2], src[3]);
       }
       fence_proxy_async_smem();
       __syncwarp();
       if (lane == 0) mbar_arrive(&full[s]);
     }
+    cp_async_wait<0>();
   }
   // extraction: identical (m, n) meaning to the bf16 kernel
   float* s_T = reinterpret_cast<float*>(s_stage);
@@ -471,7 +515,7 @@ conv1_wgrad_tf32_kernel(const float* __restrict__ in, const float* __restrict__ 
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  for (int t = threadIdx.x; t < kC1 * 25; t += kWgThreads) {
+  for (int t = threadIdx.x; t < kC1 * 25; t += tf::kThreads) {
     const int c = t / 25, tap = t % 25, dy = tap / 5, dxs = tap % 5;
     float a = 0.f;
 #pragma unroll
@@ -517,7 +561,7 @@ B200_API int b200_conv1_wgrad_tc_f32(const void* in_f32, const void* x1, const v
   g.nitems = B * g.nstrips * g.ngroups;
   const int nsm = b200_compute_sms();
   const int grid = g.nitems < nsm ? g.nitems : nsm;
-  conv1_wgrad_tf32_kernel<<<grid, kWgThreads, tf::kSmemBytes, s>>>((const float*)in_f32, (const float*)x1,
+  conv1_wgrad_tf32_kernel<<<grid, tf::kThreads, tf::kSmemBytes, s>>>((const float*)in_f32, (const float*)x1,
                                                                    (const float*)dp1, (const float*)bn,
                                                                    (const float*)red, (float*)partials, g);
   B200_LAUNCH_CHECK();

@@ -1187,14 +1187,18 @@ conv5x5_wgrad_rep_kernel(const ET* __restrict__ act, const ET* __restrict__ dxo,
 // K row = pixel), 32-byte units XOR-swizzled by the row index (sw32_off, ptx.cuh).  That happens to be the
 // NHWC memory of a 32-channel fp32 tensor, so a dx2 row segment is copied pixel by pixel with only the unit
 // permutation applied, and five consecutive row slots are again one N = 160 operand (LBO = slot stride).
-// The act tensor has 16 channels (64 B per pixel): an A row pairs two neighbouring pixels, atom j holds
-// [p1[x+2j] | p1[x+2j+1]], three atoms cover dx = 0..5, M = 128 with m = 16*dx + ci (80 useful rows).
+// The act tensor has 16 channels (64 B per pixel): an A row pairs two neighbouring pixels, row k holds
+// [p1[x+k] | p1[x+k+1]].  MN atom j of the operand must hold [p1[x+k+2j] | p1[x+k+2j+1]] - which is the SAME tile
+// two rows further down: the descriptor's atom stride (LBO) is simply 256 bytes.  The swizzle is a function of
+// the shared-memory address bits, so a tile read from a shifted start sees each row with the phase it was
+// written with.  One copy of the row (each pixel stored twice) serves dx = 0..7: M = 128, m = 16*dx + ci.
 namespace wt {
 constexpr int kSP = 64;                         // strip width in pixels
 constexpr int kAtom = kSP * 128;                // 8 KB: one 32-element MN atom over the strip
-constexpr int kSlotA = 3 * kAtom;               // 24 KB (the 4th atom an M = 128 operand spans is the next slot: unused lanes)
+constexpr int kRowsA = kSP + 8;                 // rows k = 0..69 are read (4 atoms, 2 rows apart); padded to the swizzle period
+constexpr int kSlotA = kRowsA * 128;            // 9 KB
 constexpr int kSlotB = kAtom;                   //  8 KB
-constexpr int kSlotsA = 3;
+constexpr int kSlotsA = 8;
 constexpr int kSlotsB = 12, kPhysB = kSlotsB + 4;
 constexpr int kKSteps = kSP / 8;
 constexpr int kTmemCols = 256;
@@ -1269,14 +1273,13 @@ conv5x5_wgrad_tf32_kernel(const float* __restrict__ act, const float* __restrict
           const char* row = reinterpret_cast<const char*>(act) + ((int64_t)b * g.H + y) * g.W * 64;
           uint8_t* dst = s_a + slot * wt::kSlotA;
 #pragma unroll
-          for (int jh = 0; jh < 6; ++jh) {                                     // dx = jh: atom jh >> 1, half jh & 1
+          for (int h = 0; h < 2; ++h) {                                        // half h of row k = pixel x0-2+k+h
 #pragma unroll
-            for (int k8 = 0; k8 < wt::kSP / 8; ++k8) {
+            for (int k8 = 0; k8 < wt::kRowsA / 8; ++k8) {
               const int k = k8 * 8 + ap;
-              const int x = x0 - 2 + jh + k;
+              const int x = x0 - 2 + h + k;
               const uint32_t nbytes = (x >= 0 && x < g.W) ? 16u : 0u;
-              const uint32_t u = (uint32_t)((jh & 1) * 2 + (aq >> 1));
-              cp_async16(dst + (jh >> 1) * wt::kAtom + sw32_off(k, u) + (aq & 1) * 16,
+              cp_async16(dst + sw32_off(k, (uint32_t)(h * 2 + (aq >> 1))) + (aq & 1) * 16,
                          row + (int64_t)(nbytes ? x : 0) * 64 + aq * 16, nbytes);
             }
           }
@@ -1288,7 +1291,7 @@ conv5x5_wgrad_tf32_kernel(const float* __restrict__ act, const float* __restrict
   } else if (warp == 1) {
     constexpr uint32_t idesc = umma_idesc(2, 128, 160, 1, 1);
     // MN-major SW128_32B: LBO = distance between 32-element MN atoms, SBO = distance between 4-row K groups
-    const uint64_t a_tmpl = smem_desc(0, wt::kAtom, 512, 1), b_tmpl = smem_desc(0, wt::kSlotB, 512, 1);
+    const uint64_t a_tmpl = smem_desc(0, 256, 512, 1), b_tmpl = smem_desc(0, wt::kSlotB, 512, 1);   // A: atom = +2 rows
     const uint32_t a_hi = (uint32_t)(a_tmpl >> 32), b_hi = (uint32_t)(b_tmpl >> 32);
     const uint32_t a_base = (uint32_t)a_tmpl + (smem_u32(s_a) >> 4), b_base = (uint32_t)b_tmpl + (smem_u32(s_b) >> 4);
     uint32_t ga = 0, gbase = 0;
