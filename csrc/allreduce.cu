@@ -296,6 +296,106 @@ allreduce_nvls_f32_excl_kernel(Peers P, Peers Wp, size_t n4, float scale, float 
   sys_barrier(P, epoch + 1);
 }
 
+
+// ------------------------------------------------ tile-driven fused bucket ---
+// K10 -> K16 pipeline: the fc backward kernel produces dW[10][F] slab by slab along F (all ten
+// rows of a column range at a time) and bumps a per-slab counter in symmetric memory when a block has written its
+// part (fc_bwd_kernel, `ready`).  This kernel is launched TOGETHER with the fc backward, on the side stream, and
+// consumes slabs as they become ready ON EVERY RANK: for slab t, rank r owns the r-th 1/world of its columns,
+// reduces them across ranks (NVLS: multimem.ld_reduce; P2P: one 16-byte load per peer, all in flight), applies
+// the 1/world scale and the SGD update to its fp32 master weights and writes the new WEIGHTS to every rank
+// (multimem.st / peer stores) - one pass, no reduce-scatter / all-gather split, no optimizer pass.
+// A slab's weights are only overwritten after every rank's fc backward has finished reading them (the counter is
+// bumped after the block's loads of that slab), and the trailing barrier orders the remote stores before the
+// next forward.  Every wait is bounded by g_wait_timeout_ns.
+struct TileGeom {
+  size_t F4;           // float4 per row (F / 4)
+  size_t slab4;        // float4 columns per slab
+  int nslabs, rows;    // rows <= kTileRows
+  uint32_t target;     // counter value that means "slab complete on that rank" (monotonic across steps)
+};
+constexpr int kTileRows = 10;      // rows of the fc.weight bucket (classes)
+
+template <bool NVLS>
+__global__ void __launch_bounds__(1024, 1)
+allreduce_tile_f32_kernel(Peers P, Peers Wp, Peers Rdy, TileGeom tg, float scale, float lr, uint32_t epoch) {
+  const int r = P.rank, n = P.world;
+  const size_t tstride = (size_t)gridDim.x * blockDim.x;
+  const float a = -lr * scale;
+  for (int t = 0; t < tg.nslabs; ++t) {
+    // ---- wait until slab t is complete on every rank
+    if (threadIdx.x < n) {
+      const uint32_t* cnt = reinterpret_cast<const uint32_t*>(Rdy.ptr[threadIdx.x]) + t;
+      const uint64_t t0 = b2::globaltimer_ns();
+      const uint64_t limit = g_wait_timeout_ns;
+      uint32_t spins = 0;
+      while ((int32_t)(ld_acquire_sys(cnt) - tg.target) < 0) {
+        if ((++spins & 0xFF) == 0) {
+          if (b2::globaltimer_ns() - t0 > limit) {
+            printf("b200dp: rank %d timed out after %llu ms waiting for gradient slab %d of rank %d\n", r,
+                   (unsigned long long)(limit / 1000000ull), t, (int)threadIdx.x);
+            __trap();
+          }
+          __nanosleep(200);
+        }
+      }
+    }
+    __syncthreads();
+    const size_t c0 = (size_t)t * tg.slab4;
+    const size_t c1 = min(tg.F4, c0 + tg.slab4);
+    const size_t per = (c1 - c0 + n - 1) / n;
+    const size_t lo = min(c1, c0 + per * r), hi = min(c1, lo + per);
+    // one column (16 bytes) of five rows per step: rows are F apart, so each row's accesses stay coalesced across
+    // the threads while a thread keeps five independent switch round trips in flight (64 registers at 1024 threads)
+    for (size_t i = lo + (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += tstride) {
+#pragma unroll 1
+      for (int k0 = 0; k0 < tg.rows; k0 += 5) {
+        if (NVLS) {
+          const float4* src = reinterpret_cast<const float4*>(P.mc) + i;
+          float4* dst = reinterpret_cast<float4*>(Wp.mc) + i;
+          const float4* wl = reinterpret_cast<const float4*>(Wp.ptr[r]) + i;
+          float4 v[5];
+#pragma unroll
+          for (int k = 0; k < 5; ++k)
+            if (k0 + k < tg.rows) v[k] = mc_ld_reduce_f32(src + (size_t)(k0 + k) * tg.F4);
+#pragma unroll
+          for (int k = 0; k < 5; ++k)
+            if (k0 + k < tg.rows) {
+              const float4 w = wl[(size_t)(k0 + k) * tg.F4];   // local HBM: short next to the switch round trip
+              mc_st_f32(dst + (size_t)(k0 + k) * tg.F4, make_float4(fmaf(a, v[k].x, w.x), fmaf(a, v[k].y, w.y),
+                                                                    fmaf(a, v[k].z, w.z), fmaf(a, v[k].w, w.w)));
+            }
+        } else {
+          float4 acc[5];
+#pragma unroll
+          for (int k = 0; k < 5; ++k) {
+            acc[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (k0 + k < tg.rows) {
+              const size_t e = (size_t)(k0 + k) * tg.F4 + i;
+#pragma unroll 8
+              for (int p = 0; p < n; ++p) {        // fixed rank order: every owner would compute identical bits
+                const float4 v = ld_peer16(reinterpret_cast<const float4*>(P.ptr[p]) + e);
+                acc[k].x += v.x; acc[k].y += v.y; acc[k].z += v.z; acc[k].w += v.w;
+              }
+            }
+          }
+#pragma unroll
+          for (int k = 0; k < 5; ++k)
+            if (k0 + k < tg.rows) {
+              const size_t e = (size_t)(k0 + k) * tg.F4 + i;
+              const float4 w = reinterpret_cast<const float4*>(Wp.ptr[r])[e];
+              const float4 o = make_float4(fmaf(a, acc[k].x, w.x), fmaf(a, acc[k].y, w.y),
+                                           fmaf(a, acc[k].z, w.z), fmaf(a, acc[k].w, w.w));
+              for (int p = 0; p < n; ++p)          // push the new weights to every replica (own copy included)
+                reinterpret_cast<float4*>(Wp.ptr[(r + p) % n])[e] = o;
+            }
+        }
+      }
+    }
+  }
+  sys_barrier(P, epoch);             // all weight stores have landed on every rank
+}
+
 // bf16 buffer (8 elements per 16 B), fp32 accumulation in the switch; scale applied here.
 __global__ void __launch_bounds__(512)
 allreduce_nvls_bf16_kernel(Peers P, size_t n16, float scale, uint32_t epoch) {
@@ -426,6 +526,37 @@ B200_API int b200_ar_large_f32(void* const* ptrs, void* mc, void* const* flags, 
     allreduce_nvls_f32_kernel<4><<<blocks, 512, 0, s>>>(P, Wp, n / 4, scale, lr, epoch);
   } else {
     allreduce_twoshot_f32_kernel<<<blocks, 512, 0, s>>>(P, Wp, n / 4, scale, lr, epoch);
+  }
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+// Tile-driven fused bucket all-reduce + SGD for the fc.weight gradient (see allreduce_tile_f32_kernel).
+//   ptrs / mc    gradient bucket [rows][F] on every rank / its multicast address (mc null -> P2P loads)
+//   wptrs / wmc  fp32 master weights, same layout, symmetric (required: the update is fused)
+//   rdy          per-rank pointers to the slab counters the fc backward bumps (b200_fc_bwd_tiles)
+//   target       value every counter of a complete slab has reached (blocks-per-slab x steps so far)
+B200_API int b200_ar_tile_f32(void* const* ptrs, void* mc, void* const* flags, void* const* wptrs, void* wmc,
+                              void* const* rdy, int rank, int world, int rows, size_t F, size_t slab_floats,
+                              uint32_t target, float scale, float lr, int blocks, uint32_t epoch, void* stream) {
+  B200_CHECK(world <= kMaxRanks && blocks >= 1 && blocks <= kMaxBlocks, "allreduce(tile): bad world/blocks");
+  B200_CHECK(F % 4 == 0 && slab_floats % 4 == 0 && slab_floats > 0, "allreduce(tile): F and slab must be multiples of 4");
+  B200_CHECK(wptrs != nullptr && rdy != nullptr, "allreduce(tile): weights and slab counters are required");
+  B200_CHECK(rows >= 1 && rows <= kTileRows, "allreduce(tile): at most %d rows", kTileRows);
+  Peers P = make_peers(ptrs, flags, mc, rank, world);
+  Peers Wp = make_peers(wptrs, nullptr, wmc, rank, world);
+  Peers Rdy = make_peers(rdy, nullptr, nullptr, rank, world);
+  TileGeom tg;
+  tg.F4 = F / 4; tg.slab4 = slab_floats / 4;
+  tg.nslabs = (int)((tg.F4 + tg.slab4 - 1) / tg.slab4);
+  tg.rows = rows; tg.target = target;
+  cudaStream_t s = (cudaStream_t)stream;
+  if (mc != nullptr && wmc != nullptr) {
+    B200_CUDA(set_max_smem(allreduce_tile_f32_kernel<true>, kExclusiveSmem));
+    allreduce_tile_f32_kernel<true><<<blocks, 1024, kExclusiveSmem, s>>>(P, Wp, Rdy, tg, scale, lr, epoch);
+  } else {
+    B200_CUDA(set_max_smem(allreduce_tile_f32_kernel<false>, kExclusiveSmem));
+    allreduce_tile_f32_kernel<false><<<blocks, 1024, kExclusiveSmem, s>>>(P, Wp, Rdy, tg, scale, lr, epoch);
   }
   B200_LAUNCH_CHECK();
   return 0;

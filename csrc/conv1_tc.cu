@@ -426,6 +426,9 @@ conv1_wgrad_tf32_kernel(const float* __restrict__ in, const float* __restrict__ 
     fetch(blockIdx.x, 0, 0);
     fetch(blockIdx.x + stride, 1, 1);
     named_bar_sync(1, tf::kProd);                    // s_const visible
+    float4 kc[4];                                    // this thread's channel constants stay in registers
+#pragma unroll
+    for (int cc = 0; cc < 4; ++cc) kc[cc] = s_const[q * 4 + cc];
     uint32_t n = 0;
     for (int item = blockIdx.x; item < g.nitems; item += stride, ++n) {
       const uint32_t s = n % kStages;
@@ -450,7 +453,7 @@ conv1_wgrad_tf32_kernel(const float* __restrict__ in, const float* __restrict__ 
         float o[4][4];
 #pragma unroll
         for (int cc = 0; cc < 4; ++cc) {
-          const float4 k = s_const[q * 4 + cc];                   // (sc, sh, ca, cb)
+          const float4 k = kc[cc];                                // (sc, sh, ca, cb)
           const float xv[4] = {(&xr[0].x)[cc], (&xr[1].x)[cc], (&xr[2].x)[cc], (&xr[3].x)[cc]};
           float best = fmaf(xv[0], k.x, k.y);
           int am = 0;

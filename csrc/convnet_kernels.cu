@@ -691,7 +691,8 @@ template <int BT, typename T>
 __global__ void __launch_bounds__(256)
 fc_bwd_kernel(const float* __restrict__ dl, const T* __restrict__ p2, float* W,
               float* dW, T* __restrict__ dp2, size_t F, float lr, int accumulate, float gscale,
-              const float* __restrict__ bn2, float* __restrict__ bwd_partials) {
+              const float* __restrict__ bn2, float* __restrict__ bwd_partials,
+              unsigned int* ready, int sweeps_per_slab) {
   __shared__ float s_dl[BT * kNC];
   __shared__ float s_bp[8][64];
   if (threadIdx.x < BT * kNC) s_dl[threadIdx.x] = dl[threadIdx.x];
@@ -714,7 +715,15 @@ fc_bwd_kernel(const float* __restrict__ dl, const T* __restrict__ p2, float* W,
 #pragma unroll
     for (int k = 0; k < kNC; ++k) d[b][k] = s_dl[b * kNC + k];
   const size_t n4 = F / 4;
-  for (size_t j = (size_t)blockIdx.x * 256 + threadIdx.x; j < n4; j += (size_t)gridDim.x * 256) {
+  // `ready` (data-parallel runs): a "slab" is `sweeps_per_slab` consecutive grid sweeps = a contiguous column range
+  // of all ten rows of dW.  When this block has written its share of slab t it bumps ready[t] (release, system
+  // scope); the tile-driven all-reduce kernel (allreduce.cu) running beside this one - here and on every peer -
+  // starts on a slab as soon as all blocks of all ranks have reported it.  Uniform trip count for the barrier.
+  const size_t sweep = (size_t)gridDim.x * 256;
+  int slab = 0, in_slab = 0;
+  for (size_t jb = 0; jb < n4; jb += sweep) {
+    const size_t j = jb + (size_t)blockIdx.x * 256 + threadIdx.x;
+    if (j < n4) {
     float4 w[kNC];
 #pragma unroll
     for (int k = 0; k < kNC; ++k) w[k] = *reinterpret_cast<const float4*>(W + (size_t)k * F + 4 * j);
@@ -762,6 +771,15 @@ fc_bwd_kernel(const float* __restrict__ dl, const T* __restrict__ p2, float* W,
                                fmaf(-lr, g.z, w[k].z), fmaf(-lr, g.w, w[k].w));
         *reinterpret_cast<float4*>(W + (size_t)k * F + 4 * j) = o;
       }
+    }
+    }   // j < n4
+    if (ready != nullptr && (++in_slab == sweeps_per_slab || jb + sweep >= n4)) {
+      __threadfence_system();
+      __syncthreads();
+      if (threadIdx.x == 0)
+        asm volatile("red.release.sys.global.add.u32 [%0], 1;" ::"l"(ready + slab) : "memory");
+      ++slab;
+      in_slab = 0;
     }
   }
   if (bn2) {
@@ -1096,14 +1114,15 @@ B200_API int b200_cross_entropy(const void* logits, const void* labels_i64, int 
 // bn2 / bwd_partials (both nullable): fused BatchNorm-2 backward reductions, partials [b200_fc_grid()][64].
 template <typename T>
 static int fc_bwd_t(const void* dlogits, const void* p2, void* W, void* dW, void* dp2, int bt, size_t F,
-                    float lr, int accumulate, float gscale, const void* bn2, void* bwd_partials, void* stream) {
+                    float lr, int accumulate, float gscale, const void* bn2, void* bwd_partials, void* stream,
+                    void* ready = nullptr, int sweeps_per_slab = 0) {
   B200_CHECK(bt >= 1 && bt <= 8, "fc_bwd: batch chunk must be 1..8 (got %d)", bt);
   B200_CHECK(F % 4 == 0, "fc_bwd: F must be a multiple of 4");
   B200_CHECK(!bn2 || (F % 32 == 0 && bwd_partials), "fc_bwd: fused BN statistics need F %% 32 == 0 and a partials buffer");
   cudaStream_t s = (cudaStream_t)stream;
   const int grid = b200_fc_grid();
   switch (bt) {
-#define B200_FCB(N) case N: fc_bwd_kernel<N, T><<<grid, 256, 0, s>>>((const float*)dlogits, (const T*)p2, (float*)W, (float*)dW, (T*)dp2, F, lr, accumulate, gscale, (const float*)bn2, (float*)bwd_partials); break;
+#define B200_FCB(N) case N: fc_bwd_kernel<N, T><<<grid, 256, 0, s>>>((const float*)dlogits, (const T*)p2, (float*)W, (float*)dW, (T*)dp2, F, lr, accumulate, gscale, (const float*)bn2, (float*)bwd_partials, (unsigned int*)ready, sweeps_per_slab); break;
     B200_FCB(1) B200_FCB(2) B200_FCB(3) B200_FCB(4) B200_FCB(5) B200_FCB(6) B200_FCB(7) B200_FCB(8)
 #undef B200_FCB
   }
@@ -1145,4 +1164,22 @@ B200_API int b200_nchw_f32_to_nhwc_bf16(const void* src, void* dst, int B, int C
   nchw_f32_to_nhwc_bf16_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((const float*)src, (__nv_bfloat16*)dst, B, C, H, W);
   B200_LAUNCH_CHECK();
   return 0;
+}
+
+// fc backward that reports its progress slab by slab for the tile-driven bucket all-reduce (b200_ar_tile_f32).
+//   ready            [ceil(F / b200_fc_bwd_tile_slab_floats(sweeps_per_slab))] uint32 counters in symmetric memory;
+//                    every block adds 1 to ready[t] once its part of slab t is written (monotonic: never reset)
+//   dtype            0 = bf16 activations, 1 = fp32
+// b200_fc_grid() blocks report per slab.
+B200_API size_t b200_fc_bwd_tile_slab_floats(int sweeps_per_slab) {
+  return (size_t)b200_fc_grid() * 256 * 4 * (size_t)sweeps_per_slab;
+}
+B200_API int b200_fc_bwd_tiles(const void* dlogits, const void* p2, void* W, void* dW, void* dp2, int bt, size_t F,
+                               float gscale, const void* bn2, void* bwd_partials, void* ready, int sweeps_per_slab,
+                               int dtype, void* stream) {
+  B200_CHECK(ready != nullptr && sweeps_per_slab >= 1 && dW != nullptr, "fc_bwd_tiles: needs counters, a slab size and dW");
+  if (dtype == 1)
+    return fc_bwd_t<float>(dlogits, p2, W, dW, dp2, bt, F, 0.f, 0, gscale, bn2, bwd_partials, stream, ready, sweeps_per_slab);
+  return fc_bwd_t<__nv_bfloat16>(dlogits, p2, W, dW, dp2, bt, F, 0.f, 0, gscale, bn2, bwd_partials, stream, ready,
+                                 sweeps_per_slab);
 }

@@ -123,7 +123,8 @@ def test_native_collectives():
     b2.spawn(_collectives, args=(world, b2.find_free_port()), nprocs=world)
 
 
-def _ddp_engine(rank, world, port, out_path):
+def _ddp_engine(rank, world, port, out_path, env=None):
+    os.environ.update(env or {})
     from torch_distributed_sandbox_b200.models.module import FusedModule
     from torch_distributed_sandbox_b200.models.engine import FusedConvNet
     from torch_distributed_sandbox_b200.parallel import DistributedDataParallel
@@ -177,10 +178,16 @@ def _ddp_engine(rank, world, port, out_path):
 
 
 @needs2
-def test_ddp_engine_matches_manual_gradient_averaging(tmp_path):
+@pytest.mark.parametrize("env", [
+    {"B200DP_AR_START": "tile"},                                  # fc_bwd -> all-reduce tile pipeline, NVLS when bound
+    {"B200DP_AR_START": "tile", "B200DP_AR_ALGO": "p2p"},         # same pipeline over plain peer loads / stores
+    {"B200DP_AR_START": "pool"},                                  # whole-bucket two-shot after the pool backward
+    {"B200DP_AR_START": "fc", "B200DP_AR_ALGO": "p2p"},
+], ids=["tiles-nvls", "tiles-p2p", "bucket-nvls", "bucket-p2p"])
+def test_ddp_engine_matches_manual_gradient_averaging(tmp_path, env):
     world = 2
     out = str(tmp_path / "ok")
-    b2.spawn(_ddp_engine, args=(world, b2.find_free_port(), out), nprocs=world)
+    b2.spawn(_ddp_engine, args=(world, b2.find_free_port(), out, env), nprocs=world)
     assert os.path.exists(out)
 
 

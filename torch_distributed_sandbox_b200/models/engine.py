@@ -351,17 +351,21 @@ class FusedConvNet:
         dp2 = p2
         dp2t = self.p2[:B]
         fuse_stats = self.fuse_bwd_stats and self.conv_backend == "tc"
-        for b0 in range(0, B, 8):
-            b1 = min(B, b0 + 8)
-            ops.fc_bwd(self.dlogits[b0:b1], p2[b0:b1], self.fcw, None if fused else self.fcw_grad, dp2[b0:b1],
-                       lr=self.lr if fused else 0.0, accumulate=b0 > 0, gscale=gs,
-                       bn2=self.bn2 if fuse_stats else None, bwd_partials=self.part_fcb if fuse_stats else None)
+        tiled = (self.comm is not None and hasattr(self.comm, "fc_bwd_tiles") and
+                 self.comm.fc_bwd_tiles(self, self.dlogits[:B], p2, dp2, self.bn2 if fuse_stats else None,
+                                        self.part_fcb if fuse_stats else None))
+        if not tiled:
+            for b0 in range(0, B, 8):
+                b1 = min(B, b0 + 8)
+                ops.fc_bwd(self.dlogits[b0:b1], p2[b0:b1], self.fcw, None if fused else self.fcw_grad, dp2[b0:b1],
+                           lr=self.lr if fused else 0.0, accumulate=b0 > 0, gscale=gs,
+                           bn2=self.bn2 if fuse_stats else None, bwd_partials=self.part_fcb if fuse_stats else None)
         self._fc_fused_done = fused
         # async all-reduce of the 720 MB bucket.  By default it starts after the next kernel instead of here:
         # pool_bn_bwd is HBM-bound and lost 0.16 ms to the all-reduce's 1.4 GB of HBM traffic, while the
         # conv kernels after it are bound by the shared-memory pipe / tensor pipe and have DRAM headroom.
-        defer_ar = self.comm is not None and getattr(self.comm, "start_after_pool", False)
-        if self.comm is not None and not defer_ar:
+        defer_ar = self.comm is not None and getattr(self.comm, "start_after_pool", False) and not tiled
+        if self.comm is not None and not defer_ar and not tiled:
             self.comm.fc_grad_ready(self)
         # ---- layer 2 (statistics pass fused into fc_bwd above unless disabled)
         H2, W2 = H // 2, W // 2

@@ -257,6 +257,27 @@ def fc_bwd(dlogits, p2_bf16, W, dW, dp2_bf16, lr=0.0, accumulate=False, gscale=1
     _count(1)
 
 
+def fc_bwd_tile_slab_floats(sweeps_per_slab: int) -> int:
+    lib = _lib()
+    lib.b200_fc_bwd_tile_slab_floats.restype = c_size_t
+    return int(lib.b200_fc_bwd_tile_slab_floats(int(sweeps_per_slab)))
+
+
+def fc_bwd_tiles(dlogits, p2, W, dW, dp2, ready_u32, sweeps_per_slab, gscale=1.0, bn2=None, bwd_partials=None):
+    """K10 for data-parallel runs: fc backward that bumps ``ready_u32[t]`` (symmetric memory) once per block when
+    its share of column slab t of dW is written, so the tile-driven bucket all-reduce (K16) running beside it can
+    start on a slab while the rest of dW is still being produced.  bt <= 8."""
+    lib = _lib()
+    lib.b200_fc_bwd_tiles.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_size_t, c_float,
+                                      c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p]
+    bt, F = p2.shape[0], p2[0].numel()
+    assert p2.dtype == dp2.dtype and ready_u32.dtype in (torch.int32, torch.uint32)
+    _native.check(lib.b200_fc_bwd_tiles(_p(dlogits), _p(p2), _p(W), _p(dW), _p(dp2), bt, F, gscale, _p(bn2),
+                                        _p(bwd_partials), _p(ready_u32), int(sweeps_per_slab),
+                                        1 if p2.dtype == torch.float32 else 0, _stream()), "fc_bwd_tiles")
+    _count(1)
+
+
 def conv2_dgrad_stats_tc(dx2_bf16, w2, pooled_p1, bn1, dp1_bf16, partials) -> int:
     """K12a + K13-stats: conv2 data gradient with the BatchNorm-1 backward reductions fused into its epilogue
     (``pooled_p1`` may alias ``dp1_bf16``).  Returns the number of partial rows ([rows][32])."""

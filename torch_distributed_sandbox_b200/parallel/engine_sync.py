@@ -39,8 +39,16 @@ class EngineGradSync:
         # SM partition (common.cu); 0 = share SMs.  Each rank reduces 1/world of the bucket, so the comm CTAs a
         # step needs shrink with the world size (measured best: 8 at N=2, 4 at N=8).
         self.reserved_sms = int(os.environ.get("B200DP_RESERVED_SMS", str({2: 8, 4: 6}.get(self.world, 4))))
-        # start the big-bucket all-reduce after the HBM-bound pool/BN backward kernel ("pool") or right after fc_bwd ("fc")
-        self.start_after_pool = os.environ.get("B200DP_AR_START", "pool") == "pool"
+        # When the fc.weight bucket all-reduce starts:
+        #   "tile"  with the fc backward itself: fc_bwd reports finished column slabs of dW through counters in symmetric
+        #           memory and the all-reduce kernel, launched beside it, consumes each slab as soon as every rank has
+        #           produced it (K10 -> K16 tile pipeline);
+        #   "fc"    when the fc backward kernel has finished;  "pool"  one kernel later (after the HBM-bound pool/BN backward).
+        self.ar_start = os.environ.get("B200DP_AR_START", "pool")
+        self.start_after_pool = self.ar_start == "pool"
+        self.tile_sweeps = int(os.environ.get("B200DP_TILE_SWEEPS", "2"))      # fc_bwd grid sweeps per slab (~48 MB of dW)
+        self.tile_ready = None
+        self._tile_steps = 0
         self._debug_skip_fc = os.environ.get("B200DP_DEBUG_SKIP_FC_ALLREDUCE", "0") == "1"   # timing experiments only
         be = self.backend
         if self.world > 1 and getattr(be, "name", "") != "native":
@@ -55,11 +63,32 @@ class EngineGradSync:
                 bn = be.alloc_symmetric(128, torch.float32, multicast=False)
                 sg = be.alloc_symmetric(engine.small_grad.numel(), torch.float32, multicast=False)
                 engine.rebind_storage(fcw=wsym, fcw_grad=grad, bn_flat=bn, small_grad=sg)
+                if self.ar_start == "tile" and self.fuse_sgd and engine.B <= 8:
+                    self.tile_ready = be.alloc_symmetric(256, torch.int32, multicast=False)     # slab counters
             self.comm_stream = be.comm_stream
             if self.reserved_sms > 0 and be.multicast and (self.algo in (None, "nvls", "nvls_excl")):
                 from .. import _native
                 _native.check(_native.cuda().b200_set_reserved_sms(self.reserved_sms), "set_reserved_sms")
                 self.algo, self.blocks = "nvls_excl", self.reserved_sms
+            elif self.reserved_sms > 0 and self.tile_ready is not None:
+                from .. import _native                     # the tile kernel's CTAs also own their SMs (P2P loads)
+                _native.check(_native.cuda().b200_set_reserved_sms(self.reserved_sms), "set_reserved_sms")
+        if self.tile_ready is not None:
+            from .. import ops
+            self.tile_slab_floats = ops.fc_bwd_tile_slab_floats(self.tile_sweeps)
+            self.tile_blocks = ops.fc_grid()
+            assert (engine.F + self.tile_slab_floats - 1) // self.tile_slab_floats <= self.tile_ready.numel()
+            # Load the producer kernel NOW.  CUDA loads a kernel lazily at its first launch, and that load can wait for
+            # running kernels to drain: a first launch of fc_bwd while the consumer is already spinning on its counters
+            # would deadlock (seen on the first step: the launch call itself blocked until the consumer timed out).
+            with torch.cuda.device(engine.device):
+                Bw = min(engine.B, 8)
+                dummy_p2 = torch.zeros(Bw, 32, device=engine.device, dtype=engine.act_dtype)
+                ops.fc_bwd_tiles(torch.zeros(Bw, 10, device=engine.device), dummy_p2,
+                                 torch.zeros(10, 32, device=engine.device), torch.zeros(10, 32, device=engine.device),
+                                 torch.empty_like(dummy_p2), torch.zeros(4, dtype=torch.int32, device=engine.device),
+                                 self.tile_sweeps)
+                torch.cuda.synchronize(engine.device)
         if init_sync:
             self._sync_params()
 
@@ -74,7 +103,10 @@ class EngineGradSync:
         d = dict(self.backend.describe()) if hasattr(self.backend, "describe") else {}
         mc = bool(d.get("nvls_multicast"))
         algo = self.algo or ("nvls" if mc else "p2p")
-        d.update({"fc_bucket_algo": f"two-shot-{algo}", "fused_sgd_in_allreduce": self.fuse_sgd,
+        if self.tile_ready is not None:
+            algo = ("nvls" if mc and self.algo != "p2p" else "p2p") + f"-tiles({self.tile_sweeps} sweeps/slab, starts with fc_bwd)"
+        d.update({"fc_bucket_algo": (f"one-pass-{algo}" if self.tile_ready is not None else f"two-shot-{algo}"),
+                  "fused_sgd_in_allreduce": self.fuse_sgd,
                   "sm_partition": self.reserved_sms if algo == "nvls_excl" else 0,
                   "small_bucket_algo": "one-shot", "comm_blocks": self.blocks, "nccl_calls_on_grad_path": 0})
         return d
@@ -104,6 +136,30 @@ class EngineGradSync:
                                     blocks=self.blocks)
             self._fc_event = torch.cuda.Event()
             self._fc_event.record(self.comm_stream)
+
+    def fc_bwd_tiles(self, engine, dlogits, p2, dp2, bn2, bwd_partials) -> bool:
+        """Tile pipeline: launch the producing fc backward on the main stream and the consuming all-reduce beside it
+        on the side stream.  Returns False when the pipeline is not in use (caller runs the plain fc backward)."""
+        if self.world == 1 or self.tile_ready is None or p2.shape[0] > 8 or self._debug_skip_fc:
+            return False
+        from .. import ops
+        main = torch.cuda.current_stream()
+        start = torch.cuda.Event()
+        start.record(main)                                   # BEFORE the fc backward: the two kernels run concurrently
+        self._tile_steps += 1
+        # producer first: once its launch call has returned it cannot be held up behind the spinning consumer
+        ops.fc_bwd_tiles(dlogits, p2, engine.fcw, engine.fcw_grad, dp2, self.tile_ready, self.tile_sweeps,
+                         gscale=engine.grad_scale, bn2=bn2, bwd_partials=bwd_partials)
+        with torch.cuda.stream(self.comm_stream), trace.nvtx_range("b200dp.allreduce.fc_bucket(tiles)"):
+            self.comm_stream.wait_event(start)
+            self.backend.all_reduce_tiles(engine.fcw_grad, engine.fcw, self.tile_ready, rows=10,
+                                          slab_floats=self.tile_slab_floats,
+                                          target=self._tile_steps * self.tile_blocks, scale=1.0 / self.world,
+                                          lr=engine.lr, channel=1, blocks=max(1, self.reserved_sms or 8),
+                                          use_nvls=None if self.algo in (None, "nvls", "nvls_excl") else False)
+            self._fc_event = torch.cuda.Event()
+            self._fc_event.record(self.comm_stream)
+        return True
 
     def small_grads_ready(self, engine) -> bool:
         """One-shot all-reduce of the 53 KB bucket with the SGD update fused in; True = parameters updated."""

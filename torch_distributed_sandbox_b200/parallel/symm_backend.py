@@ -304,6 +304,28 @@ class SymmBackend:
         return Work(ev)
 
     @_on_device
+    def all_reduce_tiles(self, grad: torch.Tensor, weights: torch.Tensor, ready: torch.Tensor, rows: int,
+                         slab_floats: int, target: int, scale: float, lr: float, channel: int = 1,
+                         blocks: int = 8, use_nvls: Optional[bool] = None):
+        """Tile-driven fused bucket all-reduce + SGD (csrc/allreduce.cu: allreduce_tile_f32_kernel).  ``grad`` [rows, F],
+        ``weights`` (same shape) and the slab counters ``ready`` are symmetric tensors; the kernel is meant to be
+        launched on a side stream WHILE the producer of ``grad`` (ops.fc_bwd_tiles) runs on the main stream."""
+        g, w, r = self.lookup(grad), self.lookup(weights), self.lookup(ready)
+        if g is None or w is None or r is None:
+            raise RuntimeError("all_reduce_tiles needs gradient, weights and counters in symmetric memory")
+        lib = _lib()
+        PP = ctypes.POINTER(c_void_p)
+        lib.b200_ar_tile_f32.argtypes = [PP, c_void_p, PP, PP, c_void_p, PP, c_int, c_int, c_int, c_size_t, c_size_t,
+                                         c_uint32, c_float, c_float, c_int, c_uint32, c_void_p]
+        nvls = bool(g[0].mc and w[0].mc) if use_nvls is None else (use_nvls and bool(g[0].mc and w[0].mc))
+        F = grad.numel() // rows
+        rc = lib.b200_ar_tile_f32(g[0].ptr_array(g[1]), (g[0].mc + g[1]) if nvls else 0, self._flag_arr[channel],
+                                  w[0].ptr_array(w[1]), (w[0].mc + w[1]) if nvls else 0, r[0].ptr_array(r[1]),
+                                  self.rank, self.size, rows, F, slab_floats, target & 0xFFFFFFFF, scale, lr, blocks,
+                                  self._next_epoch(channel), self._stream())
+        _native.check(rc, "all_reduce(tiles)")
+
+    @_on_device
     def all_reduce_small_symmetric(self, t: torch.Tensor, scale: float, out: Optional[torch.Tensor] = None,
                                    sgd: Optional[Tuple[torch.Tensor, float]] = None, channel: int = 0):
         """One-shot fp32 all-reduce reading a SYMMETRIC tensor on every rank directly (no staging copy):
