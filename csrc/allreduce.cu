@@ -345,27 +345,55 @@ allreduce_tile_f32_kernel(Peers P, Peers Wp, Peers Rdy, TileGeom tg, float scale
     const size_t c1 = min(tg.F4, c0 + tg.slab4);
     const size_t per = (c1 - c0 + n - 1) / n;
     const size_t lo = min(c1, c0 + per * r), hi = min(c1, lo + per);
-    // one column (16 bytes) of five rows per step: rows are F apart, so each row's accesses stay coalesced across
-    // the threads while a thread keeps five independent switch round trips in flight (64 registers at 1024 threads)
-    for (size_t i = lo + (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += tstride) {
+    if (NVLS) {
+      // Eight independent switch round trips per thread (the register budget of 1024 threads): the link is latency
+      // bound, ~128 KB in flight per SM is what the whole-bucket kernel above runs with.  Rows are F apart, so a
+      // row's accesses stay coalesced across the threads.  Rows 0..7 of one column, then the remaining rows eight
+      // columns at a time.
+      const float4* src = reinterpret_cast<const float4*>(P.mc);
+      float4* dst = reinterpret_cast<float4*>(Wp.mc);
+      const float4* wl = reinterpret_cast<const float4*>(Wp.ptr[r]);
+      const int full = tg.rows & ~7, rem = tg.rows & 7;
+      for (int k0 = 0; k0 < full; k0 += 8)
+        for (size_t i = lo + (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += tstride) {
+          float4 v[8];
+#pragma unroll
+          for (int k = 0; k < 8; ++k) v[k] = mc_ld_reduce_f32(src + (size_t)(k0 + k) * tg.F4 + i);
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            const size_t e = (size_t)(k0 + k) * tg.F4 + i;
+            const float4 w = wl[e];                    // local HBM: short next to the switch round trip above
+            mc_st_f32(dst + e, make_float4(fmaf(a, v[k].x, w.x), fmaf(a, v[k].y, w.y), fmaf(a, v[k].z, w.z),
+                                           fmaf(a, v[k].w, w.w)));
+          }
+        }
+      for (int k = full; k < full + rem; ++k) {        // left-over rows: eight columns of one row at a time
+        const float4* srow = src + (size_t)k * tg.F4;
+        float4* drow = dst + (size_t)k * tg.F4;
+        const float4* wrow = wl + (size_t)k * tg.F4;
+        size_t i = lo + (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+        for (; i + 7 * tstride < hi; i += 8 * tstride) {
+          float4 v[8];
+#pragma unroll
+          for (int u = 0; u < 8; ++u) v[u] = mc_ld_reduce_f32(srow + i + u * tstride);
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            const float4 w = wrow[i + u * tstride];
+            mc_st_f32(drow + i + u * tstride, make_float4(fmaf(a, v[u].x, w.x), fmaf(a, v[u].y, w.y),
+                                                          fmaf(a, v[u].z, w.z), fmaf(a, v[u].w, w.w)));
+          }
+        }
+        for (; i < hi; i += tstride) {
+          const float4 v = mc_ld_reduce_f32(srow + i);
+          const float4 w = wrow[i];
+          mc_st_f32(drow + i, make_float4(fmaf(a, v.x, w.x), fmaf(a, v.y, w.y), fmaf(a, v.z, w.z), fmaf(a, v.w, w.w)));
+        }
+      }
+    } else {
+      // P2P: five rows of one column per step; every peer's load is in flight before the first add
+      for (size_t i = lo + (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += tstride) {
 #pragma unroll 1
-      for (int k0 = 0; k0 < tg.rows; k0 += 5) {
-        if (NVLS) {
-          const float4* src = reinterpret_cast<const float4*>(P.mc) + i;
-          float4* dst = reinterpret_cast<float4*>(Wp.mc) + i;
-          const float4* wl = reinterpret_cast<const float4*>(Wp.ptr[r]) + i;
-          float4 v[5];
-#pragma unroll
-          for (int k = 0; k < 5; ++k)
-            if (k0 + k < tg.rows) v[k] = mc_ld_reduce_f32(src + (size_t)(k0 + k) * tg.F4);
-#pragma unroll
-          for (int k = 0; k < 5; ++k)
-            if (k0 + k < tg.rows) {
-              const float4 w = wl[(size_t)(k0 + k) * tg.F4];   // local HBM: short next to the switch round trip
-              mc_st_f32(dst + (size_t)(k0 + k) * tg.F4, make_float4(fmaf(a, v[k].x, w.x), fmaf(a, v[k].y, w.y),
-                                                                    fmaf(a, v[k].z, w.z), fmaf(a, v[k].w, w.w)));
-            }
-        } else {
+        for (int k0 = 0; k0 < tg.rows; k0 += 5) {
           float4 acc[5];
 #pragma unroll
           for (int k = 0; k < 5; ++k) {
