@@ -149,8 +149,13 @@ allreduce_oneshot_kernel<__nv_bfloat16, float>(Peers P, __nv_bfloat16* __restric
 template <int MAXW>
 __global__ void __launch_bounds__(512)
 allreduce_oneshot_f32x4_kernel(Peers P, float4* __restrict__ out, float4* __restrict__ param, size_t n4, float scale,
-                               float lr, uint32_t epoch) {
+                               float lr, uint32_t epoch, Peers Bc, int bc_n4, int bc_root) {
   sys_barrier(P, epoch);
+  // folded broadcast (DDP's per-forward buffer sync, C4): every rank takes the root's copy of a second, tiny
+  // symmetric tensor (the 512-byte BatchNorm blob) under the same pair of barriers
+  if (Bc.ptr[0] != nullptr && P.rank != bc_root && blockIdx.x == 0 && (int)threadIdx.x < bc_n4)
+    reinterpret_cast<float4*>(Bc.ptr[P.rank])[threadIdx.x] =
+        ld_peer16(reinterpret_cast<const float4*>(Bc.ptr[bc_root]) + threadIdx.x);
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
     float4 v[MAXW];
 #pragma unroll
@@ -169,6 +174,68 @@ allreduce_oneshot_f32x4_kernel(Peers P, float4* __restrict__ out, float4* __rest
     }
   }
   sys_barrier(P, epoch + 1);
+}
+
+
+// ------------------------------------------------------------- push one-shot ---
+// Latency path for small tensors that live ANYWHERE (no staging copy, no symmetric input): every rank writes its
+// data into slot [rank] of every peer's scratch ring (peer stores over NVLink), signals, waits for everybody's
+// signal, and reduces its own - now local - copies.  One kernel, one cross-GPU synchronisation.  The scratch has
+// two halves used alternately (`buf`): a rank can only be one call ahead of a peer (it needs the peer's signal of
+// the current call to finish it), so when it overwrites a half the peer has finished reading it two calls ago and
+// no trailing barrier is needed.  The same grid runs on every rank, so the per-CTA flag barrier covers exactly the
+// elements this CTA's peers pushed.
+template <typename T, typename Acc>
+__global__ void __launch_bounds__(512)
+allreduce_push_kernel(Peers P, const T* __restrict__ in, T* __restrict__ out, size_t n, size_t slot_bytes, int buf,
+                      float scale, int op, uint32_t epoch) {
+  const size_t half = (size_t)buf * kMaxRanks * slot_bytes;
+  const size_t g0 = (size_t)blockIdx.x * blockDim.x + threadIdx.x, gs = (size_t)gridDim.x * blockDim.x;
+  for (int k = 0; k < P.world; ++k) {
+    const int p = (P.rank + k) % P.world;
+    T* dst = reinterpret_cast<T*>(reinterpret_cast<char*>(P.ptr[p]) + half + (size_t)P.rank * slot_bytes);
+    for (size_t i = g0; i < n; i += gs) dst[i] = in[i];
+  }
+  sys_barrier(P, epoch);             // my stores are visible to the peers, theirs to me
+  const char* mine = reinterpret_cast<const char*>(P.ptr[P.rank]) + half;
+  for (size_t i = g0; i < n; i += gs) {
+    Acc acc = (Acc) reinterpret_cast<const volatile T*>(mine)[i];
+    for (int p = 1; p < P.world; ++p) {
+      const Acc v = (Acc) reinterpret_cast<const volatile T*>(mine + (size_t)p * slot_bytes)[i];
+      if (op == 0) acc += v;
+      else if (op == 2) acc = v > acc ? v : acc;
+      else if (op == 3) acc = v < acc ? v : acc;
+      else acc *= v;
+    }
+    out[i] = (T)(acc * (Acc)scale);
+  }
+}
+template <>
+__global__ void __launch_bounds__(512)
+allreduce_push_kernel<__nv_bfloat16, float>(Peers P, const __nv_bfloat16* __restrict__ in, __nv_bfloat16* __restrict__ out,
+                                            size_t n, size_t slot_bytes, int buf, float scale, int op, uint32_t epoch) {
+  const size_t half = (size_t)buf * kMaxRanks * slot_bytes;
+  const size_t g0 = (size_t)blockIdx.x * blockDim.x + threadIdx.x, gs = (size_t)gridDim.x * blockDim.x;
+  for (int k = 0; k < P.world; ++k) {
+    const int p = (P.rank + k) % P.world;
+    __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(reinterpret_cast<char*>(P.ptr[p]) + half + (size_t)P.rank * slot_bytes);
+    for (size_t i = g0; i < n; i += gs) dst[i] = in[i];
+  }
+  sys_barrier(P, epoch);
+  const char* mine = reinterpret_cast<const char*>(P.ptr[P.rank]) + half;
+  for (size_t i = g0; i < n; i += gs) {
+    float acc = 0.f;
+    for (int p = 0; p < P.world; ++p) {
+      const unsigned short raw = reinterpret_cast<const volatile unsigned short*>(mine + (size_t)p * slot_bytes)[i];
+      const float v = __uint_as_float((uint32_t)raw << 16);
+      if (p == 0) acc = v;
+      else if (op == 0) acc += v;
+      else if (op == 2) acc = fmaxf(acc, v);
+      else if (op == 3) acc = fminf(acc, v);
+      else acc *= v;
+    }
+    out[i] = __float2bfloat16_rn(acc * scale);
+  }
 }
 
 // -------------------------------------------------------------- two-shot P2P ---
@@ -518,19 +585,58 @@ B200_API int b200_ar_oneshot(void* const* ptrs, void* const* flags, int rank, in
   return 0;
 }
 
-// Small fp32 SUM straight from a symmetric input (no staging copy): out (local, may be null) = scale*sum,
-// and/or param -= lr * scale * sum.  n % 4 == 0.
-B200_API int b200_ar_oneshot_f32x4(void* const* ptrs, void* const* flags, int rank, int world, void* out, void* param,
-                                   size_t n, float scale, float lr, int blocks, uint32_t epoch, void* stream) {
-  B200_CHECK(world <= kMaxRanks && blocks >= 1 && blocks <= kMaxBlocks && n % 4 == 0, "oneshot_f32x4: bad arguments");
+// Small all-reduce of an ordinary (non-symmetric) tensor through the push ring.  ptrs = every rank's mapping of the
+// scratch ring ([2 halves][kMaxRanks slots][slot_bytes]); in/out are local (may alias); n * element size <= slot_bytes.
+// dtype: 0 f32, 1 f64, 2 i32, 3 i64, 5 bf16; op: 0 sum, 2 max, 3 min, 4 prod.
+B200_API int b200_ar_push(void* const* ptrs, void* const* flags, int rank, int world, const void* in, void* out,
+                          size_t n, int dtype, int op, float scale, size_t slot_bytes, int buf, int blocks,
+                          uint32_t epoch, void* stream) {
+  B200_CHECK(world <= kMaxRanks && blocks >= 1 && blocks <= kMaxBlocks && (buf == 0 || buf == 1), "ar_push: bad arguments");
   Peers P = make_peers(ptrs, flags, nullptr, rank, world);
   cudaStream_t s = (cudaStream_t)stream;
-  if (world <= 8)
-    allreduce_oneshot_f32x4_kernel<8><<<blocks, 512, 0, s>>>(P, (float4*)out, (float4*)param, n / 4, scale, lr, epoch);
-  else
-    allreduce_oneshot_f32x4_kernel<16><<<blocks, 512, 0, s>>>(P, (float4*)out, (float4*)param, n / 4, scale, lr, epoch);
+  const size_t es = dtype == 0 || dtype == 2 ? 4 : dtype == 5 ? 2 : 8;
+  B200_CHECK(n * es <= slot_bytes, "ar_push: %zu bytes do not fit a %zu-byte slot", n * es, slot_bytes);
+  switch (dtype) {
+    case 0: allreduce_push_kernel<float, float><<<blocks, 512, 0, s>>>(P, (const float*)in, (float*)out, n, slot_bytes, buf, scale, op, epoch); break;
+    case 1: allreduce_push_kernel<double, double><<<blocks, 512, 0, s>>>(P, (const double*)in, (double*)out, n, slot_bytes, buf, scale, op, epoch); break;
+    case 2: allreduce_push_kernel<int, int><<<blocks, 512, 0, s>>>(P, (const int*)in, (int*)out, n, slot_bytes, buf, scale, op, epoch); break;
+    case 3: allreduce_push_kernel<long long, long long><<<blocks, 512, 0, s>>>(P, (const long long*)in, (long long*)out, n, slot_bytes, buf, scale, op, epoch); break;
+    case 5: allreduce_push_kernel<__nv_bfloat16, float><<<blocks, 512, 0, s>>>(P, (const __nv_bfloat16*)in, (__nv_bfloat16*)out, n, slot_bytes, buf, scale, op, epoch); break;
+    default: return b200_fail(-2, "ar_push: unsupported dtype %d", dtype);
+  }
   B200_LAUNCH_CHECK();
   return 0;
+}
+
+// Small fp32 SUM straight from a symmetric input (no staging copy): out (local, may be null) = scale*sum,
+// and/or param -= lr * scale * sum.  n % 4 == 0.
+static int oneshot_f32x4(void* const* ptrs, void* const* flags, int rank, int world, void* out, void* param, size_t n,
+                         float scale, float lr, int blocks, uint32_t epoch, void* stream, void* const* bc_ptrs,
+                         size_t bc_floats, int bc_root) {
+  B200_CHECK(world <= kMaxRanks && blocks >= 1 && blocks <= kMaxBlocks && n % 4 == 0, "oneshot_f32x4: bad arguments");
+  B200_CHECK(bc_floats % 4 == 0 && bc_floats <= 2048 && bc_root >= 0 && bc_root < world, "oneshot_f32x4: bad broadcast");
+  Peers P = make_peers(ptrs, flags, nullptr, rank, world);
+  Peers Bc = make_peers(bc_ptrs, nullptr, nullptr, rank, world);
+  cudaStream_t s = (cudaStream_t)stream;
+  if (world <= 8)
+    allreduce_oneshot_f32x4_kernel<8><<<blocks, 512, 0, s>>>(P, (float4*)out, (float4*)param, n / 4, scale, lr, epoch, Bc,
+                                                             (int)(bc_floats / 4), bc_root);
+  else
+    allreduce_oneshot_f32x4_kernel<16><<<blocks, 512, 0, s>>>(P, (float4*)out, (float4*)param, n / 4, scale, lr, epoch, Bc,
+                                                              (int)(bc_floats / 4), bc_root);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+B200_API int b200_ar_oneshot_f32x4(void* const* ptrs, void* const* flags, int rank, int world, void* out, void* param,
+                                   size_t n, float scale, float lr, int blocks, uint32_t epoch, void* stream) {
+  return oneshot_f32x4(ptrs, flags, rank, world, out, param, n, scale, lr, blocks, epoch, stream, nullptr, 0, 0);
+}
+// Same, plus "every rank copies rank `bc_root`'s `bc_floats` floats of a second symmetric tensor" in the same kernel.
+B200_API int b200_ar_oneshot_f32x4_bcast(void* const* ptrs, void* const* flags, int rank, int world, void* out,
+                                         void* param, size_t n, float scale, float lr, int blocks, uint32_t epoch,
+                                         void* stream, void* const* bc_ptrs, size_t bc_floats, int bc_root) {
+  return oneshot_f32x4(ptrs, flags, rank, world, out, param, n, scale, lr, blocks, epoch, stream, bc_ptrs, bc_floats,
+                       bc_root);
 }
 
 // In-place fp32 SUM over the symmetric buffer (n floats, n % 4 == 0).  algo: 1 = two-shot P2P,

@@ -429,3 +429,79 @@ B200_API int b200_symm_topology(int device, int* p2p_out, int* native_atomics_ou
   }
   return n;
 }
+
+// ---------------------------------------------------------------------------------------------
+// NVLink / NVSwitch discovery through NVML (loaded with dlopen: no link-time dependency, and a box
+// without the library just reports "unknown").  The reference's bring-up (test_init.py:84-91) knows nothing
+// about the fabric; here the process group reports it once and uses it to choose collective algorithms:
+//   links_active       NVLink links of `device` in the active state (18 on a B200 HGX baseboard)
+//   links_to_switch    how many of them end in an NVSwitch (all of them on HGX; 0 on bridge-connected boards)
+//   peer_links[p]      active links whose remote end is GPU p directly (bridges); 0 behind a switch
+//   link_gbs           per-link, per-direction bandwidth NVML states for the link generation (GB/s), 0 if unknown
+//   multicast          CU_DEVICE_ATTRIBUTE_MULTICAST_SUPPORTED (NVLS)
+// Returns 0 on success, 1 when NVML is unavailable (the cudaDeviceCanAccessPeer view still applies).
+#include <dlfcn.h>
+namespace {
+struct NvmlPci { char busIdLegacy[16]; unsigned int domain, bus, device, pciDeviceId, pciSubSystemId; char busId[32]; };
+typedef int (*nvmlInit_t)();
+typedef int (*nvmlByPci_t)(const char*, void**);
+typedef int (*nvmlLinkState_t)(void*, unsigned int, unsigned int*);
+typedef int (*nvmlLinkRemotePci_t)(void*, unsigned int, NvmlPci*);
+typedef int (*nvmlLinkRemoteType_t)(void*, unsigned int, unsigned int*);
+typedef int (*nvmlFieldValues_t)(void*, int, void*);
+}  // namespace
+
+B200_API int b200_nvlink_report(int device, int* links_active, int* links_to_switch, int* peer_links, int cap,
+                                int* link_gbs, int* multicast) {
+  *links_active = *links_to_switch = *link_gbs = 0;
+  for (int p = 0; p < cap; ++p) peer_links[p] = 0;
+  int mc = 0;
+  {
+    CUdevice cd;
+    if (drv().DeviceGet && drv().DeviceGet(&cd, device) == CUDA_SUCCESS && drv().DeviceGetAttribute)
+      drv().DeviceGetAttribute(&mc, CU_DEVICE_ATTRIBUTE_MULTICAST_SUPPORTED, cd);
+  }
+  *multicast = mc;
+  void* h = dlopen("libnvidia-ml.so.1", RTLD_NOW | RTLD_LOCAL);
+  if (!h) return 1;
+  auto init = (nvmlInit_t)dlsym(h, "nvmlInit_v2");
+  auto byPci = (nvmlByPci_t)dlsym(h, "nvmlDeviceGetHandleByPciBusId_v2");
+  auto linkState = (nvmlLinkState_t)dlsym(h, "nvmlDeviceGetNvLinkState");
+  auto remotePci = (nvmlLinkRemotePci_t)dlsym(h, "nvmlDeviceGetNvLinkRemotePciInfo_v2");
+  auto remoteType = (nvmlLinkRemoteType_t)dlsym(h, "nvmlDeviceGetNvLinkRemoteDeviceType");
+  if (!init || !byPci || !linkState || init() != 0) return 1;
+  char bus[64] = {0};
+  if (cudaDeviceGetPCIBusId(bus, sizeof(bus), device) != cudaSuccess) return 1;
+  void* dev = nullptr;
+  if (byPci(bus, &dev) != 0) return 1;
+  // PCI bus ids of the other visible CUDA devices, to recognise direct GPU-GPU links
+  int n = 0;
+  cudaGetDeviceCount(&n);
+  char peers[64][64];
+  for (int p = 0; p < n && p < 64; ++p) cudaDeviceGetPCIBusId(peers[p], 64, p);
+  for (unsigned int link = 0; link < 18; ++link) {
+    unsigned int active = 0;
+    if (linkState(dev, link, &active) != 0 || !active) continue;
+    ++*links_active;
+    unsigned int type = 99;
+    if (remoteType && remoteType(dev, link, &type) == 0 && type == 1 /* NVML_NVLINK_DEVICE_TYPE_SWITCH */) {
+      ++*links_to_switch;
+      continue;
+    }
+    NvmlPci pci;
+    if (remotePci && remotePci(dev, link, &pci) == 0)
+      for (int p = 0; p < n && p < cap && p < 64; ++p)
+        if (p != device && strcasecmp(pci.busId, peers[p]) == 0) ++peer_links[p];
+  }
+  // NVML field NVML_FI_DEV_NVLINK_SPEED_MBPS_COMMON (90): per-link speed in MB/s
+  struct FieldValue { unsigned int fieldId, scopeId; long long timestamp, latencyUsec; unsigned int valueType, nvmlReturn;
+                      union { double d; unsigned int ui; unsigned long ul; unsigned long long ull; long long sll; } value; };
+  auto fields = (nvmlFieldValues_t)dlsym(h, "nvmlDeviceGetFieldValues");
+  if (fields) {
+    FieldValue fv;
+    memset(&fv, 0, sizeof(fv));
+    fv.fieldId = 90;
+    if (fields(dev, 1, &fv) == 0 && fv.nvmlReturn == 0) *link_gbs = (int)(fv.value.ui / 1000);
+  }
+  return 0;
+}

@@ -57,7 +57,7 @@ def main():
         iters = 200 if nbytes <= (1 << 20) else (30 if nbytes <= (1 << 26) else 8)
         row = {"bytes": n * 4, "world": world}
         view = sym[:n]
-        algos = ["oneshot"] if n * 4 <= (256 << 10) else ((["nvls"] if be.multicast else []) + ["p2p"])
+        algos = ["oneshot"] if n * 4 <= be.oneshot_max_bytes else ((["nvls"] if be.multicast else []) + ["p2p"])
         for algo in algos:
             blocks_list = [64] if algo == "oneshot" else [32, 64, 128]
             best = None
@@ -70,9 +70,22 @@ def main():
                 if best is None or ms < best[0]:
                     best = (ms, blocks)
             row[f"ours_{algo}_ms"], row[f"ours_{algo}_blocks"] = best
+        if n * 4 >= 700_000_000 and n % 10 == 0:
+            # the DDP bucket itself: one-pass tile kernel (reduce + 1/world + SGD + weight push), counters pre-satisfied
+            if "w" not in globals():
+                globals()["w"] = be.alloc_symmetric(n, torch.float32)
+                globals()["rdy"] = be.alloc_symmetric(256, torch.int32, multicast=False)
+                globals()["rdy"].fill_(1 << 30)
+                sync()
+            from torch_distributed_sandbox_b200 import ops
+            slab = ops.fc_bwd_tile_slab_floats(8)
+            for blocks in (8, 16, 32):
+                f = lambda: be.all_reduce_tiles(view.view(10, -1), w.view(10, -1), rdy, rows=10, slab_floats=slab, target=1,
+                                                scale=1.0 / world, lr=1e-4, channel=0, blocks=blocks)
+                row[f"ours_onepass_fused_sgd_{blocks}ctas_ms"] = mx(timeit(f, iters, sync))
         f = lambda: tdist.all_reduce(plain[:n])
         row["nccl_ms"] = mx(timeit(f, iters, sync))
-        ours = min(v for k, v in row.items() if k.startswith("ours_") and k.endswith("_ms"))
+        ours = min(v for k, v in row.items() if k.startswith("ours_") and k.endswith("_ms") and "onepass" not in k)
         fac = 2 * (world - 1) / world
         row["ours_busbw_gbs"] = n * 4 / ours / 1e6 * fac
         row["nccl_busbw_gbs"] = n * 4 / row["nccl_ms"] / 1e6 * fac

@@ -36,6 +36,7 @@ class EngineGradSync:
         self.blocks = int(os.environ.get("B200DP_AR_BLOCKS", "32"))     # CTAs of the overlapped bucket all-reduce (tuned at N=2)
         self._fc_event = None
         self._steps = 0
+        self._bn_synced = False
         # SM partition (common.cu); 0 = share SMs.  Each rank reduces 1/world of the bucket, so the comm CTAs a
         # step needs shrink with the world size (measured best: 8 at N=2, 4 at N=8).
         self.reserved_sms = int(os.environ.get("B200DP_RESERVED_SMS", str({2: 8, 4: 6}.get(self.world, 4))))
@@ -119,8 +120,12 @@ class EngineGradSync:
     def before_forward(self) -> None:
         """C4: BatchNorm running stats follow rank 0 (they are not used by the train-mode
         forward; this keeps checkpoints identical on every rank, like DDP does)."""
-        if self.world > 1 and self.broadcast_buffers:
+        # Normally nothing to do: the broadcast of step k's buffers is folded into step k's small-bucket kernel
+        # (small_grads_ready), which leaves exactly the state DDP's broadcast before forward k+1 would.  A forward
+        # that was not preceded by such a step (the first one after a load, two forwards in a row) syncs here.
+        if self.world > 1 and self.broadcast_buffers and not self._bn_synced:
             self.backend.broadcast_symmetric_inplace(self.engine.bn_flat, 0)
+        self._bn_synced = False
 
     def fc_grad_ready(self, engine) -> None:
         """Called right after the fc backward kernel is enqueued (main stream)."""
@@ -165,7 +170,10 @@ class EngineGradSync:
         """One-shot all-reduce of the 53 KB bucket with the SGD update fused in; True = parameters updated."""
         if self.world == 1:
             return False
-        self.backend.all_reduce_small_symmetric(engine.small_grad, 1.0 / self.world, sgd=(engine.small, engine.lr))
+        fold = self.broadcast_buffers and os.environ.get("B200DP_FOLD_BN_BCAST", "1") == "1"
+        self.backend.all_reduce_small_symmetric(engine.small_grad, 1.0 / self.world, sgd=(engine.small, engine.lr),
+                                                bcast=(engine.bn_flat, 0) if fold else None)
+        self._bn_synced = fold
         return True
 
     def wait_fc_grad(self, engine) -> bool:

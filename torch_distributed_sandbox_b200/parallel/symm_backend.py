@@ -18,6 +18,7 @@ overlapped bucket all-reduce never shares flag words with a concurrent small col
 from __future__ import annotations
 
 import ctypes
+import os
 from ctypes import c_char_p, c_float, c_int, c_size_t, c_uint32, c_void_p
 from typing import Dict, List, Optional, Tuple
 
@@ -26,6 +27,8 @@ import torch
 from .. import _native
 
 ONESHOT_MAX_BYTES = 256 << 10
+PUSH_SLOT_BYTES = 512 << 10           # per-rank slot of the push ring (small-message all-reduce)
+PUSH_MAX_RANKS = 16
 STAGING_BYTES = 32 << 20
 _DT = {torch.float32: 0, torch.float64: 1, torch.int32: 2, torch.int64: 3, torch.bfloat16: 5}
 
@@ -174,20 +177,60 @@ class SymmBackend:
         self._flags = SymmBuffer(self, 2 * fb, multicast=False)
         self._flag_arr = [self._flags.ptr_array(0), self._flags.ptr_array(fb)]
         self._staging = SymmBuffer(self, STAGING_BYTES, multicast=True)
-        self._buffers += [self._flags, self._staging]
+        # push ring for small messages: [2 halves][16 slots][512 KiB], one copy on every rank
+        self._push = SymmBuffer(self, 2 * PUSH_MAX_RANKS * PUSH_SLOT_BYTES, multicast=False)
+        self._push_calls = 0
+        lib.b200_ar_push.argtypes = [ctypes.POINTER(c_void_p), ctypes.POINTER(c_void_p), c_int, c_int, c_void_p, c_void_p,
+                                     c_size_t, c_int, c_int, c_float, c_size_t, c_int, c_int, c_uint32, c_void_p]
+        self._push_arr = self._push.ptr_array(0)
+        self._buffers += [self._flags, self._staging, self._push]
         self.multicast = self._staging.mc != 0
         self.comm_stream = torch.cuda.Stream(device=self.device, priority=-1)
+        self.oneshot_max_bytes = self.algo_policy()["oneshot_max_bytes"]
+        if self.rank == 0 and os.environ.get("B200DP_QUIET", "0") != "1":
+            t = self.topology()
+            print(f"[b200dp] process group up: world {self.size}, {self.device}: NVLink {t['nvlink_links_active']} links "
+                  f"active ({t['nvlink_links_to_switch']} to NVSwitch, {t['nvlink_link_gbs']} GB/s each), "
+                  f"multicast {'bound' if self.multicast else 'not bound'}; "
+                  f"all-reduce: one-shot <= {self.oneshot_max_bytes >> 10} KiB, then {self.algo_policy()['large']}",
+                  flush=True)
 
     # ------------------------------------------------------------- helpers --
     def describe(self) -> Dict:
         return {"backend": "native-symmetric", "world": self.size, "nvls_multicast": bool(self.multicast)}
 
     def topology(self) -> Dict:
+        """Fabric report for this rank's GPU: CUDA peer access plus the NVML view of its NVLink links (how many are
+        up, how many end in an NVSwitch, direct links per peer, per-link speed) and NVLS multicast support."""
         n = torch.cuda.device_count()
         p2p, at = (c_int * 64)(), (c_int * 64)()
-        cnt = _lib().b200_symm_topology(self.device.index, p2p, at, 64)
-        return {"devices": cnt, "p2p": [int(p2p[i]) for i in range(min(cnt, n))],
-                "native_atomics": [int(at[i]) for i in range(min(cnt, n))], "multicast": bool(self.multicast)}
+        lib = _lib()
+        dev = self.device.index if self.device is not None else torch.cuda.current_device()
+        cnt = lib.b200_symm_topology(dev, p2p, at, 64)
+        out = {"devices": cnt, "p2p": [int(p2p[i]) for i in range(min(cnt, n))],
+               "native_atomics": [int(at[i]) for i in range(min(cnt, n))], "multicast": bool(self.multicast)}
+        la, ls, gbs, mc = c_int(0), c_int(0), c_int(0), c_int(0)
+        peer = (c_int * 64)()
+        IP = ctypes.POINTER(c_int)
+        lib.b200_nvlink_report.argtypes = [c_int, IP, IP, IP, c_int, IP, IP]
+        rc = lib.b200_nvlink_report(dev, ctypes.byref(la), ctypes.byref(ls), peer, 64, ctypes.byref(gbs), ctypes.byref(mc))
+        out.update({"nvml": rc == 0, "nvlink_links_active": la.value, "nvlink_links_to_switch": ls.value,
+                    "nvlink_direct_links": [int(peer[i]) for i in range(min(cnt, n))], "nvlink_link_gbs": gbs.value,
+                    "nvswitch": ls.value > 0, "multicast_supported": bool(mc.value)})
+        return out
+
+    def algo_policy(self) -> Dict:
+        """Collective algorithm thresholds chosen from the fabric and the world size (measured on 2/4/8 x B200,
+        profiles/allreduce_sweep_*): below `oneshot_max_bytes` every rank reads every peer (latency-bound, (n-1) x S
+        of inbound traffic is still cheap); above it the bucket is sharded - through the switch's reduction
+        (multimem) when an NVSwitch with multicast is there, with peer loads otherwise."""
+        t = self.topology()
+        nvls = bool(self.multicast and t["multicast_supported"])
+        n = self.size
+        oneshot = (512 << 10) if n <= 2 else (256 << 10) if n <= 4 else (128 << 10)
+        return {"large": "nvls" if nvls else "p2p", "oneshot_max_bytes": oneshot,
+                "why": ("NVSwitch + multicast: in-switch reduction" if nvls else
+                        "no multicast binding: two-shot over peer loads") + f"; world {n}"}
 
     def _next_epoch(self, channel: int) -> int:
         e = self.epoch[channel]
@@ -213,7 +256,8 @@ class SymmBackend:
         """COLLECTIVE.  Release the symmetric buffer `t` was allocated from (peer mappings, multicast binding and the
         physical memory); every rank must call it for the same buffer.  The tensor must not be used afterwards."""
         hit = self.lookup(t) if (self.size > 1 and t.is_cuda) else None
-        if hit is None or hit[0] in (getattr(self, "_flags", None), getattr(self, "_staging", None)):
+        if hit is None or hit[0] in (getattr(self, "_flags", None), getattr(self, "_staging", None),
+                                     getattr(self, "_push", None)):
             return False
         torch.cuda.synchronize(self.device)
         self.barrier()                       # no peer kernel may still be reading the buffer
@@ -257,7 +301,7 @@ class SymmBackend:
         nbytes = t.numel() * es
         flat = t.contiguous().view(-1) if not t.is_contiguous() else t.view(-1)
         sym = self.lookup(flat)
-        large_ok = t.dtype == torch.float32 and op == 0 and nbytes > ONESHOT_MAX_BYTES
+        large_ok = t.dtype == torch.float32 and op == 0 and nbytes > getattr(self, 'oneshot_max_bytes', ONESHOT_MAX_BYTES)
         if large_ok and sym is not None and sym[1] % 16 == 0 and flat.numel() % 4 == 0:
             buf, off = sym
             use_nvls = (algo or ("nvls" if buf.mc else "p2p")) in ("nvls", "nvls_excl")
@@ -273,6 +317,18 @@ class SymmBackend:
                                        (3 if algo == "nvls_excl" else 2) if use_nvls else 1, blocks or 64,
                                        self._next_epoch(channel), self._stream())
             _native.check(rc, "all_reduce(large)")
+        elif nbytes <= min(PUSH_SLOT_BYTES, getattr(self, "oneshot_max_bytes", ONESHOT_MAX_BYTES)) and sgd is None:
+            # latency path: one kernel pushes this rank's data into every peer's ring slot, synchronises once and
+            # reduces locally - no staging copy, the tensor can live anywhere
+            buf = self._push_calls & 1
+            self._push_calls += 1
+            rc = lib.b200_ar_push(self._push_arr, self._flag_arr[channel], self.rank, self.size,
+                                  c_void_p(flat.data_ptr()), c_void_p(flat.data_ptr()), flat.numel(), _DT[t.dtype], op,
+                                  scale, PUSH_SLOT_BYTES, buf, max(1, min(16, (nbytes + 16383) >> 14)),
+                                  self._next_epoch(channel), self._stream())
+            _native.check(rc, "all_reduce(push)")
+            if flat.data_ptr() != t.data_ptr():
+                t.copy_(flat.view_as(t))
         else:
             if sgd is not None:
                 raise RuntimeError("fused SGD is only available on symmetric fp32 buckets")
@@ -327,7 +383,8 @@ class SymmBackend:
 
     @_on_device
     def all_reduce_small_symmetric(self, t: torch.Tensor, scale: float, out: Optional[torch.Tensor] = None,
-                                   sgd: Optional[Tuple[torch.Tensor, float]] = None, channel: int = 0):
+                                   sgd: Optional[Tuple[torch.Tensor, float]] = None, channel: int = 0,
+                                   bcast: Optional[Tuple[torch.Tensor, int]] = None):
         """One-shot fp32 all-reduce reading a SYMMETRIC tensor on every rank directly (no staging copy):
         ``out = scale * sum`` and/or ``sgd[0] -= sgd[1] * scale * sum``; ``t`` itself is left untouched."""
         n = t.numel()
@@ -341,11 +398,24 @@ class SymmBackend:
         sym = self.lookup(t)
         assert sym is not None and sym[1] % 16 == 0 and n % 4 == 0 and t.dtype == torch.float32
         buf, off = sym
-        rc = _lib().b200_ar_oneshot_f32x4(buf.ptr_array(off), self._flag_arr[channel], self.rank, self.size,
-                                          c_void_p(out.data_ptr() if out is not None else 0),
-                                          c_void_p(sgd[0].data_ptr() if sgd is not None else 0), n, scale,
-                                          float(sgd[1]) if sgd is not None else 0.0,
-                                          max(1, min(32, (n // 4 + 511) // 512)), self._next_epoch(channel), self._stream())
+        lib = _lib()
+        args = (buf.ptr_array(off), self._flag_arr[channel], self.rank, self.size,
+                c_void_p(out.data_ptr() if out is not None else 0),
+                c_void_p(sgd[0].data_ptr() if sgd is not None else 0), n, scale,
+                float(sgd[1]) if sgd is not None else 0.0,
+                max(1, min(32, (n // 4 + 511) // 512)), self._next_epoch(channel), self._stream())
+        if bcast is None:
+            rc = lib.b200_ar_oneshot_f32x4(*args)
+        else:
+            # ``bcast=(symmetric fp32 tensor, root)``: every rank also takes the root's copy of that tensor, in the
+            # same kernel (DDP's per-forward BatchNorm-buffer sync folded into the small-bucket all-reduce)
+            bt, root = bcast
+            bs = self.lookup(bt)
+            assert bs is not None and bs[1] % 16 == 0 and bt.dtype == torch.float32 and bt.numel() % 4 == 0
+            PP = ctypes.POINTER(c_void_p)
+            lib.b200_ar_oneshot_f32x4_bcast.argtypes = [PP, PP, c_int, c_int, c_void_p, c_void_p, c_size_t, c_float,
+                                                        c_float, c_int, c_uint32, c_void_p, PP, c_size_t, c_int]
+            rc = lib.b200_ar_oneshot_f32x4_bcast(*args, bs[0].ptr_array(bs[1]), bt.numel(), int(root))
         _native.check(rc, "all_reduce(one-shot f32x4)")
 
     @_on_device
