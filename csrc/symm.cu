@@ -484,7 +484,7 @@ B200_API int b200_nvlink_report(int device, int* links_active, int* links_to_swi
     if (linkState(dev, link, &active) != 0 || !active) continue;
     ++*links_active;
     unsigned int type = 99;
-    if (remoteType && remoteType(dev, link, &type) == 0 && type == 1 /* NVML_NVLINK_DEVICE_TYPE_SWITCH */) {
+    if (remoteType && remoteType(dev, link, &type) == 0 && type == 2 /* NVML_NVLINK_DEVICE_TYPE_SWITCH */) {
       ++*links_to_switch;
       continue;
     }
@@ -500,8 +500,13 @@ B200_API int b200_nvlink_report(int device, int* links_active, int* links_to_swi
   if (fields) {
     FieldValue fv;
     memset(&fv, 0, sizeof(fv));
-    fv.fieldId = 90;
+    fv.fieldId = 90;                                   // NVML_FI_DEV_NVLINK_SPEED_MBPS_COMMON
     if (fields(dev, 1, &fv) == 0 && fv.nvmlReturn == 0) *link_gbs = (int)(fv.value.ui / 1000);
+    if (*link_gbs == 0) {
+      memset(&fv, 0, sizeof(fv));
+      fv.fieldId = 164;                                // NVML_FI_DEV_NVLINK_GET_SPEED, scope = link 0
+      if (fields(dev, 1, &fv) == 0 && fv.nvmlReturn == 0) *link_gbs = (int)(fv.value.ui / 1000);
+    }
   }
   return 0;
 }

@@ -37,7 +37,7 @@ def main():
     tdist.init_process_group("nccl", device_id=dev)
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
     be = dist._default().backend
-    sizes = [1 << k for k in range(10, 31, 2)] + [53_376, 720_000_040 // 16 * 16]
+    sizes = [1 << k for k in range(10, 31, 2)] + [53_376, 720_000_000]
     maxn = max(sizes) // 4
     sym = be.alloc_symmetric(maxn, torch.float32)
     plain = torch.zeros(maxn, device=dev)
@@ -54,6 +54,7 @@ def main():
 
     for nbytes in sorted(sizes):
         n = nbytes // 4 // 4 * 4
+        assert n * 4 == nbytes or nbytes == 53_376, nbytes
         iters = 200 if nbytes <= (1 << 20) else (30 if nbytes <= (1 << 26) else 8)
         row = {"bytes": n * 4, "world": world}
         view = sym[:n]

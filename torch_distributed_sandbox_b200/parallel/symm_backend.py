@@ -301,7 +301,8 @@ class SymmBackend:
         nbytes = t.numel() * es
         flat = t.contiguous().view(-1) if not t.is_contiguous() else t.view(-1)
         sym = self.lookup(flat)
-        large_ok = t.dtype == torch.float32 and op == 0 and nbytes > getattr(self, 'oneshot_max_bytes', ONESHOT_MAX_BYTES)
+        large_ok = t.dtype == torch.float32 and op == 0 and (
+            nbytes > getattr(self, 'oneshot_max_bytes', ONESHOT_MAX_BYTES) or sgd is not None or algo is not None)
         if large_ok and sym is not None and sym[1] % 16 == 0 and flat.numel() % 4 == 0:
             buf, off = sym
             use_nvls = (algo or ("nvls" if buf.mc else "p2p")) in ("nvls", "nvls_excl")
