@@ -802,6 +802,115 @@ fc_bwd_kernel(const float* __restrict__ dl, const T* __restrict__ p2, float* W,
   }
 }
 
+// Any-batch variant (batch > 8): the batch is a run-time loop INSIDE the pass over the 18M axis, so fc.weight
+// (720 MB) is read once and dW written once per step whatever the batch - the templated kernel above keeps a batch
+// chunk in registers and needs one full pass (plus a read-modify-write of dW) per 8 rows, which at batch 64 cost
+// 11 ms of a 50 ms step.  dlogits sits in shared memory (broadcast reads); a thread owns 4 columns of all ten rows.
+template <typename T>
+__global__ void __launch_bounds__(256)
+fc_bwd_anybatch_kernel(const float* __restrict__ dl, const T* __restrict__ p2, float* W, float* dW,
+                       T* __restrict__ dp2, int B, size_t F, float lr, float gscale,
+                       const float* __restrict__ bn2, float* __restrict__ bwd_partials) {
+  extern __shared__ float s_dl_dyn[];                  // [B][12]: ten dlogits per row, padded to 48 bytes
+  __shared__ float s_bp[8][64];
+  for (int i = threadIdx.x; i < B * kNC; i += 256) s_dl_dyn[(i / kNC) * 12 + (i % kNC)] = dl[i];
+  __syncthreads();
+  const int c0 = 4 * (threadIdx.x & 7);
+  float k_shift[4], k_inv[4], k_mu[4], k_rs[4], a_dy[4], a_dyx[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    a_dy[i] = 0.f; a_dyx[i] = 0.f;
+    const float sc = bn2 ? bn2[c0 + i] : 1.f;
+    k_inv[i] = sc != 0.f ? 1.f / sc : 0.f;
+    k_shift[i] = bn2 ? bn2[32 + c0 + i] : 0.f;
+    k_mu[i] = bn2 ? bn2[64 + c0 + i] : 0.f;
+    k_rs[i] = bn2 ? bn2[96 + c0 + i] : 0.f;
+  }
+  const size_t n4 = F / 4;
+  for (size_t j = (size_t)blockIdx.x * 256 + threadIdx.x; j < n4; j += (size_t)gridDim.x * 256) {
+    float4 w[kNC], g[kNC];
+#pragma unroll
+    for (int k = 0; k < kNC; ++k) {
+      w[k] = *reinterpret_cast<const float4*>(W + (size_t)k * F + 4 * j);
+      g[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    // rows in chunks of four, the next chunk's loads in flight while this one is used (rows are F apart in memory:
+    // every load is its own DRAM burst, so memory-level parallelism has to come from the row loop); two named
+    // buffers, because a run-time index into a register array would put it in local memory
+    float avA[4][4], avB[4][4];
+    auto load_chunk = [&](int b0, float (&dst)[4][4]) {
+#pragma unroll
+      for (int r = 0; r < 4; ++r)
+        if (b0 + r < B) Act<T>::load4(p2 + (size_t)(b0 + r) * F + 4 * j, dst[r]);
+    };
+    auto use_chunk = [&](int b0, float (&av)[4][4]) {
+#pragma unroll
+      for (int r = 0; r < 4; ++r) {
+        const int b = b0 + r;
+        if (b < B) {
+          const float4 d0 = *reinterpret_cast<const float4*>(s_dl_dyn + b * 12);
+          const float4 d1 = *reinterpret_cast<const float4*>(s_dl_dyn + b * 12 + 4);
+          const float2 d2 = *reinterpret_cast<const float2*>(s_dl_dyn + b * 12 + 8);
+          const float d[kNC] = {d0.x, d0.y, d0.z, d0.w, d1.x, d1.y, d1.z, d1.w, d2.x, d2.y};
+          float4 sacc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+          for (int k = 0; k < kNC; ++k) {
+            sacc.x = fmaf(d[k], w[k].x, sacc.x); sacc.y = fmaf(d[k], w[k].y, sacc.y);
+            sacc.z = fmaf(d[k], w[k].z, sacc.z); sacc.w = fmaf(d[k], w[k].w, sacc.w);
+            g[k].x = fmaf(d[k], av[r][0], g[k].x); g[k].y = fmaf(d[k], av[r][1], g[k].y);
+            g[k].z = fmaf(d[k], av[r][2], g[k].z); g[k].w = fmaf(d[k], av[r][3], g[k].w);
+          }
+          float gq[4] = {sacc.x, sacc.y, sacc.z, sacc.w};
+          Act<T>::store4(dp2 + (size_t)b * F + 4 * j, gq);
+          if (bn2) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              const float y = av[r][i];
+              const float gg = y > 0.f ? gq[i] : 0.f;
+              a_dy[i] += gg;
+              a_dyx[i] = fmaf(gg, ((y - k_shift[i]) * k_inv[i] - k_mu[i]) * k_rs[i], a_dyx[i]);
+            }
+          }
+        }
+      }
+    };
+    load_chunk(0, avA);
+    for (int b0 = 0; b0 < B; b0 += 8) {
+      load_chunk(b0 + 4, avB);
+      use_chunk(b0, avA);
+      load_chunk(b0 + 8, avA);
+      use_chunk(b0 + 4, avB);
+    }
+#pragma unroll
+    for (int k = 0; k < kNC; ++k) {
+      if (dW)
+        *reinterpret_cast<float4*>(dW + (size_t)k * F + 4 * j) =
+            make_float4(g[k].x * gscale, g[k].y * gscale, g[k].z * gscale, g[k].w * gscale);
+      if (lr != 0.f)
+        *reinterpret_cast<float4*>(W + (size_t)k * F + 4 * j) =
+            make_float4(fmaf(-lr, g[k].x, w[k].x), fmaf(-lr, g[k].y, w[k].y), fmaf(-lr, g[k].z, w[k].z),
+                        fmaf(-lr, g[k].w, w[k].w));
+    }
+  }
+  if (bn2) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      float a = a_dy[i], q = a_dyx[i];
+      a += __shfl_xor_sync(0xffffffffu, a, 8);  q += __shfl_xor_sync(0xffffffffu, q, 8);
+      a += __shfl_xor_sync(0xffffffffu, a, 16); q += __shfl_xor_sync(0xffffffffu, q, 16);
+      if (lane < 8) { s_bp[warp][4 * lane + i] = a; s_bp[warp][32 + 4 * lane + i] = q; }
+    }
+    __syncthreads();
+    if (threadIdx.x < 64) {
+      float a = 0.f;
+#pragma unroll
+      for (int w8 = 0; w8 < 8; ++w8) a += s_bp[w8][threadIdx.x];
+      bwd_partials[(size_t)blockIdx.x * 64 + threadIdx.x] = a;
+    }
+  }
+}
+
 // K14: p -= lr * g (vectorised; n need not be a multiple of 4).
 __global__ void sgd_kernel(float* __restrict__ p, const float* __restrict__ g, size_t n, float lr) {
   const size_t n4 = n / 4;
@@ -1116,11 +1225,20 @@ template <typename T>
 static int fc_bwd_t(const void* dlogits, const void* p2, void* W, void* dW, void* dp2, int bt, size_t F,
                     float lr, int accumulate, float gscale, const void* bn2, void* bwd_partials, void* stream,
                     void* ready = nullptr, int sweeps_per_slab = 0) {
-  B200_CHECK(bt >= 1 && bt <= 8, "fc_bwd: batch chunk must be 1..8 (got %d)", bt);
+  B200_CHECK(bt >= 1 && bt <= 4096, "fc_bwd: batch must be 1..4096 (got %d)", bt);
   B200_CHECK(F % 4 == 0, "fc_bwd: F must be a multiple of 4");
   B200_CHECK(!bn2 || (F % 32 == 0 && bwd_partials), "fc_bwd: fused BN statistics need F %% 32 == 0 and a partials buffer");
   cudaStream_t s = (cudaStream_t)stream;
   const int grid = b200_fc_grid();
+  if (bt > 8) {          // any-batch kernel: one pass over W for the whole batch (no accumulate, no slab counters)
+    B200_CHECK(!accumulate && !ready, "fc_bwd: batches > 8 run in one pass (accumulate / slab counters do not apply)");
+    const size_t smem = (size_t)bt * 12 * sizeof(float);
+    B200_CUDA(set_max_smem(fc_bwd_anybatch_kernel<T>, (int)smem));
+    fc_bwd_anybatch_kernel<T><<<grid, 256, smem, s>>>((const float*)dlogits, (const T*)p2, (float*)W, (float*)dW, (T*)dp2,
+                                                     bt, F, lr, gscale, (const float*)bn2, (float*)bwd_partials);
+    B200_LAUNCH_CHECK();
+    return 0;
+  }
   switch (bt) {
 #define B200_FCB(N) case N: fc_bwd_kernel<N, T><<<grid, 256, 0, s>>>((const float*)dlogits, (const T*)p2, (float*)W, (float*)dW, (T*)dp2, F, lr, accumulate, gscale, (const float*)bn2, (float*)bwd_partials, (unsigned int*)ready, sweeps_per_slab); break;
     B200_FCB(1) B200_FCB(2) B200_FCB(3) B200_FCB(4) B200_FCB(5) B200_FCB(6) B200_FCB(7) B200_FCB(8)

@@ -405,3 +405,32 @@ def test_conv2_dgrad_fused_bn1_backward_stats(ops, shape):
     ops.bn_bwd_finalize(part2, grid, 16, B * 4 * H * W, red_r, dg_r, db_r)
     report(f"fused bn1 bwd dbeta {shape}", rel(db_f, db_r), 1e-5)
     report(f"fused bn1 bwd dgamma {shape}", rel(dg_f, dg_r), 1e-2)
+
+
+@pytest.mark.parametrize("dt", [torch.bfloat16, torch.float32])
+@pytest.mark.parametrize("B", [9, 33])
+def test_fc_bwd_any_batch_single_pass(ops, B, dt):
+    """Batches > 8 run the any-batch kernel (one pass over W): dW, dp2, fused SGD and the fused BN-2 reductions
+    against fp64 matmuls / the <= 8-row kernel."""
+    C, H, W_ = 32, 8, 12
+    Fdim = C * H * W_
+    g = torch.Generator(device=DEV).manual_seed(17)
+    p2 = torch.rand(B, Fdim, device=DEV, generator=g).to(dt)
+    Wt = torch.randn(10, Fdim, device=DEV, generator=g) * 0.02
+    dl = torch.randn(B, 10, device=DEV, generator=g) * 0.1
+    bn = torch.stack([torch.rand(C, device=DEV, generator=g) + 0.5, torch.randn(C, device=DEV, generator=g) * 0.1,
+                      torch.randn(C, device=DEV, generator=g) * 0.1, torch.rand(C, device=DEV, generator=g) + 0.5]).contiguous()
+    dW, dp2, W0 = torch.zeros_like(Wt), torch.empty_like(p2), Wt.clone()
+    part = torch.zeros(ops.fc_grid(), 64, device=DEV)
+    ops.fc_bwd(dl, p2, Wt, dW, dp2, bn2=bn, bwd_partials=part)
+    report(f"fc_bwd any-batch dW B={B}", rel(dW, dl.double().t() @ p2.double()), 1e-5)
+    report(f"fc_bwd any-batch dp2 B={B}", rel(dp2, dl.double() @ W0.double()), 5e-3 if dt == torch.bfloat16 else 1e-6)
+    # BN-2 reductions: the same rows through the <= 8-row kernel, chunk by chunk
+    ref_part = torch.zeros_like(part)
+    tmp = torch.empty_like(p2)
+    for b0 in range(0, B, 8):
+        ops.fc_bwd(dl[b0:b0 + 8], p2[b0:b0 + 8], Wt, None, tmp[b0:b0 + 8], accumulate=b0 > 0, bn2=bn, bwd_partials=ref_part)
+    assert torch.equal(tmp, dp2)
+    report(f"fc_bwd any-batch bn partials B={B}", rel(part.sum(0), ref_part.sum(0)), 1e-5)
+    ops.fc_bwd(dl, p2, Wt, None, dp2, lr=0.5)
+    report(f"fc_bwd any-batch fused sgd B={B}", rel(Wt, W0.double() - 0.5 * (dl.double().t() @ p2.double())), 1e-6)

@@ -344,7 +344,7 @@ class FusedConvNet:
         x, x1, p1, x2 = self.x[:B], self.x1[:B], self.p1[:B], self.x2[:B]
         dx2, dp1 = x2, p1                  # in-place gradients (dp2 over p2, dx2 over x2, dp1 over p1)
         gs = self.grad_scale
-        fused = allow_fused_sgd and self.fuse_fc_sgd and self.comm is None and B <= 8
+        fused = allow_fused_sgd and self.fuse_fc_sgd and self.comm is None
         if not fused and self.fcw_grad is None:
             self.fcw_grad = torch.empty_like(self.fcw)
         p2 = self.p2[:B].view(B, self.F)
@@ -355,11 +355,10 @@ class FusedConvNet:
                  self.comm.fc_bwd_tiles(self, self.dlogits[:B], p2, dp2, self.bn2 if fuse_stats else None,
                                         self.part_fcb if fuse_stats else None))
         if not tiled:
-            for b0 in range(0, B, 8):
-                b1 = min(B, b0 + 8)
-                ops.fc_bwd(self.dlogits[b0:b1], p2[b0:b1], self.fcw, None if fused else self.fcw_grad, dp2[b0:b1],
-                           lr=self.lr if fused else 0.0, accumulate=b0 > 0, gscale=gs,
-                           bn2=self.bn2 if fuse_stats else None, bwd_partials=self.part_fcb if fuse_stats else None)
+            # one launch for any batch: <= 8 rows stay in registers, larger batches loop inside the single pass over W
+            ops.fc_bwd(self.dlogits[:B], p2, self.fcw, None if fused else self.fcw_grad, dp2,
+                       lr=self.lr if fused else 0.0, accumulate=False, gscale=gs,
+                       bn2=self.bn2 if fuse_stats else None, bwd_partials=self.part_fcb if fuse_stats else None)
         self._fc_fused_done = fused
         # async all-reduce of the 720 MB bucket.  By default it starts after the next kernel instead of here:
         # pool_bn_bwd is HBM-bound and lost 0.16 ms to the all-reduce's 1.4 GB of HBM traffic, while the

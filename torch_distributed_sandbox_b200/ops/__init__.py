@@ -247,8 +247,9 @@ def cross_entropy(logits, labels, loss, dlogits, dbias, gscale=1.0):
 
 
 def fc_bwd(dlogits, p2_bf16, W, dW, dp2_bf16, lr=0.0, accumulate=False, gscale=1.0, bn2=None, bwd_partials=None):
-    """K10(+K14): dW (optional), dp2 and optional in-place SGD on W, one streaming pass.  With ``bn2`` the
-    BatchNorm-2 backward reductions are produced too (partials [fc_grid()][64]), replacing a pass over x2."""
+    """K10(+K14): dW (optional), dp2 and optional in-place SGD on W, one streaming pass over W for ANY batch (up to 8
+    rows are held in registers; larger batches loop inside the pass).  With ``bn2`` the BatchNorm-2 backward
+    reductions are produced too (partials [fc_grid()][64]), replacing a pass over x2."""
     bt, F = p2_bf16.shape[0], p2_bf16[0].numel()
     assert p2_bf16.dtype == dp2_bf16.dtype
     _native.check(_fn("b200_fc_bwd", p2_bf16)(_p(dlogits), _p(p2_bf16), _p(W), _p(dW), _p(dp2_bf16), bt, F, lr,
