@@ -23,9 +23,18 @@ def log(*a):
         out.flush()
 
 
+def _fresh():
+    """Start every measurement from an empty pool and a reset peak counter (an OOM's traceback keeps its tensors
+    alive until the handler has returned, so the clean-up in `finally` alone left a stale peak for the next run)."""
+    gc.collect()
+    torch.cuda.empty_cache()
+    torch.cuda.reset_peak_memory_stats()
+
+
 def try_reference(batch, steps=2):
     import torch.nn as nn
     import mnist_onegpu as ref
+    _fresh()
     try:
         torch.manual_seed(0)
         model = ref.ConvNet()
@@ -50,11 +59,12 @@ def try_reference(batch, steps=2):
         torch.cuda.reset_peak_memory_stats()
 
 
-def try_engine(batch, steps=3, timeit=False):
+def try_engine(batch, steps=3, timeit=False, precision="bf16"):
     from torch_distributed_sandbox_b200.models.engine import FusedConvNet
     eng = None
+    _fresh()
     try:
-        eng = FusedConvNet((3000, 3000), batch_size=batch, lr=1e-4, seed=0)
+        eng = FusedConvNet((3000, 3000), batch_size=batch, lr=1e-4, seed=0, precision=precision)
         g = torch.Generator().manual_seed(0)
         imgs = torch.randint(0, 256, (batch, 28, 28), dtype=torch.uint8, generator=g).cuda()
         labels = torch.randint(0, 10, (batch,), generator=g).cuda()
@@ -98,12 +108,13 @@ def main():
         log(f"reference  batch {b:3d}: {'fits' if ok else 'OOM '}  peak {peak:5.1f} GiB")
         if not ok:
             break
-    for b in (64, 128, 256, 288):
-        ok, peak, ms = try_engine(b, timeit=True)
-        log(f"b200dp     batch {b:3d}: {'fits' if ok else 'OOM '}  peak {peak:5.1f} GiB" +
-            (f"  {ms:.1f} ms/step = {b / ms * 1e3:.0f} img/s" if ms else ""))
-        if not ok:
-            break
+    for prec, batches in (("bf16", (64, 128, 256, 288)), ("tf32", (64, 128, 144))):
+        for b in batches:
+            ok, peak, ms = try_engine(b, timeit=True, precision=prec)
+            log(f"b200dp {prec} batch {b:3d}: {'fits' if ok else 'OOM '}  peak {peak:5.1f} GiB" +
+                (f"  {ms:.1f} ms/step = {b / ms * 1e3:.0f} img/s" if ms else ""))
+            if not ok:
+                break
 
 
 if __name__ == "__main__":
