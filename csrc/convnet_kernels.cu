@@ -631,13 +631,16 @@ fc_fwd_kernel(const T* __restrict__ p2, const float* __restrict__ W,
   }
 }
 
+// one warp per output (a single thread walking 592 partials in fp64 took 40 us: a serial tail on the critical path)
 __global__ void fc_reduce_kernel(const float* __restrict__ partials, int nparts, int n,
                                  const float* __restrict__ bias, float* __restrict__ logits) {
-  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (i >= n) return;
   double s = 0.0;
-  for (int p = 0; p < nparts; ++p) s += (double)partials[(size_t)p * n + i];
-  logits[i] = (float)s + bias[i % kNC];
+  for (int p = lane; p < nparts; p += 32) s += (double)partials[(size_t)p * n + i];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  if (lane == 0) logits[i] = (float)s + bias[i % kNC];
 }
 
 // K9: CrossEntropyLoss(reduction='mean') forward + backward in one block:
@@ -1199,7 +1202,8 @@ static int fc_fwd_t(const void* p2, const void* W, const void* bias, void* parti
 #undef B200_FCF
   }
   B200_LAUNCH_CHECK();
-  fc_reduce_kernel<<<1, 128, 0, s>>>((const float*)partials, grid, bt * kNC, (const float*)bias, (float*)logits);
+  fc_reduce_kernel<<<(bt * kNC * 32 + 255) / 256, 256, 0, s>>>((const float*)partials, grid, bt * kNC, (const float*)bias,
+                                                              (float*)logits);
   B200_LAUNCH_CHECK();
   return 0;
 }
