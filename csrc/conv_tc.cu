@@ -449,7 +449,7 @@ struct RsCfg {
   // re-reads the whole A operand, so the longer ring of dgrad halves how often that happens.
   static constexpr int kTStages = 512 / COUT;
   static constexpr int kTmemCols = kTStages * COUT;          // 512
-  static constexpr int kSmemBytes = kWBytes + kSlots * kSlotBytes + 4096 + 128;
+  static constexpr int kSmemBytes = kWBytes + kSlots * kSlotBytes + 4096 + 1024;
   static_assert(kWBytes % 128 == 0 && kSlotBytes % 128 == 0, "alignment");
   static_assert(kTmemCols <= 512 && (kTmemCols & (kTmemCols - 1)) == 0, "TMEM columns");
 };
@@ -516,7 +516,14 @@ struct RowPlan {
 //     bnprev = [scale|shift|mean|rstd] of BN1:  dy = dp1 where p1 > 0,
 //     partials = [sum(dy) | sum(dy * xhat)],  xhat = ((p1 - shift)/scale - mean) * rstd.
 //     This replaces a separate pass over the 1.44 GB conv1 output.
-template <int CIN, int COUT, bool TRANSPOSED, int STATS, bool LDGSTS, typename ET = __nv_bfloat16>
+// SWZ (with LDGSTS = false): the input row is one TMA request.  A pixel's channel vector (CIN * sizeof(ET) = 32, 64
+// or 128 bytes) is a shared-memory ROW of the K-major operand in the hardware's 32 / 64 / 128-byte swizzle, which is
+// also how the pixel lies in NHWC memory: a 4-D tensor map {C, W, H, B} with box {C, 136, 1, 1} drops the whole row
+// segment, halo and zero padding included, in one request with an inner extent of a full pixel (the planar layout
+// needed one box row per 16-byte piece, which is what made TMA slow here).  The dx tap is still a start-address
+// shift - by whole rows now; the swizzle is a function of the address bits, so a shifted start reads each row with
+// the phase TMA wrote it with - and a K-step is +32 bytes inside the row.
+template <int CIN, int COUT, bool TRANSPOSED, int STATS, bool LDGSTS, typename ET = __nv_bfloat16, bool SWZ = false>
 __global__ void __launch_bounds__(kRsThreads, 1)
 conv5x5_rs_kernel(const __grid_constant__ CUtensorMap tm_act, const ET* __restrict__ act,
                   const float* __restrict__ w,
@@ -525,10 +532,17 @@ conv5x5_rs_kernel(const __grid_constant__ CUtensorMap tm_act, const ET* __restri
                   ConvGeom g) {
   using Cfg = RsCfg<CIN, COUT, ET>;
   constexpr bool kF32 = sizeof(ET) == 4;
-  static_assert(LDGSTS || !kF32, "the TMA feed exists for bf16 only");
+  static_assert(LDGSTS || SWZ || !kF32, "the planar TMA feed exists for bf16 only");
+  static_assert(!(SWZ && LDGSTS), "SWZ is a TMA feed");
+  constexpr int kRowB = CIN * (int)sizeof(ET);                       // bytes of one pixel = one operand row (SWZ)
+  constexpr uint32_t kSwzLayout = kRowB == 128 ? 2u : kRowB == 64 ? 4u : 6u;
+  static_assert(!SWZ || kRowB == 32 || kRowB == 64 || kRowB == 128, "a pixel must be one swizzle span");
+  static_assert(!SWZ || (kPW * kRowB == Cfg::kSlotBytes && Cfg::kSlotBytes % (8 * kRowB) == 0 && Cfg::kWBytes % 1024 == 0),
+                "row-major slots must keep the swizzle phase");
   constexpr int RT = Cfg::kTStages;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
-  uint8_t* smem = smem_raw + ((128u - (smem_u32(smem_raw) & 127u)) & 127u);
+  constexpr uint32_t kAlign = SWZ ? 1024u : 128u;
+  uint8_t* smem = smem_raw + ((kAlign - (smem_u32(smem_raw) & (kAlign - 1))) & (kAlign - 1));
   uint8_t* s_w = smem;
   uint8_t* s_slots = smem + Cfg::kWBytes;
   uint64_t* bars = reinterpret_cast<uint64_t*>(s_slots + Cfg::kSlots * Cfg::kSlotBytes);
@@ -613,9 +627,13 @@ conv5x5_rs_kernel(const __grid_constant__ CUtensorMap tm_act, const ET* __restri
           mbar_wait(&empty[slot], (use & 1) ^ 1);
           mbar_expect_tx(&full[slot], Cfg::kSlotBytes);
           uint8_t* dst = s_slots + slot * Cfg::kSlotBytes;
+          if constexpr (SWZ) {
+            tma_load_4d(dst, &tm_act, &full[slot], 0, x0 - 2, y0 - 2 + i, b);
+          } else {
 #pragma unroll
-          for (int p = 0; p < Cfg::kPlanes; ++p)
-            tma_load_5d(dst + p * kPlaneBytes, &tm_act, &full[slot], 0, p, x0 - 2, y0 - 2 + i, b);
+            for (int p = 0; p < Cfg::kPlanes; ++p)
+              tma_load_5d(dst + p * kPlaneBytes, &tm_act, &full[slot], 0, p, x0 - 2, y0 - 2 + i, b);
+          }
         }
       }
     }
@@ -626,8 +644,13 @@ conv5x5_rs_kernel(const __grid_constant__ CUtensorMap tm_act, const ET* __restri
     // ELECT / R2UR / BRA.U.ANY: ~285 SASS instructions per row on one lane - the bottleneck ncu showed.)
     constexpr uint32_t idesc0 = umma_idesc(UmmaKind<ET>::kFormat, kBM, 0, 0, 0);   // N filled in per MMA
     const uint32_t slots_addr = smem_u32(s_slots);
-    const uint64_t a_tmpl = smem_desc_noswz(0, kPlaneBytes, 128);          // LBO lives in the LOW word (bits 16..29)
+    // A: planar no-swizzle (LBO = plane stride, SBO = 8 pixels x 16 B) or swizzled rows (SBO = 8 rows)
+    const uint64_t a_tmpl = SWZ ? smem_desc(0, 16, 8 * kRowB, kSwzLayout) : smem_desc_noswz(0, kPlaneBytes, 128);
     const uint32_t a_hi = (uint32_t)(a_tmpl >> 32), a_lo0 = (uint32_t)a_tmpl;
+    // 16-byte units from the slot start to the operand of tap dx, K-step kk
+    auto a_off = [](int dx, int kk) -> uint32_t {
+      return SWZ ? (uint32_t)(dx * (kRowB >> 4) + kk * 2) : (uint32_t)(((2 * kk) * kPlaneBytes >> 4) + dx);
+    };
     const uint64_t b_tmpl = smem_desc_noswz(smem_u32(s_w), Cfg::kWChunkBytes, 128);
     const uint32_t b_hi = (uint32_t)(b_tmpl >> 32), b_lo0 = (uint32_t)b_tmpl;
     uint32_t gcount = 0, qbase = 0;
@@ -658,7 +681,7 @@ conv5x5_rs_kernel(const __grid_constant__ CUtensorMap tm_act, const ET* __restri
             for (int dx = 0; dx < 5; ++dx) {
 #pragma unroll
               for (int kk = 0; kk < Cfg::kKSteps; ++kk) {
-                const uint64_t a_desc = ((uint64_t)a_hi << 32) | (uint64_t)(a_lo_row + ((2 * kk) * kPlaneBytes >> 4) + dx);
+                const uint64_t a_desc = ((uint64_t)a_hi << 32) | (uint64_t)(a_lo_row + a_off(dx, kk));
                 const uint32_t b_lo = b_lo0 + (((dx * Cfg::kKSteps + kk) * Cfg::kWStepBytes) >> 4);
                 if (dx == 0 && kk == 0) {
                   UmmaKind<ET>::mma(d0, a_desc, ((uint64_t)b_hi << 32) | (uint64_t)b_lo, idesc0 | ((uint32_t)((4 * COUT) >> 3) << 17), 1u);
@@ -674,7 +697,7 @@ conv5x5_rs_kernel(const __grid_constant__ CUtensorMap tm_act, const ET* __restri
           for (int dx = 0; dx < 5; ++dx) {
 #pragma unroll
             for (int kk = 0; kk < Cfg::kKSteps; ++kk) {
-              const uint64_t a_desc = ((uint64_t)a_hi << 32) | (uint64_t)(a_lo_row + ((2 * kk) * kPlaneBytes >> 4) + dx);
+              const uint64_t a_desc = ((uint64_t)a_hi << 32) | (uint64_t)(a_lo_row + a_off(dx, kk));
               const uint32_t b_lo = b_lo0 + (((dx * Cfg::kKSteps + kk) * Cfg::kWStepBytes) >> 4);
               const bool first = (dx == 0 && kk == 0);
               const int acc_hi = first ? acc_hi_first : jj_hi;
@@ -1391,6 +1414,25 @@ int make_act_tmap(CUtensorMap* tm, const void* ptr, int B, int H, int W, int C, 
   return 0;
 }
 
+// 4-D map over an NHWC activation of `eb`-byte elements: {C, W, H, B}; box {C, boxW, 1, 1}; the inner extent is one
+// whole pixel (32 / 64 / 128 bytes) and selects the matching shared-memory swizzle.
+int make_row_tmap(CUtensorMap* tm, const void* ptr, int B, int H, int W, int C, int eb, int boxW) {
+  EncodeTiledFn enc = get_encode_fn();
+  if (!enc) return b200_fail(-3, "cuTensorMapEncodeTiled entry point not available");
+  const int rowb = C * eb;
+  cuuint64_t gdim[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)B};
+  cuuint64_t gstr[3] = {(cuuint64_t)rowb, (cuuint64_t)W * rowb, (cuuint64_t)H * W * rowb};
+  cuuint32_t box[4] = {(cuuint32_t)C, (cuuint32_t)boxW, 1, 1};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  const CUtensorMapSwizzle swz = rowb == 128 ? CU_TENSOR_MAP_SWIZZLE_128B : rowb == 64 ? CU_TENSOR_MAP_SWIZZLE_64B
+                                                                                        : CU_TENSOR_MAP_SWIZZLE_32B;
+  CUresult r = enc(tm, eb == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4,
+                   const_cast<void*>(ptr), gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swz,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return b200_fail((int)r, "cuTensorMapEncodeTiled (row map) failed with CUresult %d", (int)r);
+  return 0;
+}
+
 // Pick the row-segment length that best fills the persistent grid.
 ConvGeom make_geom(int B, int H, int W, int nsm, int halo_rows) {
   ConvGeom g;
@@ -1413,17 +1455,21 @@ ConvGeom make_geom(int B, int H, int W, int nsm, int halo_rows) {
 }
 
 // 1 = tap-stationary + TMA, 2 = row-stationary + TMA, 3 = row-stationary + cp.async feed,
-// 4 = 3 with the dx-replicated weight-gradient kernel (M = 128) (default)
-int g_conv_tc_version = 4;
+// 4 = 3 with the dx-replicated weight-gradient kernel (M = 128),
+// 5 = 4 with forward / dgrad fed by ONE TMA request per input row into swizzled pixel rows (default)
+int g_conv_tc_version = 5;
 
-template <int CIN, int COUT, bool TRANSPOSED, int STATS, bool LDGSTS, typename ET = __nv_bfloat16>
+template <int CIN, int COUT, bool TRANSPOSED, int STATS, bool LDGSTS, typename ET = __nv_bfloat16, bool SWZ = false>
 int launch_conv_rs(const void* act, const void* w, const void* bias, void* out, void* partials, int B, int H, int W,
                    cudaStream_t s, int* grid_out, const void* pooled = nullptr, const void* bnprev = nullptr) {
   using Cfg = RsCfg<CIN, COUT, ET>;
-  auto kern = conv5x5_rs_kernel<CIN, COUT, TRANSPOSED, STATS, LDGSTS, ET>;
+  auto kern = conv5x5_rs_kernel<CIN, COUT, TRANSPOSED, STATS, LDGSTS, ET, SWZ>;
   B200_CUDA(set_max_smem(kern, Cfg::kSmemBytes));
   CUtensorMap tm;
-  if (!LDGSTS) {
+  if (SWZ) {
+    int rc = make_row_tmap(&tm, act, B, H, W, CIN, (int)sizeof(ET), kPW);
+    if (rc) return rc;
+  } else if (!LDGSTS) {
     int rc = make_act_tmap(&tm, act, B, H, W, CIN, kPW);
     if (rc) return rc;
   } else {
@@ -1443,6 +1489,9 @@ int launch_conv_rs(const void* act, const void* w, const void* bias, void* out, 
 template <int CIN, int COUT, bool TRANSPOSED, bool STATS>
 int launch_conv(const void* act, const void* w, const void* bias, void* out, void* partials, int B, int H, int W,
                 cudaStream_t s, int* grid_out) {
+  if (g_conv_tc_version >= 5)
+    return launch_conv_rs<CIN, COUT, TRANSPOSED, STATS ? 1 : 0, false, __nv_bfloat16, true>(act, w, bias, out, partials, B,
+                                                                                            H, W, s, grid_out);
   if (g_conv_tc_version >= 3)
     return launch_conv_rs<CIN, COUT, TRANSPOSED, STATS ? 1 : 0, true>(act, w, bias, out, partials, B, H, W, s, grid_out);
   if (g_conv_tc_version == 2)
@@ -1488,7 +1537,7 @@ int launch_wgrad_rep(const void* p1, const void* dx2, void* partials, void* dw2,
 // the partials buffer with b200_conv_tc_max_grid() x 2*COUT floats.
 B200_API int b200_conv_tc_max_grid() { return b200_num_sms(); }
 B200_API int b200_conv_tc_set_version(int v) {
-  if (v < 1 || v > 4) return b200_fail(-2, "conv_tc version must be 1..4");
+  if (v < 1 || v > 5) return b200_fail(-2, "conv_tc version must be 1..5");
   g_conv_tc_version = v;
   return 0;
 }
@@ -1513,6 +1562,9 @@ B200_API int b200_conv2_dgrad_tc(const void* dx2_bf16, const void* w2, void* dp1
 B200_API int b200_conv2_dgrad_stats_tc(const void* dx2_bf16, const void* w2, const void* pooled, const void* bn1,
                                        void* dp1_bf16, void* partials, int B, int H, int W, int* nparts_out,
                                        void* stream) {
+  if (g_conv_tc_version >= 5)
+    return launch_conv_rs<32, 16, true, 2, false, __nv_bfloat16, true>(dx2_bf16, w2, nullptr, dp1_bf16, partials, B, H, W,
+                                                                       (cudaStream_t)stream, nparts_out, pooled, bn1);
   if (g_conv_tc_version == 2)
     return launch_conv_rs<32, 16, true, 2, false>(dx2_bf16, w2, nullptr, dp1_bf16, partials, B, H, W,
                                                   (cudaStream_t)stream, nparts_out, pooled, bn1);
@@ -1553,16 +1605,25 @@ B200_API int b200_conv2_wgrad_tc(const void* p1_bf16, const void* dx2_bf16, void
 // Same contracts as the bf16 entry points above with every activation / gradient tensor in fp32.
 B200_API int b200_conv2_fwd_tc_f32(const void* p1, const void* w2, const void* b2, void* x2, void* partials, int B,
                                    int H, int W, int* nparts_out, void* stream) {
+  if (g_conv_tc_version >= 5)
+    return launch_conv_rs<16, 32, false, 1, false, float, true>(p1, w2, b2, x2, partials, B, H, W, (cudaStream_t)stream,
+                                                                nparts_out);
   return launch_conv_rs<16, 32, false, 1, true, float>(p1, w2, b2, x2, partials, B, H, W, (cudaStream_t)stream,
                                                        nparts_out);
 }
 B200_API int b200_conv2_dgrad_tc_f32(const void* dx2, const void* w2, void* dp1, int B, int H, int W, void* stream) {
+  if (g_conv_tc_version >= 5)
+    return launch_conv_rs<32, 16, true, 0, false, float, true>(dx2, w2, nullptr, dp1, nullptr, B, H, W,
+                                                               (cudaStream_t)stream, nullptr);
   return launch_conv_rs<32, 16, true, 0, true, float>(dx2, w2, nullptr, dp1, nullptr, B, H, W, (cudaStream_t)stream,
                                                       nullptr);
 }
 B200_API int b200_conv2_dgrad_stats_tc_f32(const void* dx2, const void* w2, const void* pooled, const void* bn1,
                                            void* dp1, void* partials, int B, int H, int W, int* nparts_out,
                                            void* stream) {
+  if (g_conv_tc_version >= 5)
+    return launch_conv_rs<32, 16, true, 2, false, float, true>(dx2, w2, nullptr, dp1, partials, B, H, W,
+                                                               (cudaStream_t)stream, nparts_out, pooled, bn1);
   return launch_conv_rs<32, 16, true, 2, true, float>(dx2, w2, nullptr, dp1, partials, B, H, W, (cudaStream_t)stream,
                                                       nparts_out, pooled, bn1);
 }

@@ -82,7 +82,8 @@ int b200_conv1_wgrad_tc(const void* in_f32, const void* x1_bf16, const void* dp1
  * partials (wgrad): [b200_conv_tc_max_grid()][12800] scratch. */
 int b200_conv_tc_max_grid(void);
 int b200_conv_tc_set_version(int v);   /* 1 tap-stationary+TMA, 2 row-stationary+TMA, 3 row-stationary+cp.async,
-                                          4 = 3 + dx-replicated M=128 weight-gradient kernel (default) */
+                                          4 = 3 + dx-replicated M=128 weight-gradient kernel,
+                                          5 = 4 + one TMA request per input row into swizzled pixel rows (default) */
 int b200_conv_tc_get_version(void);
 int b200_set_reserved_sms(int n);      /* SM partition for an overlapped collective (DDP); 0 = none, at most SM count - 1 */
 int b200_get_reserved_sms(void);

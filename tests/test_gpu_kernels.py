@@ -112,11 +112,12 @@ def test_bn_relu_pool(ops, C):
     report(f"bn_relu_pool C={C}", rel(to_nchw(p), ref), 4e-3)
 
 
-@pytest.fixture(params=[4, 3, 2, 1], ids=["rowstat_cpasync_wgradM128", "rowstat_cpasync", "rowstat_tma", "tapstat_tma"])
+@pytest.fixture(params=[5, 4, 3, 2, 1], ids=["rowstat_tma_swizzled_rows", "rowstat_cpasync_wgradM128", "rowstat_cpasync",
+                                              "rowstat_tma", "tapstat_tma"])
 def tc_version(ops, request):
     ops.conv_tc_set_version(request.param)
     yield request.param
-    ops.conv_tc_set_version(4)
+    ops.conv_tc_set_version(5)
 
 
 @pytest.mark.parametrize("shape", [(2, 24, 200), (1, 50, 128), (3, 17, 300), (1, 3, 40), (2, 133, 260)])
@@ -149,7 +150,7 @@ def few_ctas(ops):
     ops.set_reserved_sms(0)
 
 
-@pytest.mark.parametrize("ver", [4, 3, 2])
+@pytest.mark.parametrize("ver", [5, 4, 3, 2])
 def test_conv2_tc_long_items(ops, few_ctas, ver):
     ops.conv_tc_set_version(ver)
     try:
@@ -181,7 +182,7 @@ def test_conv2_tc_long_items(ops, few_ctas, ver):
         refw = torch.nn.grad.conv2d_weight(to_nchw(xb), (32, 16, 5, 5), to_nchw(dy), padding=2)
         report(f"conv2_wgrad_tc long items v{ver}", rel(dw, refw), 5e-3)
     finally:
-        ops.conv_tc_set_version(4)
+        ops.conv_tc_set_version(5)
 
 
 def test_conv1_tc_many_items_per_cta(ops, few_ctas):

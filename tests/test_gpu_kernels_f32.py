@@ -29,6 +29,14 @@ def ops():
     return o
 
 
+@pytest.fixture(params=[4, 5], ids=["cpasync_planar", "tma_swizzled_rows"])
+def feed(ops, request):
+    """conv2 forward / dgrad operand feed: 4 = cp.async into 16-byte planes, 5 = one TMA request per row into swizzled rows."""
+    ops.conv_tc_set_version(request.param)
+    yield request.param
+    ops.conv_tc_set_version(5)
+
+
 @pytest.fixture
 def few_ctas(ops):
     ops.set_reserved_sms(ops.sm_count() - 2)
@@ -77,7 +85,7 @@ def test_bn_relu_pool_f32(ops, C):
 
 
 @pytest.mark.parametrize("shape", [(2, 24, 200), (1, 50, 128), (3, 17, 300), (1, 3, 40), (2, 133, 260)])
-def test_conv2_fwd_tf32(ops, shape):
+def test_conv2_fwd_tf32(ops, shape, feed):
     B, H, W = shape
     g = torch.Generator(device=DEV).manual_seed(4)
     x = torch.randn(B, 16, H, W, device=DEV, generator=g)
@@ -95,7 +103,7 @@ def test_conv2_fwd_tf32(ops, shape):
 
 
 @pytest.mark.parametrize("shape", [(2, 24, 200), (1, 50, 128), (1, 2, 24), (2, 133, 260)])
-def test_conv2_dgrad_tf32(ops, shape):
+def test_conv2_dgrad_tf32(ops, shape, feed):
     B, H, W = shape
     g = torch.Generator(device=DEV).manual_seed(5)
     dy = torch.randn(B, 32, H, W, device=DEV, generator=g)
@@ -121,7 +129,7 @@ def test_conv2_wgrad_tf32(ops, shape):
     report(f"conv2_wgrad tf32 {shape}", rel(dw, ref), 1.5e-3)
 
 
-def test_conv2_tf32_long_items(ops, few_ctas):
+def test_conv2_tf32_long_items(ops, few_ctas, feed):
     """2 CTAs walk many long items: operand rings and the TMEM ring wrap and carry across items (fp32 slots are twice
     as large, so the ring geometry differs from the bf16 kernels')."""
     B, H, W = 3, 150, 300
@@ -232,7 +240,7 @@ def test_conv1_wgrad_f32(ops, shape, impl):
 
 
 @pytest.mark.parametrize("shape", [(2, 24, 200), (1, 50, 128)])
-def test_conv2_dgrad_fused_bn1_stats_tf32(ops, shape):
+def test_conv2_dgrad_fused_bn1_stats_tf32(ops, shape, feed):
     B, H, W = shape
     g = torch.Generator(device=DEV).manual_seed(22)
     x1 = nhwc(torch.randn(B, 16, 2 * H, 2 * W, device=DEV, generator=g) * 1.3 + 0.2)

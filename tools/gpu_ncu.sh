@@ -1,7 +1,7 @@
 #!/bin/bash
 # ncu capture of one kernel (plain run first, same command line, as the recipe requires)
 # usage: gpu_ncu.sh <kernel key of run_one_kernel.py> <kernel-name regex> [tc version] [launch skip] [precision]
-K=$1; REGEX=$2; VER=${3:-4}; SKIP=${4:-2}; PREC=${5:-bf16}
+K=$1; REGEX=$2; VER=${3:-5}; SKIP=${4:-2}; PREC=${5:-bf16}
 mkdir -p gpurun_out
 export B200DP_PRECISION=$PREC
 python tools/run_one_kernel.py $K $VER 3 > gpurun_out/plain_${K}_$PREC.log 2>&1 && \

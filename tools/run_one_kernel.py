@@ -11,7 +11,7 @@ from torch_distributed_sandbox_b200 import ops
 from torch_distributed_sandbox_b200.models.engine import FusedConvNet
 
 which = sys.argv[1]
-ver = int(sys.argv[2]) if len(sys.argv) > 2 else 4
+ver = int(sys.argv[2]) if len(sys.argv) > 2 else 5
 iters = int(sys.argv[3]) if len(sys.argv) > 3 else 3
 ops.conv_tc_set_version(ver)
 B = 5

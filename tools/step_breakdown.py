@@ -12,7 +12,7 @@ from torch_distributed_sandbox_b200.models.engine import FusedConvNet
 
 ap = argparse.ArgumentParser()
 ap.add_argument("--precision", default="bf16")
-ap.add_argument("--ver", type=int, default=4)
+ap.add_argument("--ver", type=int, default=5)
 ap.add_argument("--batch", type=int, default=5)
 ap.add_argument("--image", type=int, default=3000)
 a = ap.parse_args()

@@ -112,7 +112,8 @@ def fc_grid() -> int:
 
 def conv_tc_set_version(v: int) -> None:
     """tcgen05 conv variant (bf16 kernels): 1 = tap-stationary + TMA, 2 = row-stationary + TMA, 3 = row-stationary +
-    cp.async, 4 = 3 with the dx-replicated M=128 weight-gradient kernel (default)."""
+    cp.async, 4 = 3 with the dx-replicated M=128 weight-gradient kernel, 5 = 4 with forward / dgrad fed by one TMA
+    request per input row into swizzled pixel rows (default; fp32 kernels support 4 and 5)."""
     _native.check(_lib().b200_conv_tc_set_version(int(v)), "conv_tc_set_version")
 
 
