@@ -1228,9 +1228,14 @@ constexpr int kTmemCols = 256;
 constexpr int kSmemBytes = kSlotsA * kSlotA + kPhysB * kSlotB + 1024 + 1024;
 }  // namespace wt
 
+// TMAB: the dx2 row is one TMA request (tensor map {32 ch, W, H, B}, box {32, 64, 1, 1}, swizzle 128B with 32-byte
+// atoms = exactly the MN-major TF32 operand layout) instead of 512 cp.async pieces: the cp.async wavefronts in the L1
+// data pipe (one per 32-byte sector) were a third of this kernel's shared-memory traffic.  The act row keeps cp.async:
+// its rows pair two neighbouring pixels, and a tensor map cannot zero-fill on the SUM of two coordinates.
+template <bool TMAB>
 __global__ void __launch_bounds__(kThreads, 1)
-conv5x5_wgrad_tf32_kernel(const float* __restrict__ act, const float* __restrict__ dxo, float* __restrict__ partials,
-                          ConvGeom g) {
+conv5x5_wgrad_tf32_kernel(const __grid_constant__ CUtensorMap tm_dxo, const float* __restrict__ act,
+                          const float* __restrict__ dxo, float* __restrict__ partials, ConvGeom g) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);     // swizzle atoms: 1 KB aligned
   uint8_t* s_a = smem;
@@ -1246,9 +1251,10 @@ conv5x5_wgrad_tf32_kernel(const float* __restrict__ act, const float* __restrict
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < wt::kSlotsA; ++i) { mbar_init(&fullA[i], 32); mbar_init(&emptyA[i], 1); }
-    for (int i = 0; i < wt::kSlotsB; ++i) { mbar_init(&fullB[i], 32); mbar_init(&emptyB[i], 1); }
+    for (int i = 0; i < wt::kSlotsB; ++i) { mbar_init(&fullB[i], TMAB ? 1 : 32); mbar_init(&emptyB[i], 1); }
     mbar_init(done, 1);
     mbar_fence_init();
+    if (TMAB) tma_prefetch_desc(&tm_dxo);
   }
   if (warp == 1) tmem_alloc<wt::kTmemCols>(s_tmem);
   tc_fence_before();
@@ -1270,7 +1276,18 @@ conv5x5_wgrad_tf32_kernel(const float* __restrict__ act, const float* __restrict
       const int rows = min(g.rseg, g.H - r0);
       const int x0 = strip * wt::kSP;
       for (int i = 0; i < rows + 4; ++i) {
-        {
+        if constexpr (TMAB) {
+          const uint32_t slot = gb % wt::kSlotsB, use = gb / wt::kSlotsB;
+          if (lane == 0) {
+            mbar_wait(&emptyB[slot], (use & 1) ^ 1);
+            mbar_expect_tx(&fullB[slot], slot < 4 ? 2 * wt::kSlotB : wt::kSlotB);
+            tma_load_4d(s_b + slot * wt::kSlotB, &tm_dxo, &fullB[slot], 0, x0, r0 - 2 + i, b);
+            if (slot < 4)      // mirror of slots 0..3
+              tma_load_4d(s_b + (wt::kSlotsB + slot) * wt::kSlotB, &tm_dxo, &fullB[slot], 0, x0, r0 - 2 + i, b);
+          }
+          __syncwarp();
+          ++gb;
+        } else {
           const uint32_t slot = gb % wt::kSlotsB, use = gb / wt::kSlotsB;
           mbar_wait(&emptyB[slot], (use & 1) ^ 1);
           const int y = r0 - 2 + i;
@@ -1416,7 +1433,7 @@ int make_act_tmap(CUtensorMap* tm, const void* ptr, int B, int H, int W, int C, 
 
 // 4-D map over an NHWC activation of `eb`-byte elements: {C, W, H, B}; box {C, boxW, 1, 1}; the inner extent is one
 // whole pixel (32 / 64 / 128 bytes) and selects the matching shared-memory swizzle.
-int make_row_tmap(CUtensorMap* tm, const void* ptr, int B, int H, int W, int C, int eb, int boxW) {
+int make_row_tmap(CUtensorMap* tm, const void* ptr, int B, int H, int W, int C, int eb, int boxW, bool atom32 = false) {
   EncodeTiledFn enc = get_encode_fn();
   if (!enc) return b200_fail(-3, "cuTensorMapEncodeTiled entry point not available");
   const int rowb = C * eb;
@@ -1424,8 +1441,11 @@ int make_row_tmap(CUtensorMap* tm, const void* ptr, int B, int H, int W, int C, 
   cuuint64_t gstr[3] = {(cuuint64_t)rowb, (cuuint64_t)W * rowb, (cuuint64_t)H * W * rowb};
   cuuint32_t box[4] = {(cuuint32_t)C, (cuuint32_t)boxW, 1, 1};
   cuuint32_t estr[4] = {1, 1, 1, 1};
-  const CUtensorMapSwizzle swz = rowb == 128 ? CU_TENSOR_MAP_SWIZZLE_128B : rowb == 64 ? CU_TENSOR_MAP_SWIZZLE_64B
-                                                                                        : CU_TENSOR_MAP_SWIZZLE_32B;
+  // atom32: 128-byte rows whose 32-byte units are permuted (the MN-major TF32 operand layout, sw32_off in ptx.cuh)
+  const CUtensorMapSwizzle swz = atom32        ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B
+                                 : rowb == 128 ? CU_TENSOR_MAP_SWIZZLE_128B
+                                 : rowb == 64  ? CU_TENSOR_MAP_SWIZZLE_64B
+                                               : CU_TENSOR_MAP_SWIZZLE_32B;
   CUresult r = enc(tm, eb == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4,
                    const_cast<void*>(ptr), gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swz,
                    CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
@@ -1630,12 +1650,22 @@ B200_API int b200_conv2_dgrad_stats_tc_f32(const void* dx2, const void* w2, cons
 B200_API int b200_conv2_wgrad_tc_f32(const void* p1, const void* dx2, void* partials, void* dw2, int B, int H, int W,
                                      float gscale, void* stream) {
   cudaStream_t s = (cudaStream_t)stream;
-  B200_CUDA(set_max_smem(conv5x5_wgrad_tf32_kernel, wt::kSmemBytes));
   const int nsm = b200_compute_sms();
   ConvGeom g = make_geom_w(B, H, W, nsm, 4, wt::kSP);
   const int grid = g.nitems < nsm ? g.nitems : nsm;
-  conv5x5_wgrad_tf32_kernel<<<grid, kThreads, wt::kSmemBytes, s>>>((const float*)p1, (const float*)dx2,
-                                                                   (float*)partials, g);
+  CUtensorMap tm;
+  if (g_conv_tc_version >= 5) {
+    int rc = make_row_tmap(&tm, dx2, B, H, W, 32, 4, wt::kSP, /*atom32=*/true);
+    if (rc) return rc;
+    B200_CUDA(set_max_smem(conv5x5_wgrad_tf32_kernel<true>, wt::kSmemBytes));
+    conv5x5_wgrad_tf32_kernel<true><<<grid, kThreads, wt::kSmemBytes, s>>>(tm, (const float*)p1, (const float*)dx2,
+                                                                           (float*)partials, g);
+  } else {
+    memset(&tm, 0, sizeof(tm));
+    B200_CUDA(set_max_smem(conv5x5_wgrad_tf32_kernel<false>, wt::kSmemBytes));
+    conv5x5_wgrad_tf32_kernel<false><<<grid, kThreads, wt::kSmemBytes, s>>>(tm, (const float*)p1, (const float*)dx2,
+                                                                            (float*)partials, g);
+  }
   B200_LAUNCH_CHECK();
   return b200_reduce_partials(partials, grid, 32 * 16 * kTaps, dw2, gscale, stream);
 }

@@ -116,7 +116,7 @@ def test_conv2_dgrad_tf32(ops, shape, feed):
 
 
 @pytest.mark.parametrize("shape", [(2, 24, 200), (1, 50, 128), (3, 17, 300), (1, 2, 24), (2, 133, 260)])
-def test_conv2_wgrad_tf32(ops, shape):
+def test_conv2_wgrad_tf32(ops, shape, feed):
     B, H, W = shape
     g = torch.Generator(device=DEV).manual_seed(6)
     x = torch.randn(B, 16, H, W, device=DEV, generator=g)
