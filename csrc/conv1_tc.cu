@@ -20,7 +20,9 @@
 // what the FFMA version (2.5 ms, csrc/convnet_kernels.cu) could not get near.
 #include "common.h"
 #include "ptx.cuh"
+#include <cuda.h>
 #include <cstdint>
+#include <cstdlib>
 #include <mutex>
 
 namespace {
@@ -528,6 +530,227 @@ conv1_wgrad_tf32_kernel(const float* __restrict__ in, const float* __restrict__ 
   if (warp == 0) { __syncwarp(); tmem_dealloc<kTmemCols>(tmem_base); }
 }
 
+
+// ------------------------------------------------------------------------------------------------
+// Same kernel with every global load done by TMA (one elected thread, three requests per item) instead of
+// 7 cp.async per producer thread: in the cp.async version the L1 data pipe was ~80 % busy, 1400 of its ~3200
+// wavefronts per item being LDGSTS sectors.  Per item the loader warp fetches into a two-stage raw ring
+//   x1 tile   8 rows x 64 px x 16 ch fp32 = 32 KB  - map {32 floats = 2 pixels, W/2, H, B}, 128-byte swizzle: the eight
+//             windows a warp reads at once are eight consecutive 128-byte lines, the swizzle spreads their 16-byte
+//             pieces over all banks (4 wavefronts per LDS.128 = the minimum for 512 bytes);
+//   dp1 tile  4 x 32 pooled px x 16 ch = 8 KB     - map {16, W/2, H/2, B};
+//   input     12 rows x 72 px fp32                - map {W, H, B}; out-of-image rows / columns arrive as zeros.
+// Producers wait on the stage's mbarrier, so the per-item named barrier is gone too.
+namespace tt {
+constexpr int kXBytes = 8 * tf::kXW * 64;             // 32768
+constexpr int kGBytes = 4 * (tf::kXW / 2) * 64;       // 8192
+constexpr int kInW = 80;                              // input row x0-4 .. x0+75: the tile starts 16-byte aligned in global memory
+constexpr int kIBytes = kERows * kInW * 4;            // 3840
+constexpr int kRawStage = 45056;                      // 44 KB (1 KB multiple: the swizzled tile needs 1 KB alignment)
+constexpr int kRawStages = 2;
+constexpr int kThreads = 64 + tf::kProd;              // warp 0 MMA issue, warp 1 TMA loader, 16 producer warps
+constexpr int kSmemBytes = kStages * tf::kStageBytes + kRawStages * kRawStage + 1024 + 1024;
+static_assert(kXBytes + kGBytes + kIBytes <= kRawStage, "raw stage layout");
+}  // namespace tt
+
+__device__ __forceinline__ void tma_load_3d(void* smem_dst, const void* tmap, uint64_t* bar, int c0, int c1, int c2) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+      ::"r"(smem_u32(smem_dst)), "l"(tmap), "r"(c0), "r"(c1), "r"(c2), "r"(smem_u32(bar))
+      : "memory");
+}
+
+__global__ void __launch_bounds__(tt::kThreads, 1)
+conv1_wgrad_tf32_tma_kernel(const __grid_constant__ CUtensorMap tm_x1, const __grid_constant__ CUtensorMap tm_dp1,
+                            const __grid_constant__ CUtensorMap tm_in, const float* __restrict__ bn,
+                            const float* __restrict__ red, float* __restrict__ partials, WgGeom g) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  uint8_t* s_stage = smem;                                                          // [kStages][A | E]
+  uint8_t* s_rawb = smem + kStages * tf::kStageBytes;                               // [2][x1 | dp1 | in]
+  float4* s_const = reinterpret_cast<float4*>(s_rawb + tt::kRawStages * tt::kRawStage);   // [16] (sc, sh, ca, cb)
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_const + kC1);
+  uint64_t* full = bars;                       // [kStages]  producers -> MMA
+  uint64_t* empty = full + kStages;            // [kStages]  MMA -> producers
+  uint64_t* rfull = empty + kStages;           // [2]        TMA -> producers
+  uint64_t* rempty = rfull + tt::kRawStages;   // [2]        producers -> loader
+  uint64_t* done = rempty + tt::kRawStages;
+  uint32_t* s_tmem = reinterpret_cast<uint32_t*>(done + 1);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < kStages; ++i) { mbar_init(&full[i], tf::kProdWarps); mbar_init(&empty[i], 1); }
+    for (int i = 0; i < tt::kRawStages; ++i) { mbar_init(&rfull[i], 1); mbar_init(&rempty[i], tf::kProdWarps); }
+    mbar_init(done, 1);
+    mbar_fence_init();
+    tma_prefetch_desc(&tm_x1); tma_prefetch_desc(&tm_dp1); tma_prefetch_desc(&tm_in);
+  }
+  for (int c = threadIdx.x; c < kC1; c += tt::kThreads) {
+    const float s_ = bn[c], mu = bn[2 * kC1 + c], rs = bn[3 * kC1 + c];
+    const float mdy = red[c], mdyx = red[kC1 + c];
+    s_const[c] = make_float4(s_, bn[kC1 + c], s_ * (rs * mdyx * mu - mdy), -s_ * rs * mdyx);
+  }
+  if (warp == 0) tmem_alloc<kTmemCols>(s_tmem);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *s_tmem;
+
+  if (warp == 0) {
+    // ================= MMA issue =================
+    constexpr uint32_t idesc = umma_idesc(2, 128, kNCols, 1, 1);
+    const uint64_t tmpl = smem_desc(0, tf::kAtom, 512, 1);
+    const uint32_t hi = (uint32_t)(tmpl >> 32), lo0 = (uint32_t)tmpl;
+    uint32_t n = 0;
+    for (int item = blockIdx.x; item < g.nitems; item += gridDim.x, ++n) {
+      const uint32_t s = n % kStages;
+      mbar_wait(&full[s], (n / kStages) & 1);
+      tc_fence_after();
+      const uint32_t a_lo = lo0 + (smem_u32(s_stage + s * tf::kStageBytes) >> 4);
+      const uint32_t b_lo = a_lo + (tf::kABytes >> 4);
+      const uint32_t acc0 = n == 0 ? 0u : 1u;
+      if (elect_one()) {
+#pragma unroll
+        for (int kb = 0; kb < tf::kXW / 8; ++kb)
+          umma_tf32(tmem_base, ((uint64_t)hi << 32) | (uint64_t)(a_lo + kb * 64),
+                    ((uint64_t)hi << 32) | (uint64_t)(b_lo + kb * 64), idesc, kb == 0 ? acc0 : 1u);
+        umma_commit(&empty[s]);
+      }
+      __syncwarp();
+    }
+    if (elect_one()) umma_commit(done);
+    __syncwarp();
+  } else if (warp == 1) {
+    // ================= TMA loader =================
+    if (lane == 0) {
+      uint32_t n = 0;
+      for (int item = blockIdx.x; item < g.nitems; item += gridDim.x, ++n) {
+        const int strip = item % g.nstrips;
+        const int grp = (item / g.nstrips) % g.ngroups;
+        const int b = item / (g.nstrips * g.ngroups);
+        const int y0 = grp * kRows, x0 = strip * tf::kXW;
+        const uint32_t rs = n % tt::kRawStages;
+        mbar_wait(&rempty[rs], ((n / tt::kRawStages) & 1) ^ 1);
+        uint8_t* dst = s_rawb + rs * tt::kRawStage;
+        mbar_expect_tx(&rfull[rs], tt::kXBytes + tt::kGBytes + tt::kIBytes);
+        tma_load_4d(dst, &tm_x1, &rfull[rs], 0, x0 >> 1, y0, b);
+        tma_load_4d(dst + tt::kXBytes, &tm_dp1, &rfull[rs], 0, x0 >> 1, y0 >> 1, b);
+        tma_load_3d(dst + tt::kXBytes + tt::kGBytes, &tm_in, &rfull[rs], x0 - 4, y0 - 2, b);
+      }
+    }
+  } else {
+    // ================= producers: 512 threads, one 2x2 window x 4 channels each =================
+    const int pt = threadIdx.x - 64;                 // 0..511
+    const int q = pt & 3, w = pt >> 2;               // channels 4q..4q+3 of window w
+    const int wr = w >> 5, wc = w & 31;              // window row 0..3, window col 0..31
+    float4 kc[4];
+#pragma unroll
+    for (int cc = 0; cc < 4; ++cc) kc[cc] = s_const[q * 4 + cc];
+    constexpr int kInTot = kERows * tf::kInW;
+    const int stride = (int)gridDim.x;
+    // (strip, group) of the current item, advanced without divisions
+    int c_strip = (int)blockIdx.x % g.nstrips, c_grp = ((int)blockIdx.x / g.nstrips) % g.ngroups;
+    const int d_strip = stride % g.nstrips, d_grp = (stride / g.nstrips) % g.ngroups;
+    // byte offsets of this thread's pieces inside a raw stage (x1 tile: 128-byte swizzle, chunk ^= line index)
+    uint32_t xoff[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+      xoff[i] = (uint32_t)((2 * wr + (i >> 1)) * (tf::kXW * 64) + wc * 128 + ((((i & 1) * 4 + q) ^ (wc & 7)) << 4));
+    const uint32_t goff = (uint32_t)(tt::kXBytes + wr * (tf::kXW / 2) * 64 + wc * 64 + q * 16);
+    uint32_t n = 0;
+    for (int item = blockIdx.x; item < g.nitems; item += stride, ++n) {
+      const uint32_t s = n % kStages, rs = n % tt::kRawStages;
+      uint8_t* sA = s_stage + s * tf::kStageBytes;
+      uint8_t* sE = sA + tf::kABytes;
+      const uint8_t* raw = s_rawb + rs * tt::kRawStage;
+      const float* sI = reinterpret_cast<const float*>(raw + tt::kXBytes + tt::kGBytes);
+      const bool wvalid = (c_grp * kRows + 2 * wr) < g.H && (c_strip * tf::kXW + 2 * wc) < g.W;
+      c_strip += d_strip; c_grp += d_grp;
+      if (c_strip >= g.nstrips) { c_strip -= g.nstrips; ++c_grp; }
+      if (c_grp >= g.ngroups) c_grp -= g.ngroups;
+      mbar_wait(&rfull[rs], (n / tt::kRawStages) & 1);
+      float4 xr[4], gr;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) xr[i] = *reinterpret_cast<const float4*>(raw + xoff[i]);
+      gr = *reinterpret_cast<const float4*>(raw + goff);
+      mbar_wait(&empty[s], ((n / kStages) & 1) ^ 1);
+      {
+        float o[4][4];
+#pragma unroll
+        for (int cc = 0; cc < 4; ++cc) {
+          const float4 k = kc[cc];                                // (sc, sh, ca, cb)
+          const float xv[4] = {(&xr[0].x)[cc], (&xr[1].x)[cc], (&xr[2].x)[cc], (&xr[3].x)[cc]};
+          float best = fmaf(xv[0], k.x, k.y);
+          int am = 0;
+#pragma unroll
+          for (int i = 1; i < 4; ++i) {
+            const float y = fmaf(xv[i], k.x, k.y);
+            if (y > best) { best = y; am = i; }
+          }
+          const float gq = best > 0.f ? (&gr.x)[cc] * k.x : 0.f;  // ReLU mask, dy * scale, routed to the arg-max
+#pragma unroll
+          for (int i = 0; i < 4; ++i) o[i][cc] = fmaf(k.w, xv[i], k.z);
+#pragma unroll
+          for (int i = 0; i < 4; ++i)
+            if (am == i) o[i][cc] += gq;
+        }
+        if (!wvalid) {
+#pragma unroll
+          for (int i = 0; i < 4; ++i)
+#pragma unroll
+            for (int cc = 0; cc < 4; ++cc) o[i][cc] = 0.f;
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int kx = 2 * wc + (i & 1);                        // image row r = 2*wr + (i >> 1): atom wr
+          *reinterpret_cast<float4*>(sA + wr * tf::kAtom + sw32_off(kx, 2 * (i >> 1) + (q >> 1)) + 16 * (q & 1)) =
+              make_float4(o[i][0], o[i][1], o[i][2], o[i][3]);
+        }
+      }
+      // expanded input E[r'][k][dxs]: 12 rows x 64 pixels x 2 pieces of 16 B, 3 per thread
+#pragma unroll
+      for (int j = 0; j < (2 * kERows * tf::kXW) / tf::kProd; ++j) {
+        const int idx = pt + j * tf::kProd;
+        const int kx = idx & (tf::kXW - 1), c2 = idx >> 6, rr = c2 >> 1;
+        const float* src = sI + rr * tt::kInW + kx + 2 + 4 * (c2 & 1);      // in[.., x0 + kx - 2 + dxs]
+        *reinterpret_cast<float4*>(sE + (rr >> 2) * tf::kAtom + sw32_off(kx, rr & 3) + 16 * (c2 & 1)) =
+            make_float4(src[0], src[1], src[2], src[3]);
+      }
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) { mbar_arrive(&rempty[rs]); mbar_arrive(&full[s]); }
+      (void)kInTot;
+    }
+  }
+  // extraction: identical (m, n) meaning to the bf16 kernel
+  float* s_T = reinterpret_cast<float*>(s_stage);
+  constexpr int kTP = kNCols + 1;
+  if (warp >= 2 && warp <= 5) {
+    mbar_wait(done, 0);
+    tc_fence_after();
+    const int qq = warp & 3, m = qq * 32 + lane;
+#pragma unroll 1
+    for (int c0 = 0; c0 < kNCols; c0 += 16) {
+      uint32_t v[16];
+      tmem_ld16(tmem_base + ((uint32_t)(qq * 32) << 16) + c0, v);
+      tmem_ld_wait();
+#pragma unroll
+      for (int j = 0; j < 16; ++j) s_T[m * kTP + c0 + j] = __uint_as_float(v[j]);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  for (int t = threadIdx.x; t < kC1 * 25; t += tt::kThreads) {
+    const int c = t / 25, tap = t % 25, dy = tap / 5, dxs = tap % 5;
+    float a = 0.f;
+#pragma unroll
+    for (int r = 0; r < kRows; ++r) a += s_T[(16 * r + c) * kTP + (r + dy) * 8 + dxs];
+    partials[(size_t)blockIdx.x * 400 + t] = a;
+  }
+  if (warp == 0) { __syncwarp(); tmem_dealloc<kTmemCols>(tmem_base); }
+}
+
 }  // namespace
 
 // Same contract as b200_conv1_wgrad (partials: [b200_conv1_wgrad_grid()][400] scratch).
@@ -551,11 +774,77 @@ B200_API int b200_conv1_wgrad_tc(const void* in_f32, const void* x1, const void*
 }
 
 // fp32 storage, kind::tf32 (same contract; x1 and dp1 are fp32).
+namespace {
+typedef CUresult (*EncodeTiledFn1)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn1 encode_fn1() {
+  static EncodeTiledFn1 fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = (EncodeTiledFn1)p;
+  });
+  return fn;
+}
+// fp32 tensor map: dims / strides (bytes, for dims 1..n-1) / box, innermost first
+int f32_map(CUtensorMap* tm, const void* ptr, int nd, const cuuint64_t* dims, const cuuint64_t* strides,
+            const cuuint32_t* box, CUtensorMapSwizzle swz) {
+  EncodeTiledFn1 enc = encode_fn1();
+  if (!enc) return b200_fail(-3, "cuTensorMapEncodeTiled entry point not available");
+  cuuint32_t estr[5] = {1, 1, 1, 1, 1};
+  CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, (cuuint32_t)nd, const_cast<void*>(ptr), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, swz, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return b200_fail((int)r, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+  return 0;
+}
+}  // namespace
+
 B200_API int b200_conv1_wgrad_tc_f32(const void* in_f32, const void* x1, const void* dp1, const void* bn,
                                      const void* red, void* partials, void* dw1, int B, int H, int W, float gscale,
                                      void* stream) {
   B200_CHECK(H % 2 == 0 && W % 2 == 0, "conv1_wgrad_tc_f32: H and W must be even");
   cudaStream_t s = (cudaStream_t)stream;
+  static const bool use_tma = [] { const char* e = getenv("B200DP_CONV1_WGRAD_FEED"); return !(e && e[0] == 'c'); }();
+  if (use_tma && W % 4 == 0) {      // TMA needs 16-byte row strides (W * 4 bytes for the input image)
+    WgGeom g;
+    g.B = B; g.H = H; g.W = W;
+    g.nstrips = (W + tf::kXW - 1) / tf::kXW;
+    g.ngroups = (H + kRows - 1) / kRows;
+    g.nitems = B * g.nstrips * g.ngroups;
+    const int nsm = b200_compute_sms();
+    const int grid = g.nitems < nsm ? g.nitems : nsm;
+    CUtensorMap tx, tg, ti;
+    {
+      cuuint64_t d[4] = {32, (cuuint64_t)W / 2, (cuuint64_t)H, (cuuint64_t)B};
+      cuuint64_t st[3] = {128, (cuuint64_t)W * 64, (cuuint64_t)H * W * 64};
+      cuuint32_t bx[4] = {32, tf::kXW / 2, kRows, 1};
+      int rc = f32_map(&tx, x1, 4, d, st, bx, CU_TENSOR_MAP_SWIZZLE_128B);
+      if (rc) return rc;
+    }
+    {
+      cuuint64_t d[4] = {16, (cuuint64_t)W / 2, (cuuint64_t)H / 2, (cuuint64_t)B};
+      cuuint64_t st[3] = {64, (cuuint64_t)(W / 2) * 64, (cuuint64_t)(H / 2) * (W / 2) * 64};
+      cuuint32_t bx[4] = {16, tf::kXW / 2, kRows / 2, 1};
+      int rc = f32_map(&tg, dp1, 4, d, st, bx, CU_TENSOR_MAP_SWIZZLE_NONE);
+      if (rc) return rc;
+    }
+    {
+      cuuint64_t d[3] = {(cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)B};
+      cuuint64_t st[2] = {(cuuint64_t)W * 4, (cuuint64_t)H * W * 4};
+      cuuint32_t bx[3] = {tt::kInW, kERows, 1};
+      int rc = f32_map(&ti, in_f32, 3, d, st, bx, CU_TENSOR_MAP_SWIZZLE_NONE);
+      if (rc) return rc;
+    }
+    B200_CUDA(set_max_smem(conv1_wgrad_tf32_tma_kernel, tt::kSmemBytes));
+    conv1_wgrad_tf32_tma_kernel<<<grid, tt::kThreads, tt::kSmemBytes, s>>>(tx, tg, ti, (const float*)bn, (const float*)red,
+                                                                           (float*)partials, g);
+    B200_LAUNCH_CHECK();
+    return b200_reduce_partials(partials, grid, 400, dw1, gscale, stream);
+  }
   B200_CUDA(set_max_smem(conv1_wgrad_tf32_kernel, tf::kSmemBytes));
   WgGeom g;
   g.B = B; g.H = H; g.W = W;
