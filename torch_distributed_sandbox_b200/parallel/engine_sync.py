@@ -50,6 +50,11 @@ class EngineGradSync:
         self.tile_sweeps = int(os.environ.get("B200DP_TILE_SWEEPS", "2"))      # fc_bwd grid sweeps per slab (~48 MB of dW)
         self.tile_ready = None
         self._tile_steps = 0
+        # "onepass": run the whole-bucket exchange with the one-pass kernel of the tile pipeline (reduce + 1/N + SGD +
+        # weight push in a single sweep, no reduce-scatter / all-gather split) instead of the two-shot kernel;
+        # with B200DP_AR_START=pool|fc its slab counters are simply not waited for (target 0).
+        self.onepass = os.environ.get("B200DP_AR_KERNEL", "twoshot") == "onepass"
+        self._onepass_ready = None
         self._debug_skip_fc = os.environ.get("B200DP_DEBUG_SKIP_FC_ALLREDUCE", "0") == "1"   # timing experiments only
         be = self.backend
         if self.world > 1 and getattr(be, "name", "") != "native":
@@ -66,12 +71,14 @@ class EngineGradSync:
                 engine.rebind_storage(fcw=wsym, fcw_grad=grad, bn_flat=bn, small_grad=sg)
                 if self.ar_start == "tile" and self.fuse_sgd and engine.B <= 8:
                     self.tile_ready = be.alloc_symmetric(256, torch.int32, multicast=False)     # slab counters
+                elif self.onepass and self.fuse_sgd:
+                    self._onepass_ready = be.alloc_symmetric(256, torch.int32, multicast=False)  # stays zero
             self.comm_stream = be.comm_stream
             if self.reserved_sms > 0 and be.multicast and (self.algo in (None, "nvls", "nvls_excl")):
                 from .. import _native
                 _native.check(_native.cuda().b200_set_reserved_sms(self.reserved_sms), "set_reserved_sms")
                 self.algo, self.blocks = "nvls_excl", self.reserved_sms
-            elif self.reserved_sms > 0 and self.tile_ready is not None:
+            elif self.reserved_sms > 0 and (self.tile_ready is not None or self._onepass_ready is not None):
                 from .. import _native                     # the tile kernel's CTAs also own their SMs (P2P loads)
                 _native.check(_native.cuda().b200_set_reserved_sms(self.reserved_sms), "set_reserved_sms")
         if self.tile_ready is not None:
@@ -106,7 +113,10 @@ class EngineGradSync:
         algo = self.algo or ("nvls" if mc else "p2p")
         if self.tile_ready is not None:
             algo = ("nvls" if mc and self.algo != "p2p" else "p2p") + f"-tiles({self.tile_sweeps} sweeps/slab, starts with fc_bwd)"
-        d.update({"fc_bucket_algo": (f"one-pass-{algo}" if self.tile_ready is not None else f"two-shot-{algo}"),
+        elif self._onepass_ready is not None:
+            algo = ("nvls" if mc and self.algo not in ("p2p",) else "p2p") + f"(starts after {self.ar_start})"
+        d.update({"fc_bucket_algo": (f"one-pass-{algo}" if (self.tile_ready is not None or self._onepass_ready is not None)
+                                     else f"two-shot-{algo}"),
                   "fused_sgd_in_allreduce": self.fuse_sgd,
                   "sm_partition": self.reserved_sms if algo == "nvls_excl" else 0,
                   "small_bucket_algo": "one-shot", "comm_blocks": self.blocks, "nccl_calls_on_grad_path": 0})
@@ -134,6 +144,18 @@ class EngineGradSync:
         main = torch.cuda.current_stream()
         ready = torch.cuda.Event()
         ready.record(main)
+        if self._onepass_ready is not None:
+            from .. import ops
+            with torch.cuda.stream(self.comm_stream), trace.nvtx_range("b200dp.allreduce.fc_bucket(onepass)"):
+                self.comm_stream.wait_event(ready)
+                self.backend.all_reduce_tiles(engine.fcw_grad, engine.fcw, self._onepass_ready, rows=10,
+                                              slab_floats=ops.fc_bwd_tile_slab_floats(8), target=0,
+                                              scale=1.0 / self.world, lr=engine.lr, channel=1,
+                                              blocks=max(1, self.reserved_sms or 8),
+                                              use_nvls=None if self.algo in (None, "nvls", "nvls_excl") else False)
+                self._fc_event = torch.cuda.Event()
+                self._fc_event.record(self.comm_stream)
+            return
         with torch.cuda.stream(self.comm_stream), trace.nvtx_range("b200dp.allreduce.fc_bucket"):
             self.comm_stream.wait_event(ready)
             self.backend.all_reduce(engine.fcw_grad, dist.ReduceOp.SUM, channel=1, scale=1.0 / self.world,
