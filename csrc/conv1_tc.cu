@@ -905,10 +905,12 @@ struct FwGeom {
   int nys, nxs, nitems;
 };
 
-template <typename OT>       // OT = storage type of the output: __nv_bfloat16 or float
+// OT = storage type of the output: __nv_bfloat16 or float; POOL (float only) = second pass of the two-pass forward
+template <typename OT, bool POOL = false>
 __global__ void __launch_bounds__(kFwThreads, 1)
 conv1_fwd_tc_kernel(const float* __restrict__ in, const float* __restrict__ w1, const float* __restrict__ b1,
-                    OT* __restrict__ x1, float* __restrict__ partials, FwGeom g) {
+                    OT* __restrict__ x1, float* __restrict__ partials, FwGeom g,
+                    const float* __restrict__ bn = nullptr, float* __restrict__ pooled = nullptr) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((128u - (smem_u32(smem_raw) & 127u)) & 127u);
   uint8_t* s_x = smem;                                   // [kFwStages][hi | lo][row planes][columns][16 B]
@@ -922,7 +924,9 @@ conv1_fwd_tc_kernel(const float* __restrict__ in, const float* __restrict__ w1, 
   uint32_t* s_tmem = reinterpret_cast<uint32_t*>(tempty + kFwTStages);
   float* s_bias = reinterpret_cast<float*>(s_tmem + 4);  // [16]
   float* s_stat = s_bias + 16;                            // [8 warps][32]
+  float* s_bn = s_stat + 8 * 32;                          // [scale 16 | shift 16] (fused BN+ReLU+pool epilogue)
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (POOL && threadIdx.x < 32) s_bn[threadIdx.x] = bn[threadIdx.x];
 
   // Toeplitz weight tiles (hi / lo)
   for (int i = threadIdx.x; i < 5 * 2 * 128 * 8; i += kFwThreads) {
@@ -1084,14 +1088,32 @@ conv1_fwd_tc_kernel(const float* __restrict__ in, const float* __restrict__ w1, 
             for (int e = 0; e < 32; ++e) {
               const float f0 = __uint_as_float(v[e]) + bias[e & 15];
               v[e] = __float_as_uint(f0);
-              if (ok) { ssum[e & 15] += f0; ssq[e & 15] = fmaf(f0, f0, ssq[e & 15]); }
+              if (!POOL && ok) { ssum[e & 15] += f0; ssq[e & 15] = fmaf(f0, f0, ssq[e & 15]); }
             }
-            if (ok) {
+            if (ok && x1 != nullptr) {        // x1 == nullptr: statistics-only pass
               float* o = reinterpret_cast<float*>(ocol) + (size_t)(c0 >> 4) * g.W * 16;
               st_global_v8(o, &v[0]);
               st_global_v8(o + 8, &v[8]);
               st_global_v8(o + (size_t)g.W * 16, &v[16]);
               st_global_v8(o + (size_t)g.W * 16 + 8, &v[24]);
+            }
+            if constexpr (POOL) {
+              // second pass of the two-pass forward: the batch statistics are known (first pass), so BN + ReLU + the
+              // 2x2 max-pool run here and the separate pass over the 2.88 GB conv output (K5) disappears.  The two
+              // rows of a window are this chunk's two rows, the two columns are this lane and its neighbour.
+              uint32_t pm[16];
+#pragma unroll
+              for (int c = 0; c < 16; ++c) {
+                const float sc = s_bn[c], sh = s_bn[16 + c];
+                float m = fmaxf(fmaxf(0.f, fmaf(__uint_as_float(v[c]), sc, sh)), fmaf(__uint_as_float(v[16 + c]), sc, sh));
+                m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 1));
+                pm[c] = __float_as_uint(m);
+              }
+              if (ok && !(lane & 1)) {
+                float* po = pooled + (((size_t)b * (g.H >> 1) + ((yb + (c0 >> 4)) >> 1)) * (g.W >> 1) + (x >> 1)) * 16;
+                st_global_v8(po, &pm[0]);
+                st_global_v8(po + 8, &pm[8]);
+              }
             }
             if (k < 3) tmem_ld_wait();
             else { tc_fence_before(); mbar_arrive(&tempty[ts]); }
@@ -1143,9 +1165,29 @@ conv1_fwd_tc_kernel(const float* __restrict__ in, const float* __restrict__ w1, 
 // Same contract as b200_conv1_fwd; partials must hold [b200_sm_count()][32]; *nparts_out = rows written.
 template <typename OT>
 static int conv1_fwd_tc_t(const void* in_f32, const void* w1, const void* b1, void* x1, void* partials, int B,
-                          int H, int W, int* nparts_out, void* stream) {
+                          int H, int W, int* nparts_out, void* stream, const void* bn = nullptr, void* pooled = nullptr) {
   B200_CHECK(H % 2 == 0 && W % 2 == 0, "conv1_fwd_tc: H and W must be even");
   cudaStream_t s = (cudaStream_t)stream;
+  if (pooled != nullptr) {
+    if constexpr (sizeof(OT) == 4) {
+      B200_CUDA(set_max_smem(conv1_fwd_tc_kernel<OT, true>, kFwSmemBytes));
+      FwGeom gp;
+      gp.B = B; gp.H = H; gp.W = W;
+      gp.nys = (H + kFwSegRows - 1) / kFwSegRows;
+      gp.nxs = (W + kFwCols - 1) / kFwCols;
+      gp.nitems = B * gp.nys * gp.nxs;
+      const int nsmp = b200_compute_sms();
+      const int gridp = gp.nitems < nsmp ? gp.nitems : nsmp;
+      conv1_fwd_tc_kernel<OT, true><<<gridp, kFwThreads, kFwSmemBytes, s>>>((const float*)in_f32, (const float*)w1,
+                                                                            (const float*)b1, (OT*)x1, (float*)partials,
+                                                                            gp, (const float*)bn, (float*)pooled);
+      B200_LAUNCH_CHECK();
+      if (nparts_out) *nparts_out = gridp;
+      return 0;
+    } else {
+      return b200_fail(-2, "conv1_fwd_pool: fp32 storage only");
+    }
+  }
   B200_CUDA(set_max_smem(conv1_fwd_tc_kernel<OT>, kFwSmemBytes));
   FwGeom g;
   g.B = B; g.H = H; g.W = W;
@@ -1155,7 +1197,8 @@ static int conv1_fwd_tc_t(const void* in_f32, const void* w1, const void* b1, vo
   const int nsm = b200_compute_sms();
   const int grid = g.nitems < nsm ? g.nitems : nsm;
   conv1_fwd_tc_kernel<OT><<<grid, kFwThreads, kFwSmemBytes, s>>>((const float*)in_f32, (const float*)w1,
-                                                                 (const float*)b1, (OT*)x1, (float*)partials, g);
+                                                                 (const float*)b1, (OT*)x1, (float*)partials, g,
+                                                                 (const float*)bn, (float*)pooled);
   B200_LAUNCH_CHECK();
   if (nparts_out) *nparts_out = grid;
   return 0;
@@ -1168,4 +1211,20 @@ B200_API int b200_conv1_fwd_tc(const void* in_f32, const void* w1, const void* b
 B200_API int b200_conv1_fwd_tc_f32(const void* in_f32, const void* w1, const void* b1, void* x1_f32, void* partials,
                                    int B, int H, int W, int* nparts_out, void* stream) {
   return conv1_fwd_tc_t<float>(in_f32, w1, b1, x1_f32, partials, B, H, W, nparts_out, stream);
+}
+
+// Two-pass fp32 forward of layer 1 (the conv is cheap on the tensor cores, its 2.88 GB output is not):
+//   b200_conv1_stats_tc_f32      pass 1 - batch statistics only, nothing stored (0.24 ms at batch 5);
+//   b200_conv1_fwd_pool_tc_f32   pass 2 - recomputes the conv, stores it (the backward needs it) and applies
+//                                BN (bn = [scale | shift | ...]) + ReLU + 2x2 max-pool in the epilogue -> p1.
+// Both passes produce bit-identical conv values (same MMAs in the same order), so the statistics of pass 1 are those
+// of the tensor pass 2 stores.
+B200_API int b200_conv1_stats_tc_f32(const void* in_f32, const void* w1, const void* b1, void* partials, int B, int H,
+                                     int W, int* nparts_out, void* stream) {
+  return conv1_fwd_tc_t<float>(in_f32, w1, b1, nullptr, partials, B, H, W, nparts_out, stream);
+}
+B200_API int b200_conv1_fwd_pool_tc_f32(const void* in_f32, const void* w1, const void* b1, const void* bn, void* x1_f32,
+                                        void* p1_f32, void* partials, int B, int H, int W, void* stream) {
+  B200_CHECK(bn != nullptr && p1_f32 != nullptr && x1_f32 != nullptr, "conv1_fwd_pool: bn, x1 and p1 are required");
+  return conv1_fwd_tc_t<float>(in_f32, w1, b1, x1_f32, partials, B, H, W, nullptr, stream, bn, p1_f32);
 }

@@ -269,3 +269,30 @@ def test_conv2_dgrad_fused_bn1_stats_tf32(ops, shape, feed):
     ops.bn_bwd_finalize(part2, grid, 16, B * 4 * H * W, red_r, dg_r, db_r)
     report(f"fused bn1 bwd f32 dbeta {shape}", rel(db_f, db_r), 1e-5)
     report(f"fused bn1 bwd f32 dgamma {shape}", rel(dg_f, dg_r), 1e-3)
+
+
+@pytest.mark.parametrize("shape", [(2, 64, 96), (1, 36, 200), (3, 128, 132), (2, 4, 8)])
+def test_conv1_two_pass_equals_conv_then_pool(ops, shape):
+    """Statistics-only pass + conv/BN/ReLU/pool pass == conv1_fwd_tc followed by bn_relu_pool, bit for bit."""
+    B, H, W = shape
+    g = torch.Generator(device=DEV).manual_seed(41)
+    x = torch.rand(B, H, W, device=DEV, generator=g)
+    w = torch.randn(16, 1, 5, 5, device=DEV, generator=g) * 0.2
+    b = torch.randn(16, device=DEV, generator=g) * 0.1
+    bn = torch.zeros(4, 16, device=DEV)
+    bn[0] = torch.randn(16, device=DEV, generator=g)          # scale, both signs
+    bn[1] = torch.randn(16, device=DEV, generator=g) * 0.3
+    x1a = torch.empty(B, H, W, 16, device=DEV)
+    pa = torch.zeros(ops.conv1_fwd_grid(), 32, device=DEV)
+    na = ops.conv1_fwd_tc(x, w, b, x1a, pa)
+    p1a = torch.empty(B, H // 2, W // 2, 16, device=DEV)
+    ops.bn_relu_pool(x1a, bn, p1a)
+    pb = torch.zeros(ops.conv1_fwd_grid(), 32, device=DEV)
+    nb = ops.conv1_stats_tc(x, w, b, pb)
+    assert na == nb and torch.equal(pa[:na], pb[:nb])
+    x1b = torch.full((B, H, W, 16), float("nan"), device=DEV)
+    p1b = torch.full((B, H // 2, W // 2, 16), float("nan"), device=DEV)
+    ops.conv1_fwd_pool_tc(x, w, b, bn, x1b, p1b, torch.zeros(ops.conv1_fwd_grid(), 32, device=DEV))
+    torch.cuda.synchronize()
+    assert torch.equal(x1a, x1b)
+    assert torch.equal(p1a, p1b), float((p1a - p1b).abs().max())

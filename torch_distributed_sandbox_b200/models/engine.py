@@ -98,6 +98,7 @@ class FusedConvNet:
         # BN-backward reductions fused into fc_bwd / the conv2-dgrad epilogue (0: separate passes over x2 / x1)
         self.fuse_bwd_stats = os.environ.get("B200DP_FUSE_BWD_STATS", "1") == "1"
         self.fuse_fc_sgd = bool(fuse_fc_sgd)
+        self.conv1_two_pass = os.environ.get("B200DP_CONV1_TWO_PASS", "1") == "1"    # tf32 mode only
         self.F = rn.feature_size((H, W))
         self.comm = None           # set by parallel.ddp for data-parallel runs
         self._b = int(batch_size)  # size of the batch currently in the buffers (<= B: short last batch)
@@ -142,6 +143,7 @@ class FusedConvNet:
             self.g_c1, self.g_wg1 = ops.conv1_fwd_grid(), ops.conv1_wgrad_grid()
             self.g_tc, self.g_pbb, self.g_fc = ops.conv_tc_max_grid(), ops.pool_bn_bwd_grid(), ops.fc_grid()
             self.part_c1 = torch.empty(self.g_c1, 32, **f32)
+            self.part_c1b = torch.empty(self.g_c1, 32, **f32)       # scratch of the second conv1 pass (unused sums)
             self.part_c2 = torch.empty(self.g_tc, 64, **f32)
             self.part_bwd = torch.empty(self.g_pbb, 64, **f32)
             self.part_wg1 = torch.empty(self.g_wg1, 400, **f32)
@@ -297,14 +299,22 @@ class FusedConvNet:
         # mnist_onegpu.py:55-59) runs on leading-dimension views of the same buffers
         P, B, H, W = self.params, self._b, self.H, self.W
         x, x1, p1, x2, p2t = self.x[:B], self.x1[:B], self.p1[:B], self.x2[:B], self.p2[:B]
-        if self.conv1_backend == "tc" or self.precision == "tf32":
+        two_pass = self.precision == "tf32" and self.conv1_two_pass
+        if two_pass:
+            # fp32 storage: conv1 is cheap on the tensor cores (0.24 ms without its store), its 2.88 GB output is not -
+            # a statistics-only pass, then conv + store + BN/ReLU/pool in one epilogue instead of a pass over x1
+            n1 = ops.conv1_stats_tc(x, P["layer1.0.weight"], P["layer1.0.bias"], self.part_c1)
+        elif self.conv1_backend == "tc" or self.precision == "tf32":
             n1 = ops.conv1_fwd_tc(x, P["layer1.0.weight"], P["layer1.0.bias"], x1, self.part_c1)
         else:
             ops.conv1_fwd(x, P["layer1.0.weight"], P["layer1.0.bias"], x1, self.part_c1)
             n1 = self.g_c1
         ops.bn_finalize(self.part_c1, n1, 16, B * H * W, P["layer1.1.weight"], P["layer1.1.bias"],
                         self.bn_buf[1]["mean"], self.bn_buf[1]["var"], self.bn_buf[1]["nbt"], self.bn1)
-        ops.bn_relu_pool(x1, self.bn1, p1)
+        if two_pass:
+            ops.conv1_fwd_pool_tc(x, P["layer1.0.weight"], P["layer1.0.bias"], self.bn1, x1, p1, self.part_c1b)
+        else:
+            ops.bn_relu_pool(x1, self.bn1, p1)
         if self.conv_backend == "tc":
             nparts = ops.conv2_fwd_tc(p1, P["layer2.0.weight"], P["layer2.0.bias"], x2, self.part_c2)
         else:

@@ -150,6 +150,33 @@ def conv1_fwd_tc(x_f32, w1, b1, x1_bf16, partials) -> int:
     return n.value
 
 
+def conv1_stats_tc(x_f32, w1, b1, partials) -> int:
+    """First pass of the two-pass fp32 layer-1 forward: BatchNorm batch statistics of conv1's output, nothing stored.
+    Returns the number of partial rows."""
+    B, H, W = x_f32.shape
+    n = c_int(0)
+    lib = _lib()
+    lib.b200_conv1_stats_tc_f32.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int,
+                                            ctypes.POINTER(c_int), c_void_p]
+    _native.check(lib.b200_conv1_stats_tc_f32(_p(x_f32), _p(w1), _p(b1), _p(partials), B, H, W, ctypes.byref(n), _stream()),
+                  "conv1_stats_tc")
+    _count(1)
+    return n.value
+
+
+def conv1_fwd_pool_tc(x_f32, w1, b1, bn, x1_f32, p1_f32, partials):
+    """Second pass: conv1 again (bit-identical values), stored to ``x1_f32`` for the backward, with BN-apply + ReLU +
+    2x2 max-pool fused into the epilogue -> ``p1_f32``; replaces conv1_fwd_tc + bn_relu_pool (K3 + K5)."""
+    B, H, W = x_f32.shape
+    assert x1_f32.dtype == torch.float32 and p1_f32.dtype == torch.float32
+    lib = _lib()
+    lib.b200_conv1_fwd_pool_tc_f32.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                               c_int, c_int, c_int, c_void_p]
+    _native.check(lib.b200_conv1_fwd_pool_tc_f32(_p(x_f32), _p(w1), _p(b1), _p(bn), _p(x1_f32), _p(p1_f32), _p(partials),
+                                                 B, H, W, _stream()), "conv1_fwd_pool_tc")
+    _count(1)
+
+
 def bn_finalize(partials, nparts, C, count, gamma, beta, running_mean, running_var, nbt, out, momentum=0.1,
                 eps=1e-5):
     """K4: batch stats -> [scale|shift|mean|rstd] + running-stat update."""
