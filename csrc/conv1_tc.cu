@@ -751,6 +751,237 @@ conv1_wgrad_tf32_tma_kernel(const __grid_constant__ CUtensorMap tm_x1, const __g
   if (warp == 0) { __syncwarp(); tmem_dealloc<kTmemCols>(tmem_base); }
 }
 
+
+// ------------------------------------------------------------------------------------------------
+// Layer-1 weight gradient WITHOUT the conv1 output.  g = ca + cb*x1 + routed, so
+//   dW1[c][tap] = sum_p routed[p,c] * in[p+tap]                      (tensor cores, as above: D1 = A x E)
+//               + ca_c * S[tap] + cb_c * R[c][tap],   S[tap] = sum_p in[p+tap],   R[c][tap] = sum_p x1[p,c] * in[p+tap]
+// and since x1 = b + sum_tap' w[tap'] * in[p+tap'],   R[c][tap] = b_c * S[tap] + sum_tap' w[c][tap'] * M[tap'][tap]
+// with the 25 x 25 Gram matrix M[tap'][tap] = sum_p in[p+tap'] * in[p+tap] of the zero-padded input.  M and S come out
+// of ONE more MMA per K-step on the operand that is already in shared memory: D2 = E4 x E, where E4 is E plus a row of
+// ones.  So the kernel reads dp1 (0.72 GB), the forward's arg-max/ReLU bytes (0.18 GB) and the input (0.18 GB) instead
+// of x1 (2.88 GB), the producers only route (mask byte -> one non-zero of four), and the forward never stores x1.
+// Needs H % 8 == 0 (a partial row group would put products of real input rows with no output pixel into M; partial
+// strips are handled by zeroing the out-of-image columns of E).  Per-CTA partial row: [400 routed | 625 M | 25 S].
+namespace tn {
+constexpr int kEBytes = 4 * tf::kAtom;                // E4: three atoms of E + the "ones" atom (32 KB)
+constexpr int kStageBytes = tf::kABytes + kEBytes;    // 64 KB
+constexpr int kGBytes = 4 * (tf::kXW / 2) * 64;       // dp1 tile   8192
+constexpr int kMBytes = 4 * (tf::kXW / 2) * 16;       // mask tile  2048
+constexpr int kIBytes = kERows * tt::kInW * 4;        // input rows 3840
+constexpr int kRawStage = 14336;
+constexpr int kRawStages = 3;
+constexpr int kThreads = 64 + tf::kProd;
+constexpr int kPartial = 400 + 625 + 25;
+constexpr int kSmemBytes = kStages * kStageBytes + kRawStages * kRawStage + 1024 + 1024;
+static_assert(kGBytes + kMBytes + kIBytes <= kRawStage, "raw stage layout");
+}  // namespace tn
+
+__global__ void __launch_bounds__(tn::kThreads, 1)
+conv1_wgrad_nox1_tf32_kernel(const __grid_constant__ CUtensorMap tm_dp1, const __grid_constant__ CUtensorMap tm_mask,
+                             const __grid_constant__ CUtensorMap tm_in, const float* __restrict__ bn,
+                             float* __restrict__ partials, WgGeom g) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  uint8_t* s_stage = smem;                                                          // [kStages][A | E4]
+  uint8_t* s_rawb = smem + kStages * tn::kStageBytes;                               // [3][dp1 | mask | in]
+  float* s_sc = reinterpret_cast<float*>(s_rawb + tn::kRawStages * tn::kRawStage);  // [16] BN scale
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_sc + kC1);
+  uint64_t* full = bars;
+  uint64_t* empty = full + kStages;
+  uint64_t* rfull = empty + kStages;
+  uint64_t* rempty = rfull + tn::kRawStages;
+  uint64_t* done = rempty + tn::kRawStages;
+  uint32_t* s_tmem = reinterpret_cast<uint32_t*>(done + 1);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < kStages; ++i) { mbar_init(&full[i], tf::kProdWarps); mbar_init(&empty[i], 1); }
+    for (int i = 0; i < tn::kRawStages; ++i) { mbar_init(&rfull[i], 1); mbar_init(&rempty[i], tf::kProdWarps); }
+    mbar_init(done, 1);
+    mbar_fence_init();
+    tma_prefetch_desc(&tm_dp1); tma_prefetch_desc(&tm_mask); tma_prefetch_desc(&tm_in);
+  }
+  if (threadIdx.x < kC1) s_sc[threadIdx.x] = bn[threadIdx.x];
+  // the "ones" atom of both stages: element 0 of unit 0 of every pixel row is 1, the rest 0 (written once)
+  for (int i = threadIdx.x; i < kStages * tf::kXW * 8; i += tn::kThreads) {
+    const int st = i / (tf::kXW * 8), r = i % (tf::kXW * 8), k = r >> 3, piece = r & 7;
+    uint8_t* atom = s_stage + st * tn::kStageBytes + tf::kABytes + 3 * tf::kAtom;
+    const float one = (piece == 0) ? 1.f : 0.f;       // logical unit 0, first 16 bytes
+    *reinterpret_cast<float4*>(atom + sw32_off(k, piece >> 1) + 16 * (piece & 1)) = make_float4(one, 0.f, 0.f, 0.f);
+  }
+  fence_proxy_async_smem();
+  if (warp == 0) tmem_alloc<256>(s_tmem);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *s_tmem;
+
+  if (warp == 0) {
+    // ================= MMA issue: D1 (cols 0..95) = A x E, D2 (cols 96..191) = E4 x E =================
+    constexpr uint32_t idesc = umma_idesc(2, 128, kNCols, 1, 1);
+    const uint64_t tmpl = smem_desc(0, tf::kAtom, 512, 1);
+    const uint32_t hi = (uint32_t)(tmpl >> 32), lo0 = (uint32_t)tmpl;
+    uint32_t n = 0;
+    for (int item = blockIdx.x; item < g.nitems; item += gridDim.x, ++n) {
+      const uint32_t s = n % kStages;
+      mbar_wait(&full[s], (n / kStages) & 1);
+      tc_fence_after();
+      const uint32_t a_lo = lo0 + (smem_u32(s_stage + s * tn::kStageBytes) >> 4);
+      const uint32_t e_lo = a_lo + (tf::kABytes >> 4);
+      const uint32_t acc0 = n == 0 ? 0u : 1u;
+      if (elect_one()) {
+#pragma unroll
+        for (int kb = 0; kb < tf::kXW / 8; ++kb) {
+          const uint64_t ed = ((uint64_t)hi << 32) | (uint64_t)(e_lo + kb * 64);
+          umma_tf32(tmem_base, ((uint64_t)hi << 32) | (uint64_t)(a_lo + kb * 64), ed, idesc, kb == 0 ? acc0 : 1u);
+          umma_tf32(tmem_base + kNCols, ed, ed, idesc, kb == 0 ? acc0 : 1u);
+        }
+        umma_commit(&empty[s]);
+      }
+      __syncwarp();
+    }
+    if (elect_one()) umma_commit(done);
+    __syncwarp();
+  } else if (warp == 1) {
+    // ================= TMA loader =================
+    if (lane == 0) {
+      uint32_t n = 0;
+      for (int item = blockIdx.x; item < g.nitems; item += gridDim.x, ++n) {
+        const int strip = item % g.nstrips;
+        const int grp = (item / g.nstrips) % g.ngroups;
+        const int b = item / (g.nstrips * g.ngroups);
+        const int y0 = grp * kRows, x0 = strip * tf::kXW;
+        const uint32_t rs = n % tn::kRawStages;
+        mbar_wait(&rempty[rs], ((n / tn::kRawStages) & 1) ^ 1);
+        uint8_t* dst = s_rawb + rs * tn::kRawStage;
+        mbar_expect_tx(&rfull[rs], tn::kGBytes + tn::kMBytes + tn::kIBytes);
+        tma_load_4d(dst, &tm_dp1, &rfull[rs], 0, x0 >> 1, y0 >> 1, b);
+        tma_load_4d(dst + tn::kGBytes, &tm_mask, &rfull[rs], 0, x0 >> 1, y0 >> 1, b);
+        tma_load_3d(dst + tn::kGBytes + tn::kMBytes, &tm_in, &rfull[rs], x0 - 4, y0 - 2, b);
+      }
+    }
+  } else {
+    // ================= producers: route dp1 to the arg-max pixel of its window =================
+    const int pt = threadIdx.x - 64;                 // 0..511
+    const int q = pt & 3, w = pt >> 2;               // channels 4q..4q+3 of window w
+    const int wr = w >> 5, wc = w & 31;
+    const float4 sc4 = *reinterpret_cast<const float4*>(s_sc + 4 * q);
+    const int stride = (int)gridDim.x;
+    int c_strip = (int)blockIdx.x % g.nstrips;
+    const int d_strip = stride % g.nstrips;
+    const uint32_t goff = (uint32_t)(wr * (tf::kXW / 2) * 64 + wc * 64 + q * 16);
+    const uint32_t moff = (uint32_t)(tn::kGBytes + (wr * (tf::kXW / 2) + wc) * 16 + q * 4);
+    uint32_t n = 0;
+    for (int item = blockIdx.x; item < g.nitems; item += stride, ++n) {
+      const uint32_t s = n % kStages, rs = n % tn::kRawStages;
+      uint8_t* sA = s_stage + s * tn::kStageBytes;
+      uint8_t* sE = sA + tf::kABytes;
+      const uint8_t* raw = s_rawb + rs * tn::kRawStage;
+      const float* sI = reinterpret_cast<const float*>(raw + tn::kGBytes + tn::kMBytes);
+      const int kvalid = g.W - c_strip * tf::kXW;       // pixels of this strip inside the image (>= 64: all)
+      c_strip += d_strip;
+      if (c_strip >= g.nstrips) c_strip -= g.nstrips;
+      mbar_wait(&rfull[rs], (n / tn::kRawStages) & 1);
+      const float4 gr = *reinterpret_cast<const float4*>(raw + goff);
+      const uint32_t mk = *reinterpret_cast<const uint32_t*>(raw + moff);
+      mbar_wait(&empty[s], ((n / kStages) & 1) ^ 1);
+      {
+        float o[4][4];
+#pragma unroll
+        for (int cc = 0; cc < 4; ++cc) {
+          const uint32_t mb = (mk >> (8 * cc)) & 0xFFu;
+          const float gq = (mb & 4u) ? (&gr.x)[cc] * (&sc4.x)[cc] : 0.f;     // ReLU-active: dy * scale
+          const uint32_t am = mb & 3u;
+#pragma unroll
+          for (int i = 0; i < 4; ++i) o[i][cc] = (am == (uint32_t)i) ? gq : 0.f;
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int kx = 2 * wc + (i & 1);
+          *reinterpret_cast<float4*>(sA + wr * tf::kAtom + sw32_off(kx, 2 * (i >> 1) + (q >> 1)) + 16 * (q & 1)) =
+              make_float4(o[i][0], o[i][1], o[i][2], o[i][3]);
+        }
+      }
+      // expanded input E[r'][k][dxs]; columns past the image edge are zeroed (no output pixel there)
+#pragma unroll
+      for (int j = 0; j < (2 * kERows * tf::kXW) / tf::kProd; ++j) {
+        const int idx = pt + j * tf::kProd;
+        const int kx = idx & (tf::kXW - 1), c2 = idx >> 6, rr = c2 >> 1;
+        const float* src = sI + rr * tt::kInW + kx + 2 + 4 * (c2 & 1);
+        const float4 e = kx < kvalid ? make_float4(src[0], src[1], src[2], src[3]) : make_float4(0.f, 0.f, 0.f, 0.f);
+        *reinterpret_cast<float4*>(sE + (rr >> 2) * tf::kAtom + sw32_off(kx, rr & 3) + 16 * (c2 & 1)) = e;
+      }
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) { mbar_arrive(&rempty[rs]); mbar_arrive(&full[s]); }
+    }
+  }
+  // ================= extraction: D1 -> routed dW, D2 -> Gram matrix M and column sums S =================
+  float* s_T1 = reinterpret_cast<float*>(s_stage);               // [128][97]
+  constexpr int kTP = kNCols + 1;
+  float* s_T2 = s_T1 + 128 * kTP;                                // [128][97]
+  if (warp >= 2 && warp <= 5) {
+    mbar_wait(done, 0);
+    tc_fence_after();
+    const int qq = warp & 3, m = qq * 32 + lane;
+#pragma unroll 1
+    for (int c0 = 0; c0 < 2 * kNCols; c0 += 16) {
+      uint32_t v[16];
+      tmem_ld16(tmem_base + ((uint32_t)(qq * 32) << 16) + c0, v);
+      tmem_ld_wait();
+      float* dstT = c0 < kNCols ? s_T1 + m * kTP + c0 : s_T2 + m * kTP + (c0 - kNCols);
+#pragma unroll
+      for (int j = 0; j < 16; ++j) dstT[j] = __uint_as_float(v[j]);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  float* prow = partials + (size_t)blockIdx.x * tn::kPartial;
+  for (int t = threadIdx.x; t < tn::kPartial; t += tn::kThreads) {
+    float a = 0.f;
+    if (t < 400) {                                   // routed: sum_r D1[(r, c)][(r + dy, dx)]
+      const int c = t / 25, tap = t % 25, dy = tap / 5, dxs = tap % 5;
+#pragma unroll
+      for (int r = 0; r < kRows; ++r) a += s_T1[(16 * r + c) * kTP + (r + dy) * 8 + dxs];
+    } else if (t < 1025) {                           // M[tap'][tap] = sum_r D2[(r + dy', dx')][(r + dy, dx)]
+      const int u = t - 400, t1 = u / 25, t2 = u % 25;
+#pragma unroll
+      for (int r = 0; r < kRows; ++r) a += s_T2[((r + t1 / 5) * 8 + t1 % 5) * kTP + (r + t2 / 5) * 8 + t2 % 5];
+    } else {                                         // S[tap] = sum_r D2[ones row 96][(r + dy, dx)]
+      const int tap = t - 1025;
+#pragma unroll
+      for (int r = 0; r < kRows; ++r) a += s_T2[96 * kTP + (r + tap / 5) * 8 + tap % 5];
+    }
+    prow[t] = a;
+  }
+  if (warp == 0) { __syncwarp(); tmem_dealloc<256>(tmem_base); }
+}
+
+// dW1 = gscale * (routed + ca * S + cb * (w1 . M + b1 * S)), from the fp64-reduced partial rows
+__global__ void conv1_wgrad_nox1_combine_kernel(const float* __restrict__ partials, int nparts,
+                                                const float* __restrict__ w1, const float* __restrict__ b1,
+                                                const float* __restrict__ bn, const float* __restrict__ red,
+                                                float* __restrict__ dw1, float gscale) {
+  __shared__ double s_red[tn::kPartial];
+  for (int t = threadIdx.x; t < tn::kPartial; t += blockDim.x) {
+    double a = 0.0;
+    for (int i = 0; i < nparts; ++i) a += (double)partials[(size_t)i * tn::kPartial + t];
+    s_red[t] = a;
+  }
+  __syncthreads();
+  for (int t = threadIdx.x; t < 400; t += blockDim.x) {
+    const int c = t / 25, tap = t % 25;
+    const double sc = bn[c], mu = bn[2 * kC1 + c], rs = bn[3 * kC1 + c], mdy = red[c], mdyx = red[kC1 + c];
+    const double ca = sc * (rs * mdyx * mu - mdy), cb = -sc * rs * mdyx;
+    const double S = s_red[1025 + tap];
+    double R = (double)b1[c] * S;
+    for (int t1 = 0; t1 < 25; ++t1) R += (double)w1[c * 25 + t1] * s_red[400 + t1 * 25 + tap];
+    dw1[t] = (float)((double)gscale * (s_red[t] + ca * S + cb * R));
+  }
+}
+
 }  // namespace
 
 // Same contract as b200_conv1_wgrad (partials: [b200_conv1_wgrad_grid()][400] scratch).
@@ -860,6 +1091,58 @@ B200_API int b200_conv1_wgrad_tc_f32(const void* in_f32, const void* x1, const v
   return b200_reduce_partials(partials, grid, 400, dw1, gscale, stream);
 }
 
+// Layer-1 weight gradient without the conv output (see conv1_wgrad_nox1_tf32_kernel).  amask_u8 = the bytes
+// b200_conv1_fwd_pool_mask_tc_f32 wrote; partials: [b200_conv1_wgrad_grid()][b200_conv1_wgrad_nox1_partial()] floats.
+// Requires H % 8 == 0 and W % 4 == 0 (returns -4 otherwise: use b200_conv1_wgrad_tc_f32 with the stored x1).
+B200_API int b200_conv1_wgrad_nox1_partial() { return tn::kPartial; }
+B200_API int b200_conv1_wgrad_nox1_f32(const void* in_f32, const void* dp1, const void* amask_u8, const void* w1,
+                                       const void* b1, const void* bn, const void* red, void* partials, void* dw1, int B,
+                                       int H, int W, float gscale, void* stream) {
+  if (H % 8 != 0 || W % 4 != 0) return b200_fail(-4, "conv1_wgrad_nox1: needs H %% 8 == 0 and W %% 4 == 0 (got %d x %d)", H, W);
+  cudaStream_t s = (cudaStream_t)stream;
+  WgGeom g;
+  g.B = B; g.H = H; g.W = W;
+  g.nstrips = (W + tf::kXW - 1) / tf::kXW;
+  g.ngroups = H / kRows;
+  g.nitems = B * g.nstrips * g.ngroups;
+  const int nsm = b200_compute_sms();
+  const int grid = g.nitems < nsm ? g.nitems : nsm;
+  CUtensorMap tg, tmk, ti;
+  {
+    cuuint64_t d[4] = {16, (cuuint64_t)W / 2, (cuuint64_t)H / 2, (cuuint64_t)B};
+    cuuint64_t st[3] = {64, (cuuint64_t)(W / 2) * 64, (cuuint64_t)(H / 2) * (W / 2) * 64};
+    cuuint32_t bx[4] = {16, tf::kXW / 2, kRows / 2, 1};
+    int rc = f32_map(&tg, dp1, 4, d, st, bx, CU_TENSOR_MAP_SWIZZLE_NONE);
+    if (rc) return rc;
+  }
+  {
+    EncodeTiledFn1 enc = encode_fn1();
+    if (!enc) return b200_fail(-3, "cuTensorMapEncodeTiled entry point not available");
+    cuuint64_t d[4] = {16, (cuuint64_t)W / 2, (cuuint64_t)H / 2, (cuuint64_t)B};
+    cuuint64_t st[3] = {16, (cuuint64_t)(W / 2) * 16, (cuuint64_t)(H / 2) * (W / 2) * 16};
+    cuuint32_t bx[4] = {16, tf::kXW / 2, kRows / 2, 1};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    CUresult r = enc(&tmk, CU_TENSOR_MAP_DATA_TYPE_UINT8, 4, const_cast<void*>(amask_u8), d, st, bx, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return b200_fail((int)r, "cuTensorMapEncodeTiled (mask map) failed with CUresult %d", (int)r);
+  }
+  {
+    cuuint64_t d[3] = {(cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)B};
+    cuuint64_t st[2] = {(cuuint64_t)W * 4, (cuuint64_t)H * W * 4};
+    cuuint32_t bx[3] = {tt::kInW, kERows, 1};
+    int rc = f32_map(&ti, in_f32, 3, d, st, bx, CU_TENSOR_MAP_SWIZZLE_NONE);
+    if (rc) return rc;
+  }
+  B200_CUDA(set_max_smem(conv1_wgrad_nox1_tf32_kernel, tn::kSmemBytes));
+  conv1_wgrad_nox1_tf32_kernel<<<grid, tn::kThreads, tn::kSmemBytes, s>>>(tg, tmk, ti, (const float*)bn, (float*)partials, g);
+  B200_LAUNCH_CHECK();
+  conv1_wgrad_nox1_combine_kernel<<<1, 512, 0, s>>>((const float*)partials, grid, (const float*)w1, (const float*)b1,
+                                                    (const float*)bn, (const float*)red, (float*)dw1, gscale);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
 // =====================================================================================
 // K3 (+K4 statistics), conv1 forward as a Toeplitz GEMM on tcgen05.
 //
@@ -910,7 +1193,8 @@ template <typename OT, bool POOL = false>
 __global__ void __launch_bounds__(kFwThreads, 1)
 conv1_fwd_tc_kernel(const float* __restrict__ in, const float* __restrict__ w1, const float* __restrict__ b1,
                     OT* __restrict__ x1, float* __restrict__ partials, FwGeom g,
-                    const float* __restrict__ bn = nullptr, float* __restrict__ pooled = nullptr) {
+                    const float* __restrict__ bn = nullptr, float* __restrict__ pooled = nullptr,
+                    uint8_t* __restrict__ amask = nullptr) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((128u - (smem_u32(smem_raw) & 127u)) & 127u);
   uint8_t* s_x = smem;                                   // [kFwStages][hi | lo][row planes][columns][16 B]
@@ -1101,18 +1385,29 @@ conv1_fwd_tc_kernel(const float* __restrict__ in, const float* __restrict__ w1, 
               // second pass of the two-pass forward: the batch statistics are known (first pass), so BN + ReLU + the
               // 2x2 max-pool run here and the separate pass over the 2.88 GB conv output (K5) disappears.  The two
               // rows of a window are this chunk's two rows, the two columns are this lane and its neighbour.
-              uint32_t pm[16];
+              // amask (optional): one byte per pooled element = arg-max position (first maximum in row-major order,
+              // as ATen picks it) | ReLU-active << 2 - all the backward needs to route dp1 without the conv output.
+              uint32_t pm[16], mb[4] = {0u, 0u, 0u, 0u};
 #pragma unroll
               for (int c = 0; c < 16; ++c) {
                 const float sc = s_bn[c], sh = s_bn[16 + c];
-                float m = fmaxf(fmaxf(0.f, fmaf(__uint_as_float(v[c]), sc, sh)), fmaf(__uint_as_float(v[16 + c]), sc, sh));
-                m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 1));
-                pm[c] = __float_as_uint(m);
+                const float y0 = fmaf(__uint_as_float(v[c]), sc, sh), y1 = fmaf(__uint_as_float(v[16 + c]), sc, sh);
+                const float n0 = __shfl_xor_sync(0xffffffffu, y0, 1), n1 = __shfl_xor_sync(0xffffffffu, y1, 1);
+                // on the even lane: y0 = (row 0, col 0), n0 = (row 0, col 1), y1 = (row 1, col 0), n1 = (row 1, col 1)
+                float best = y0;
+                uint32_t am = 0;
+                if (n0 > best) { best = n0; am = 1; }
+                if (y1 > best) { best = y1; am = 2; }
+                if (n1 > best) { best = n1; am = 3; }
+                pm[c] = __float_as_uint(fmaxf(best, 0.f));
+                mb[c >> 2] |= (am | (best > 0.f ? 4u : 0u)) << (8 * (c & 3));
               }
               if (ok && !(lane & 1)) {
-                float* po = pooled + (((size_t)b * (g.H >> 1) + ((yb + (c0 >> 4)) >> 1)) * (g.W >> 1) + (x >> 1)) * 16;
+                const size_t pix = ((size_t)b * (g.H >> 1) + ((yb + (c0 >> 4)) >> 1)) * (g.W >> 1) + (x >> 1);
+                float* po = pooled + pix * 16;
                 st_global_v8(po, &pm[0]);
                 st_global_v8(po + 8, &pm[8]);
+                if (amask != nullptr) *reinterpret_cast<uint4*>(amask + pix * 16) = make_uint4(mb[0], mb[1], mb[2], mb[3]);
               }
             }
             if (k < 3) tmem_ld_wait();
@@ -1165,7 +1460,8 @@ conv1_fwd_tc_kernel(const float* __restrict__ in, const float* __restrict__ w1, 
 // Same contract as b200_conv1_fwd; partials must hold [b200_sm_count()][32]; *nparts_out = rows written.
 template <typename OT>
 static int conv1_fwd_tc_t(const void* in_f32, const void* w1, const void* b1, void* x1, void* partials, int B,
-                          int H, int W, int* nparts_out, void* stream, const void* bn = nullptr, void* pooled = nullptr) {
+                          int H, int W, int* nparts_out, void* stream, const void* bn = nullptr, void* pooled = nullptr,
+                          void* amask = nullptr) {
   B200_CHECK(H % 2 == 0 && W % 2 == 0, "conv1_fwd_tc: H and W must be even");
   cudaStream_t s = (cudaStream_t)stream;
   if (pooled != nullptr) {
@@ -1180,7 +1476,8 @@ static int conv1_fwd_tc_t(const void* in_f32, const void* w1, const void* b1, vo
       const int gridp = gp.nitems < nsmp ? gp.nitems : nsmp;
       conv1_fwd_tc_kernel<OT, true><<<gridp, kFwThreads, kFwSmemBytes, s>>>((const float*)in_f32, (const float*)w1,
                                                                             (const float*)b1, (OT*)x1, (float*)partials,
-                                                                            gp, (const float*)bn, (float*)pooled);
+                                                                            gp, (const float*)bn, (float*)pooled,
+                                                                            (uint8_t*)amask);
       B200_LAUNCH_CHECK();
       if (nparts_out) *nparts_out = gridp;
       return 0;
@@ -1227,4 +1524,12 @@ B200_API int b200_conv1_fwd_pool_tc_f32(const void* in_f32, const void* w1, cons
                                         void* p1_f32, void* partials, int B, int H, int W, void* stream) {
   B200_CHECK(bn != nullptr && p1_f32 != nullptr && x1_f32 != nullptr, "conv1_fwd_pool: bn, x1 and p1 are required");
   return conv1_fwd_tc_t<float>(in_f32, w1, b1, x1_f32, partials, B, H, W, nullptr, stream, bn, p1_f32);
+}
+// Same, without the conv output: x1 may be null (nothing of the 2.88 GB tensor is written) and `amask`
+// ([B][H/2][W/2][16] bytes: arg-max position | ReLU-active << 2) is what b200_conv1_wgrad_nox1_f32 routes dp1 with.
+B200_API int b200_conv1_fwd_pool_mask_tc_f32(const void* in_f32, const void* w1, const void* b1, const void* bn,
+                                             void* x1_f32_or_null, void* p1_f32, void* amask_u8, void* partials, int B,
+                                             int H, int W, void* stream) {
+  B200_CHECK(bn != nullptr && p1_f32 != nullptr && amask_u8 != nullptr, "conv1_fwd_pool_mask: bn, p1 and the mask are required");
+  return conv1_fwd_tc_t<float>(in_f32, w1, b1, x1_f32_or_null, partials, B, H, W, nullptr, stream, bn, p1_f32, amask_u8);
 }

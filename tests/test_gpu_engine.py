@@ -131,7 +131,7 @@ def test_tf32_engine_matches_pure_fp32_model():
     to match.  The bands are TF32's 10-bit operand mantissa, an order of magnitude tighter than the bf16 mode's."""
     shape, B = (64, 96), 4
     ref, eng, out = _run_pair(shape, B, steps=4, lr=1e-3, backend="tc", fuse=True, emulate=False, precision="tf32")
-    assert eng.x1.dtype == torch.float32 and eng.p2.dtype == torch.float32
+    assert eng.p1.dtype == torch.float32 and eng.p2.dtype == torch.float32
     for s, (loss, loss_ref, grads, grads_ref) in enumerate(out):
         print(f"[engine/tf32] step {s}: loss {loss:.6f} ref {loss_ref:.6f}")
         # step 0 compares the same weights; afterwards two slightly different gradient streams drive the weights apart

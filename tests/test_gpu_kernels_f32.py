@@ -296,3 +296,51 @@ def test_conv1_two_pass_equals_conv_then_pool(ops, shape):
     torch.cuda.synchronize()
     assert torch.equal(x1a, x1b)
     assert torch.equal(p1a, p1b), float((p1a - p1b).abs().max())
+
+
+@pytest.mark.parametrize("shape", [(2, 40, 72), (1, 8, 128), (3, 64, 300), (2, 136, 260)])
+def test_conv1_wgrad_without_the_conv_output(ops, shape):
+    """Forward pass 2 emits arg-max/ReLU bytes instead of (or next to) x1; the x1-free weight gradient (routed part on
+    the tensor cores + dense BatchNorm term from the input's Gram matrix) must match the fp32 PyTorch oracle."""
+    B, H, W = shape
+    g = torch.Generator(device=DEV).manual_seed(43)
+    xin = torch.rand(B, H, W, device=DEV, generator=g)
+    w = torch.randn(16, 1, 5, 5, device=DEV, generator=g) * 0.2
+    b = torch.randn(16, device=DEV, generator=g) * 0.05
+    gamma = torch.rand(16, device=DEV, generator=g) + 0.5
+    gamma[::5] *= -1
+    beta = torch.randn(16, device=DEV, generator=g) * 0.2
+    dp = nhwc(torch.randn(B, 16, H // 2, W // 2, device=DEV, generator=g))
+    part = torch.zeros(ops.conv1_fwd_grid(), 32, device=DEV)
+    n = ops.conv1_stats_tc(xin, w, b, part)
+    bn = torch.zeros(4, 16, device=DEV)
+    rm, rv = torch.zeros(16, device=DEV), torch.ones(16, device=DEV)
+    ops.bn_finalize(part, n, 16, B * H * W, gamma, beta, rm, rv, None, bn)
+    x1 = torch.empty(B, H, W, 16, device=DEV)
+    p1 = torch.empty(B, H // 2, W // 2, 16, device=DEV)
+    mask = torch.full((B, H // 2, W // 2, 16), 255, device=DEV, dtype=torch.uint8)
+    ops.conv1_fwd_pool_tc(xin, w, b, bn, x1, p1, torch.zeros_like(part), amask_u8=mask)
+    p1_ref = torch.empty_like(p1)
+    ops.bn_relu_pool(x1, bn, p1_ref)
+    assert torch.equal(p1, p1_ref)
+    # the mask agrees with torch's max-pool indices wherever the window maximum is unique and positive
+    y = nchw(x1) * bn[0].view(1, 16, 1, 1) + bn[1].view(1, 16, 1, 1)
+    pooled, idx = F.max_pool2d(y, 2, return_indices=True)
+    yy, xx = idx // W, idx % W
+    am_ref = ((yy % 2) * 2 + (xx % 2)).permute(0, 2, 3, 1)
+    relu_ref = (pooled > 0).permute(0, 2, 3, 1)
+    assert torch.equal((mask & 3).long(), am_ref) and torch.equal((mask >> 2).bool(), relu_ref)
+    # BN backward reductions (from x1, as the engine gets them from the dgrad epilogue), then both weight gradients
+    grid = ops.pool_bn_bwd_grid()
+    partb, red = torch.zeros(grid, 64, device=DEV), torch.zeros(2, 16, device=DEV)
+    dg, db = torch.zeros(16, device=DEV), torch.zeros(16, device=DEV)
+    ops.pool_bn_bwd(x1, dp, bn, red, partb, None, mode=0)
+    ops.bn_bwd_finalize(partb, grid, 16, B * H * W, red, dg, db)
+    pw = torch.zeros(ops.conv1_wgrad_grid(), ops.conv1_wgrad_nox1_partial(), device=DEV)
+    dw = torch.zeros(16, 1, 5, 5, device=DEV)
+    ops.conv1_wgrad_nox1(xin, dp, mask, w, b, bn, red, pw, dw)
+    x1r = nchw(x1).requires_grad_(True)
+    yb = F.batch_norm(x1r, None, None, gamma, beta, training=True)
+    F.max_pool2d(F.relu(yb), 2).backward(nchw(dp))
+    ref = torch.nn.grad.conv2d_weight(xin[:, None], (16, 1, 5, 5), x1r.grad, padding=2)
+    report(f"conv1_wgrad without x1 {shape}", rel(dw, ref), 3e-3)

@@ -99,6 +99,12 @@ class FusedConvNet:
         self.fuse_bwd_stats = os.environ.get("B200DP_FUSE_BWD_STATS", "1") == "1"
         self.fuse_fc_sgd = bool(fuse_fc_sgd)
         self.conv1_two_pass = os.environ.get("B200DP_CONV1_TWO_PASS", "1") == "1"    # tf32 mode only
+        # tf32 mode: never store the conv1 output (2.88 GB at batch 5).  The second forward pass writes the pooled tensor
+        # and one byte per pooled element (arg-max | ReLU), the weight-gradient kernel routes dp1 with those bytes and
+        # gets the dense BatchNorm term from the input's Gram matrix.
+        self.conv1_no_x1 = (os.environ.get("B200DP_CONV1_NO_X1", "1") == "1" and self.precision == "tf32" and
+                            self.conv1_two_pass and self.fuse_bwd_stats and conv_backend == "tc" and
+                            H % 8 == 0 and W % 4 == 0)
         self.F = rn.feature_size((H, W))
         self.comm = None           # set by parallel.ddp for data-parallel runs
         self._b = int(batch_size)  # size of the batch currently in the buffers (<= B: short last batch)
@@ -134,7 +140,8 @@ class FusedConvNet:
             self._bind_bn_views()
             # ---- activations (gradients alias them) -------------------------
             self.x = torch.empty(B, H, W, **f32)
-            self.x1 = torch.empty(B, H, W, 16, **bf)
+            self.x1 = None if self.conv1_no_x1 else torch.empty(B, H, W, 16, **bf)
+            self.mask1 = torch.empty(B, H // 2, W // 2, 16, device=dev, dtype=torch.uint8) if self.conv1_no_x1 else None
             self.p1 = torch.empty(B, H // 2, W // 2, 16, **bf)
             self.x2 = torch.empty(B, H // 2, W // 2, 32, **bf)
             self.p2 = torch.empty(B, H // 4, W // 4, 32, **bf)
@@ -146,7 +153,7 @@ class FusedConvNet:
             self.part_c1b = torch.empty(self.g_c1, 32, **f32)       # scratch of the second conv1 pass (unused sums)
             self.part_c2 = torch.empty(self.g_tc, 64, **f32)
             self.part_bwd = torch.empty(self.g_pbb, 64, **f32)
-            self.part_wg1 = torch.empty(self.g_wg1, 400, **f32)
+            self.part_wg1 = torch.empty(self.g_wg1, ops.conv1_wgrad_nox1_partial() if self.conv1_no_x1 else 400, **f32)
             self.part_wg2 = torch.empty(self.g_tc, 32 * 16 * 25, **f32)
             self.part_fc = torch.empty(self.g_fc, 80, **f32)
             self.part_fcb = torch.empty(self.g_fc, 64, **f32)
@@ -298,7 +305,8 @@ class FusedConvNet:
         # B = size of THIS batch: a short last batch (the reference's loaders are drop_last=False,
         # mnist_onegpu.py:55-59) runs on leading-dimension views of the same buffers
         P, B, H, W = self.params, self._b, self.H, self.W
-        x, x1, p1, x2, p2t = self.x[:B], self.x1[:B], self.p1[:B], self.x2[:B], self.p2[:B]
+        x, p1, x2, p2t = self.x[:B], self.p1[:B], self.x2[:B], self.p2[:B]
+        x1 = self.x1[:B] if self.x1 is not None else None
         two_pass = self.precision == "tf32" and self.conv1_two_pass
         if two_pass:
             # fp32 storage: conv1 is cheap on the tensor cores (0.24 ms without its store), its 2.88 GB output is not -
@@ -312,7 +320,8 @@ class FusedConvNet:
         ops.bn_finalize(self.part_c1, n1, 16, B * H * W, P["layer1.1.weight"], P["layer1.1.bias"],
                         self.bn_buf[1]["mean"], self.bn_buf[1]["var"], self.bn_buf[1]["nbt"], self.bn1)
         if two_pass:
-            ops.conv1_fwd_pool_tc(x, P["layer1.0.weight"], P["layer1.0.bias"], self.bn1, x1, p1, self.part_c1b)
+            ops.conv1_fwd_pool_tc(x, P["layer1.0.weight"], P["layer1.0.bias"], self.bn1, x1, p1, self.part_c1b,
+                                  amask_u8=self.mask1[:B] if self.conv1_no_x1 else None)
         else:
             ops.bn_relu_pool(x1, self.bn1, p1)
         if self.conv_backend == "tc":
@@ -351,7 +360,8 @@ class FusedConvNet:
 
     def _backward(self, allow_fused_sgd: bool) -> None:
         P, G, B, H, W = self.params, self.grads, self._b, self.H, self.W
-        x, x1, p1, x2 = self.x[:B], self.x1[:B], self.p1[:B], self.x2[:B]
+        x, p1, x2 = self.x[:B], self.p1[:B], self.x2[:B]
+        x1 = self.x1[:B] if self.x1 is not None else None
         dx2, dp1 = x2, p1                  # in-place gradients (dp2 over p2, dx2 over x2, dp1 over p1)
         gs = self.grad_scale
         fused = allow_fused_sgd and self.fuse_fc_sgd and self.comm is None
@@ -405,8 +415,12 @@ class FusedConvNet:
             ops.pool_bn_bwd(x1, dp1, self.bn1, self.red1, self.part_bwd, None, mode=0)
             ops.bn_bwd_finalize(self.part_bwd, self.g_pbb, 16, B * H * W, self.red1, G["layer1.1.weight"],
                                 G["layer1.1.bias"], gs)
-        wg1 = ops.conv1_wgrad_tc if self.conv1_backend == "tc" else ops.conv1_wgrad
-        wg1(x, x1, dp1, self.bn1, self.red1, self.part_wg1, G["layer1.0.weight"], gs)
+        if self.conv1_no_x1:
+            ops.conv1_wgrad_nox1(x, dp1, self.mask1[:B], P["layer1.0.weight"], P["layer1.0.bias"], self.bn1, self.red1,
+                                 self.part_wg1, G["layer1.0.weight"], gs)
+        else:
+            wg1 = ops.conv1_wgrad_tc if self.conv1_backend == "tc" else ops.conv1_wgrad
+            wg1(x, x1, dp1, self.bn1, self.red1, self.part_wg1, G["layer1.0.weight"], gs)
         G["layer1.0.bias"].zero_()
 
     def step(self) -> None:
@@ -471,5 +485,5 @@ class FusedConvNet:
         self.dp1[:B].copy_(dxin.permute(0, 2, 3, 1))
 
     def activation_bytes(self) -> int:
-        ts = (self.x, self.x1, self.p1, self.x2, self.p2)
-        return sum(t.numel() * t.element_size() for t in ts)
+        ts = (self.x, self.x1, self.mask1, self.p1, self.x2, self.p2)
+        return sum(t.numel() * t.element_size() for t in ts if t is not None)

@@ -164,17 +164,44 @@ def conv1_stats_tc(x_f32, w1, b1, partials) -> int:
     return n.value
 
 
-def conv1_fwd_pool_tc(x_f32, w1, b1, bn, x1_f32, p1_f32, partials):
-    """Second pass: conv1 again (bit-identical values), stored to ``x1_f32`` for the backward, with BN-apply + ReLU +
-    2x2 max-pool fused into the epilogue -> ``p1_f32``; replaces conv1_fwd_tc + bn_relu_pool (K3 + K5)."""
+def conv1_fwd_pool_tc(x_f32, w1, b1, bn, x1_f32, p1_f32, partials, amask_u8=None):
+    """Second pass: conv1 again (bit-identical values) with BN-apply + ReLU + 2x2 max-pool fused into the epilogue ->
+    ``p1_f32``; replaces conv1_fwd_tc + bn_relu_pool (K3 + K5).  The conv output goes to ``x1_f32`` for the backward -
+    or nowhere (``x1_f32=None``) when ``amask_u8`` ([B,H/2,W/2,16] uint8: arg-max | ReLU << 2) is produced for
+    ``conv1_wgrad_nox1``."""
     B, H, W = x_f32.shape
-    assert x1_f32.dtype == torch.float32 and p1_f32.dtype == torch.float32
+    assert p1_f32.dtype == torch.float32 and (x1_f32 is None or x1_f32.dtype == torch.float32)
     lib = _lib()
+    if amask_u8 is not None:
+        assert amask_u8.dtype == torch.uint8 and amask_u8.numel() == p1_f32.numel()
+        lib.b200_conv1_fwd_pool_mask_tc_f32.argtypes = [c_void_p] * 8 + [c_int, c_int, c_int, c_void_p]
+        _native.check(lib.b200_conv1_fwd_pool_mask_tc_f32(_p(x_f32), _p(w1), _p(b1), _p(bn), _p(x1_f32), _p(p1_f32),
+                                                          _p(amask_u8), _p(partials), B, H, W, _stream()),
+                      "conv1_fwd_pool_mask_tc")
+        _count(1)
+        return
+    assert x1_f32 is not None
     lib.b200_conv1_fwd_pool_tc_f32.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                                c_int, c_int, c_int, c_void_p]
     _native.check(lib.b200_conv1_fwd_pool_tc_f32(_p(x_f32), _p(w1), _p(b1), _p(bn), _p(x1_f32), _p(p1_f32), _p(partials),
                                                  B, H, W, _stream()), "conv1_fwd_pool_tc")
     _count(1)
+
+
+def conv1_wgrad_nox1_partial() -> int:
+    return int(_lib().b200_conv1_wgrad_nox1_partial())
+
+
+def conv1_wgrad_nox1(x_f32, dp1_f32, amask_u8, w1, b1, bn, red, partials, dw1, gscale=1.0):
+    """K13 without the conv1 output: routes dp1 through the forward's arg-max/ReLU bytes on the tensor cores and gets the
+    dense BatchNorm term from the input's 25x25 Gram matrix (same kernel, one more MMA per K-step).  fp32 storage,
+    H % 8 == 0.  partials: [conv1_wgrad_grid()][conv1_wgrad_nox1_partial()]."""
+    B, H, W = x_f32.shape
+    lib = _lib()
+    lib.b200_conv1_wgrad_nox1_f32.argtypes = [c_void_p] * 9 + [c_int, c_int, c_int, c_float, c_void_p]
+    _native.check(lib.b200_conv1_wgrad_nox1_f32(_p(x_f32), _p(dp1_f32), _p(amask_u8), _p(w1), _p(b1), _p(bn), _p(red),
+                                                _p(partials), _p(dw1), B, H, W, gscale, _stream()), "conv1_wgrad_nox1")
+    _count(2)
 
 
 def bn_finalize(partials, nparts, C, count, gamma, beta, running_mean, running_var, nbt, out, momentum=0.1,
