@@ -115,3 +115,42 @@ def test_conv1_wgrad_fullsize(ops, dt, tol, name):
     # 9 M pixels of BatchNorm-backward cancellation amplify the operand rounding of each mode: the bf16 kernel
     # (bf16 gradient and input operands) is measured at 8e-2 here, the tf32 one at ~1e-3
     report(f"conv1_wgrad {name}", rel(dw, ref), 1.5e-1 if dt == torch.bfloat16 else 5e-3)
+
+
+def test_conv1_two_pass_and_wgrad_without_x1_fullsize(ops):
+    """The tf32 mode's layer 1 at 3000x3000: statistics pass, conv+BN+ReLU+pool pass that stores no conv output (only the
+    pooled tensor and the arg-max/ReLU bytes), weight gradient from those bytes + the input's Gram matrix - against
+    plain fp32 PyTorch on the explicitly materialised conv output."""
+    g = torch.Generator(device=DEV).manual_seed(34)
+    xin = torch.rand(1, S, S, device=DEV, generator=g)
+    w = torch.randn(16, 1, 5, 5, device=DEV, generator=g) * 0.2
+    b = torch.randn(16, device=DEV, generator=g) * 0.05
+    gamma = torch.rand(16, device=DEV, generator=g) + 0.5
+    beta = torch.randn(16, device=DEV, generator=g) * 0.2
+    dp = nhwc(torch.randn(1, 16, S // 2, S // 2, device=DEV, generator=g), torch.float32)
+    part = torch.zeros(ops.conv1_fwd_grid(), 32, device=DEV)
+    n = ops.conv1_stats_tc(xin, w, b, part)
+    bn = torch.zeros(4, 16, device=DEV)
+    rm, rv = torch.zeros(16, device=DEV), torch.ones(16, device=DEV)
+    ops.bn_finalize(part, n, 16, S * S, gamma, beta, rm, rv, None, bn)
+    p1 = torch.empty(1, S // 2, S // 2, 16, device=DEV)
+    mask = torch.empty(1, S // 2, S // 2, 16, device=DEV, dtype=torch.uint8)
+    ops.conv1_fwd_pool_tc(xin, w, b, bn, None, p1, torch.zeros_like(part), amask_u8=mask)
+    x1 = F.conv2d(xin[:, None], w, b, padding=2)                        # oracle conv output, fp32
+    x1r = x1.clone().requires_grad_(True)
+    y = F.batch_norm(x1r, None, None, gamma, beta, training=True)
+    pooled = F.max_pool2d(F.relu(y), 2)
+    report("conv1 two-pass pooled output", rel(nchw(p1), pooled.detach()), 2e-5)
+    pooled.backward(nchw(dp))
+    ref = torch.nn.grad.conv2d_weight(xin[:, None], (16, 1, 5, 5), x1r.grad, padding=2)
+    # BN backward reductions from the oracle (the engine takes them from the dgrad epilogue)
+    xhat = (x1 - bn[2].view(1, 16, 1, 1)) * bn[3].view(1, 16, 1, 1)
+    yd = y.detach().requires_grad_(True)
+    F.max_pool2d(F.relu(yd), 2).backward(nchw(dp))
+    dy = yd.grad
+    red = torch.stack([dy.mean((0, 2, 3)), (dy * xhat).mean((0, 2, 3))]).contiguous()
+    pw = torch.zeros(ops.conv1_wgrad_grid(), ops.conv1_wgrad_nox1_partial(), device=DEV)
+    dw = torch.zeros(16, 1, 5, 5, device=DEV)
+    ops.conv1_wgrad_nox1(xin, dp, mask, w, b, bn, red, pw, dw)
+    torch.cuda.synchronize()
+    report("conv1_wgrad without x1, full size", rel(dw, ref), 5e-3)
