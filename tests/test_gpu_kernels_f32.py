@@ -344,3 +344,72 @@ def test_conv1_wgrad_without_the_conv_output(ops, shape):
     F.max_pool2d(F.relu(yb), 2).backward(nchw(dp))
     ref = torch.nn.grad.conv2d_weight(xin[:, None], (16, 1, 5, 5), x1r.grad, padding=2)
     report(f"conv1_wgrad without x1 {shape}", rel(dw, ref), 3e-3)
+
+
+@pytest.mark.parametrize("shape", [(2, 40, 72), (1, 8, 128), (3, 64, 300), (2, 136, 1100), (1, 302, 2020)])
+def test_conv1_row_operand_two_pass(ops, shape):
+    """csrc/conv1_hz.cu: the kind::tf32 layer-1 forward whose MMA operand is the image row as TMA delivered it.
+    Pass 1 = batch statistics, pass 2 = pooled tensor + arg-max/ReLU bytes; both against plain fp32 PyTorch
+    (TF32 error level: the input is truncated to 10 mantissa bits, as cuDNN's TF32 conv of the reference does)."""
+    B, H, W = shape
+    g = torch.Generator(device=DEV).manual_seed(47)
+    xin = torch.rand(B, H, W, device=DEV, generator=g)
+    w = torch.randn(16, 1, 5, 5, device=DEV, generator=g) * 0.2
+    b = torch.randn(16, device=DEV, generator=g) * 0.1
+    gamma = torch.rand(16, device=DEV, generator=g) + 0.5
+    gamma[::5] *= -1
+    beta = torch.randn(16, device=DEV, generator=g) * 0.2
+    x1 = F.conv2d(xin[:, None], w, b, padding=2)
+    part = torch.zeros(ops.conv1_fwd_grid(), 32, device=DEV)
+    n = ops.conv1_stats_tc(xin, w, b, part, row_operand=True)
+    sums = part[:n].double().sum(0)
+    ref_sum, ref_sq = x1.double().sum((0, 2, 3)), (x1.double() ** 2).sum((0, 2, 3))
+    report(f"conv1 row-operand stats: sum {shape}", rel(sums[:16].float(), ref_sum.float()), 2e-3)
+    report(f"conv1 row-operand stats: sumsq {shape}", rel(sums[16:].float(), ref_sq.float()), 2e-3)
+    bn = torch.zeros(4, 16, device=DEV)
+    rm, rv = torch.zeros(16, device=DEV), torch.ones(16, device=DEV)
+    ops.bn_finalize(part, n, 16, B * H * W, gamma, beta, rm, rv, None, bn)
+    p1 = torch.full((B, H // 2, W // 2, 16), float("nan"), device=DEV)
+    mask = torch.full((B, H // 2, W // 2, 16), 255, device=DEV, dtype=torch.uint8)
+    ops.conv1_fwd_pool_tc(xin, w, b, bn, None, p1, None, amask_u8=mask, row_operand=True)
+    torch.cuda.synchronize()
+    y = x1 * bn[0].view(1, 16, 1, 1) + bn[1].view(1, 16, 1, 1)
+    pooled, idx = F.max_pool2d(y, 2, return_indices=True)
+    report(f"conv1 row-operand pooled {shape}", rel(nchw(p1), F.relu(pooled)), 2e-3)
+    # arg-max / ReLU bytes: equal to the fp32 oracle's except where TF32 rounding flips a near-tie
+    yy, xx = idx // W, idx % W
+    am_ref = ((yy % 2) * 2 + (xx % 2)).permute(0, 2, 3, 1)
+    relu_ref = (pooled > 0).permute(0, 2, 3, 1)
+    assert int(mask.max()) <= 7
+    bad_am = ((mask & 3).long() != am_ref).float().mean().item()
+    bad_relu = ((mask >> 2).bool() != relu_ref).float().mean().item()
+    print(f"[f32] row-operand mask mismatch vs fp32 oracle: arg-max {bad_am:.2e}, relu {bad_relu:.2e}")
+    assert bad_am < 5e-3 and bad_relu < 5e-3
+    # Against an oracle that rounds its operands the way the kernel does (input truncated, weights rounded to nearest,
+    # exact accumulation) the choice of arg-max is the same up to accumulation-order ties, and the weight gradient
+    # routed with the kernel's bytes matches to TF32 error.  (Against the plain fp32 oracle a flipped near-tie moves a
+    # gradient value by one pixel - on this white-noise input that alone is a few percent of dW.)
+    xt = (xin.view(torch.int32) & -8192).view(torch.float32)
+    wt = ((w.view(torch.int32) + 4096) & -8192).view(torch.float32)
+    x1t = (F.conv2d(xt[:, None].double(), wt.double(), b.double(), padding=2)).float()
+    yt = x1t * bn[0].view(1, 16, 1, 1) + bn[1].view(1, 16, 1, 1)
+    pooled_t, idx_t = F.max_pool2d(yt, 2, return_indices=True)
+    am_t = (((idx_t // W) % 2) * 2 + (idx_t % W) % 2).permute(0, 2, 3, 1)
+    bad_t = ((mask & 3).long() != am_t).float().mean().item()
+    bad_rt = ((mask >> 2).bool() != (pooled_t > 0).permute(0, 2, 3, 1)).float().mean().item()
+    print(f"[f32] row-operand mask mismatch vs operand-rounded oracle: arg-max {bad_t:.2e}, relu {bad_rt:.2e}")
+    assert bad_t < 2e-5 and bad_rt < 2e-5
+    dp = nhwc(torch.randn(B, 16, H // 2, W // 2, device=DEV, generator=g))
+    if H % 8 == 0:
+        x1r = x1t.clone().requires_grad_(True)
+        yb = F.batch_norm(x1r, None, None, gamma, beta, training=True)
+        F.max_pool2d(F.relu(yb), 2).backward(nchw(dp))
+        ref = torch.nn.grad.conv2d_weight(xin[:, None], (16, 1, 5, 5), x1r.grad, padding=2)
+        yd = yb.detach().requires_grad_(True)
+        F.max_pool2d(F.relu(yd), 2).backward(nchw(dp))
+        xhat = (x1t - bn[2].view(1, 16, 1, 1)) * bn[3].view(1, 16, 1, 1)
+        red = torch.stack([yd.grad.mean((0, 2, 3)), (yd.grad * xhat).mean((0, 2, 3))]).contiguous()
+        pw = torch.zeros(ops.conv1_wgrad_grid(), ops.conv1_wgrad_nox1_partial(), device=DEV)
+        dw = torch.zeros(16, 1, 5, 5, device=DEV)
+        ops.conv1_wgrad_nox1(xin, dp, mask, w, b, bn, red, pw, dw)
+        report(f"conv1_wgrad from row-operand mask {shape}", rel(dw, ref), 5e-3)

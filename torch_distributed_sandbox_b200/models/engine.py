@@ -105,6 +105,9 @@ class FusedConvNet:
         self.conv1_no_x1 = (os.environ.get("B200DP_CONV1_NO_X1", "1") == "1" and self.precision == "tf32" and
                             self.conv1_two_pass and self.fuse_bwd_stats and conv_backend == "tc" and
                             H % 8 == 0 and W % 4 == 0)
+        # ... and run both forward passes on the kind::tf32 kernel that takes the image rows themselves as its MMA
+        # operand (csrc/conv1_hz.cu); "vt" = the bf16 hi/lo vertical-Toeplitz kernel of conv1_tc.cu
+        self.conv1_row_operand = self.conv1_no_x1 and os.environ.get("B200DP_CONV1_FWD", "hz") != "vt"
         self.F = rn.feature_size((H, W))
         self.comm = None           # set by parallel.ddp for data-parallel runs
         self._b = int(batch_size)  # size of the batch currently in the buffers (<= B: short last batch)
@@ -311,7 +314,8 @@ class FusedConvNet:
         if two_pass:
             # fp32 storage: conv1 is cheap on the tensor cores (0.24 ms without its store), its 2.88 GB output is not -
             # a statistics-only pass, then conv + store + BN/ReLU/pool in one epilogue instead of a pass over x1
-            n1 = ops.conv1_stats_tc(x, P["layer1.0.weight"], P["layer1.0.bias"], self.part_c1)
+            n1 = ops.conv1_stats_tc(x, P["layer1.0.weight"], P["layer1.0.bias"], self.part_c1,
+                                    row_operand=self.conv1_row_operand)
         elif self.conv1_backend == "tc" or self.precision == "tf32":
             n1 = ops.conv1_fwd_tc(x, P["layer1.0.weight"], P["layer1.0.bias"], x1, self.part_c1)
         else:
@@ -321,7 +325,8 @@ class FusedConvNet:
                         self.bn_buf[1]["mean"], self.bn_buf[1]["var"], self.bn_buf[1]["nbt"], self.bn1)
         if two_pass:
             ops.conv1_fwd_pool_tc(x, P["layer1.0.weight"], P["layer1.0.bias"], self.bn1, x1, p1, self.part_c1b,
-                                  amask_u8=self.mask1[:B] if self.conv1_no_x1 else None)
+                                  amask_u8=self.mask1[:B] if self.conv1_no_x1 else None,
+                                  row_operand=self.conv1_row_operand)
         else:
             ops.bn_relu_pool(x1, self.bn1, p1)
         if self.conv_backend == "tc":

@@ -150,12 +150,20 @@ def conv1_fwd_tc(x_f32, w1, b1, x1_bf16, partials) -> int:
     return n.value
 
 
-def conv1_stats_tc(x_f32, w1, b1, partials) -> int:
+def conv1_stats_tc(x_f32, w1, b1, partials, row_operand=False) -> int:
     """First pass of the two-pass fp32 layer-1 forward: BatchNorm batch statistics of conv1's output, nothing stored.
-    Returns the number of partial rows."""
+    Returns the number of partial rows.  ``row_operand``: the kind::tf32 kernel whose A operand is the raw image row
+    (csrc/conv1_hz.cu; W % 4 == 0) instead of the bf16 hi/lo vertical-Toeplitz kernel - use the same choice in pass 2."""
     B, H, W = x_f32.shape
     n = c_int(0)
     lib = _lib()
+    if row_operand:
+        lib.b200_conv1_stats_tf32.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int,
+                                              ctypes.POINTER(c_int), c_void_p]
+        _native.check(lib.b200_conv1_stats_tf32(_p(x_f32), _p(w1), _p(b1), _p(partials), B, H, W, ctypes.byref(n),
+                                                _stream()), "conv1_stats_tf32")
+        _count(1)
+        return n.value
     lib.b200_conv1_stats_tc_f32.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int,
                                             ctypes.POINTER(c_int), c_void_p]
     _native.check(lib.b200_conv1_stats_tc_f32(_p(x_f32), _p(w1), _p(b1), _p(partials), B, H, W, ctypes.byref(n), _stream()),
@@ -164,7 +172,7 @@ def conv1_stats_tc(x_f32, w1, b1, partials) -> int:
     return n.value
 
 
-def conv1_fwd_pool_tc(x_f32, w1, b1, bn, x1_f32, p1_f32, partials, amask_u8=None):
+def conv1_fwd_pool_tc(x_f32, w1, b1, bn, x1_f32, p1_f32, partials, amask_u8=None, row_operand=False):
     """Second pass: conv1 again (bit-identical values) with BN-apply + ReLU + 2x2 max-pool fused into the epilogue ->
     ``p1_f32``; replaces conv1_fwd_tc + bn_relu_pool (K3 + K5).  The conv output goes to ``x1_f32`` for the backward -
     or nowhere (``x1_f32=None``) when ``amask_u8`` ([B,H/2,W/2,16] uint8: arg-max | ReLU << 2) is produced for
@@ -172,6 +180,14 @@ def conv1_fwd_pool_tc(x_f32, w1, b1, bn, x1_f32, p1_f32, partials, amask_u8=None
     B, H, W = x_f32.shape
     assert p1_f32.dtype == torch.float32 and (x1_f32 is None or x1_f32.dtype == torch.float32)
     lib = _lib()
+    if row_operand:
+        assert x1_f32 is None and amask_u8 is not None, "the row-operand kernel stores no conv output"
+        assert amask_u8.dtype == torch.uint8 and amask_u8.numel() == p1_f32.numel()
+        lib.b200_conv1_fwd_pool_mask_tf32.argtypes = [c_void_p] * 6 + [c_int, c_int, c_int, c_void_p]
+        _native.check(lib.b200_conv1_fwd_pool_mask_tf32(_p(x_f32), _p(w1), _p(b1), _p(bn), _p(p1_f32), _p(amask_u8),
+                                                        B, H, W, _stream()), "conv1_fwd_pool_mask_tf32")
+        _count(1)
+        return
     if amask_u8 is not None:
         assert amask_u8.dtype == torch.uint8 and amask_u8.numel() == p1_f32.numel()
         lib.b200_conv1_fwd_pool_mask_tc_f32.argtypes = [c_void_p] * 8 + [c_int, c_int, c_int, c_void_p]
