@@ -110,8 +110,8 @@ int b200_fc_bwd(const void* dlogits, const void* p2_bf16, void* W, void* dW_or_n
 /* ------------------------------- fp32 storage / TF32 math ("tf32" mode) --- */
 /* ref: the reference's own numerics - fp32 tensors everywhere, cuDNN convolutions with allow_tf32 (the default),
  * fp32 cuBLAS fc (mnist_distributed.py:28-38, no autocast).  Same contracts as the entry points above with every
- * activation / gradient tensor in fp32 (NHWC); conv2 runs tcgen05.mma.kind::tf32, conv1 forward keeps its bf16
- * hi/lo split (fp32-level products), conv1 weight gradient is kind::tf32 (tc) or exact fp32 FFMA. */
+ * activation / gradient tensor in fp32 (NHWC); conv2 runs tcgen05.mma.kind::tf32, conv1 forward is kind::tf32 too (row-operand
+ * kernel, below) or keeps its bf16 hi/lo split (fp32-level products), conv1 weight gradient is kind::tf32 or exact fp32 FFMA. */
 int b200_conv1_fwd_tc_f32(const void* in_f32, const void* w1, const void* b1, void* x1_f32, void* partials, int B,
                           int H, int W, int* nparts_out, void* stream);
 int b200_bn_relu_pool_f32(const void* x, const void* bn, void* p, int B, int H, int W, int C, void* stream);
@@ -133,6 +133,41 @@ int b200_fc_fwd_f32(const void* p2, const void* W, const void* bias, void* parti
 int b200_fc_bwd_f32(const void* dlogits, const void* p2, void* W, void* dW_or_null, void* dp2, int bt, size_t F,
                     float lr_fused_sgd, int accumulate, float gscale, const void* bn2_or_null,
                     void* bwd_partials_or_null, void* stream);
+
+/* Layer 1 of the tf32 mode without its 2.88 GB conv output (mnist_distributed.py:28-31 forward, its backward inside
+ * loss.backward()).  Two forward passes over the image instead of one over x1:
+ *   b200_conv1_stats_*            BatchNorm batch statistics of conv1(in)+bias, nothing stored
+ *                                 (partials: [b200_conv1_fwd_grid()][32], *nparts_out rows written);
+ *   b200_conv1_fwd_pool_*         conv again (same MMAs in the same order: bit-identical values), BN (bn = [scale 16 |
+ *                                 shift 16 | mean | rstd]) + ReLU + 2x2 max-pool -> p1 [B][H/2][W/2][16]; the _mask_
+ *                                 forms also write one byte per pooled element (arg-max position | ReLU-active << 2)
+ *                                 and take x1 = NULL.
+ * *_tc_f32: bf16 hi/lo vertical-Toeplitz kernel (fp32-level products; may also store x1).
+ * *_tf32:   kind::tf32 kernel whose MMA operand is the image row as TMA delivered it (csrc/conv1_hz.cu; W % 4 == 0,
+ *           input truncated to tf32 by the tensor core as in cuDNN's TF32 convolution; stores no x1).
+ * Use the same family for both passes.  b200_conv1_wgrad_nox1_f32 is the matching weight gradient: dp1 is routed with
+ * the mask bytes on the tensor cores, the dense BatchNorm term comes from the input's 25x25 Gram matrix
+ * (partials: [b200_conv1_wgrad_grid()][b200_conv1_wgrad_nox1_partial()]; H % 8 == 0, W % 4 == 0). */
+int b200_conv1_stats_tc_f32(const void* in_f32, const void* w1, const void* b1, void* partials, int B, int H, int W,
+                            int* nparts_out, void* stream);
+int b200_conv1_fwd_pool_tc_f32(const void* in_f32, const void* w1, const void* b1, const void* bn, void* x1_f32,
+                               void* p1_f32, void* partials, int B, int H, int W, void* stream);
+int b200_conv1_fwd_pool_mask_tc_f32(const void* in_f32, const void* w1, const void* b1, const void* bn,
+                                    void* x1_f32_or_null, void* p1_f32, void* amask_u8, void* partials, int B, int H,
+                                    int W, void* stream);
+int b200_conv1_stats_tf32(const void* in_f32, const void* w1, const void* b1, void* partials, int B, int H, int W,
+                          int* nparts_out, void* stream);
+int b200_conv1_fwd_pool_mask_tf32(const void* in_f32, const void* w1, const void* b1, const void* bn, void* p1_f32,
+                                  void* amask_u8, int B, int H, int W, void* stream);
+int b200_conv1_wgrad_nox1_partial(void);
+int b200_conv1_wgrad_nox1_f32(const void* in_f32, const void* dp1, const void* amask_u8, const void* w1, const void* b1,
+                              const void* bn, const void* red, void* partials, void* dw1, int B, int H, int W,
+                              float gscale, void* stream);
+/* fc backward that publishes its weight gradient slab by slab (ready[slab] counts finished sweeps, release at system
+ * scope) for b200_ar_tile_f32 to all-reduce while later slabs are still being computed.  dtype: 0 bf16, 1 fp32. */
+size_t b200_fc_bwd_tile_slab_floats(int sweeps_per_slab);
+int b200_fc_bwd_tiles(const void* dlogits, const void* p2, void* W, void* dW, void* dp2, int bt, size_t F, float gscale,
+                      const void* bn2, void* bwd_partials, void* ready, int sweeps_per_slab, int dtype, void* stream);
 
 /* ------------------------------------------------------ optimizer (K14) --- */
 /* ref: torch.optim.SGD(model.parameters(), 1e-4).step(), mnist_distributed.py:65,97. */
@@ -176,6 +211,24 @@ int b200_ar_broadcast(void* const* ptrs, void* const* flags, int rank, int world
                       int blocks, uint32_t epoch, void* stream);
 int b200_ar_allgather(void* const* ptrs, void* const* flags, int rank, int world, void* out, size_t bytes, int blocks,
                       uint32_t epoch, void* stream);
+/* Small all-reduce through per-peer push rings (each rank writes its data + flag into every peer's slot; two ring
+ * halves, no trailing barrier): the <= 64 KB path of SymmBackend.all_reduce. */
+int b200_ar_push(void* const* ptrs, void* const* flags, int rank, int world, const void* in, void* out, size_t n,
+                 int dtype, int op, float scale, size_t slot_bytes, int buf, int blocks, uint32_t epoch, void* stream);
+/* One-shot fp32 all-reduce + SGD with a broadcast of bc_floats floats from bc_root folded into the same launch
+ * (the BatchNorm-buffer broadcast DDP does before each forward). */
+int b200_ar_oneshot_f32x4_bcast(void* const* ptrs, void* const* flags, int rank, int world, void* out, void* param,
+                                size_t n, float scale, float lr, int blocks, uint32_t epoch, void* stream,
+                                void* const* bc_ptrs, size_t bc_floats, int bc_root);
+/* Tile-driven one-pass all-reduce + SGD of the fc weight gradient: consumes the slab counters b200_fc_bwd_tiles
+ * publishes (rdy[r] = rank r's counters), reduces each slab as soon as every rank has produced it. */
+int b200_ar_tile_f32(void* const* ptrs, void* mc, void* const* flags, void* const* wptrs, void* wmc, void* const* rdy,
+                     int rank, int world, int rows, size_t F, size_t slab_floats, uint32_t target, float scale, float lr,
+                     int blocks, uint32_t epoch, void* stream);
+/* NVLink topology of `device` from NVML (dlopen): active links, links that end at an NVSwitch, per-peer direct links
+ * (peer_links[cap]), per-link GB/s, multicast capability. */
+int b200_nvlink_report(int device, int* links_active, int* links_to_switch, int* peer_links, int cap, int* link_gbs,
+                       int* multicast);
 
 /* =========================================================== host library === */
 /* ref: the TCPStore behind env:// rendezvous, test_init.py:76-91 (D2). */

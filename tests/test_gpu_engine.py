@@ -148,8 +148,10 @@ def test_tf32_engine_matches_pure_fp32_model():
             # Parameters whose gradient is a BatchNorm-backward sum with heavy cancellation (conv weights, BN-1, BN-2
             # beta) amplify the 2^-11 TF32 operand rounding to ~1e-2: torch's own cuDNN TF32 path shows 1e-2 .. 6e-2
             # on the same quantities at this shape (profiles/precision_error_vs_cudnn_tf32.txt); the rest is tight.
+            # Layer 1 runs kind::tf32 as well (csrc/conv1_hz.cu, input truncated to tf32 as in cuDNN): a flipped
+            # near-tie of the max-pool moves a gradient value by one pixel; cuDNN's TF32 path: 2.4e-2 .. 5.3e-2 there.
             loose = k.startswith("layer1") or k in ("layer2.0.weight", "layer2.1.bias")
-            assert e < (3e-2 if loose else 2e-3), f"grad {k}: {e}"
+            assert e < ((6e-2 if k.startswith("layer1") else 3e-2) if loose else 2e-3), f"grad {k}: {e}"
     sd, sd_ref = eng.state_dict(), ref.state_dict()
     for k in sd_ref:
         if k.endswith("num_batches_tracked"):

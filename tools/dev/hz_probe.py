@@ -33,3 +33,9 @@ for ro in (True, False):
     t1 = timeit(lambda: ops.conv1_stats_tc(x, w, b, part, row_operand=ro))
     t2 = timeit(lambda: ops.conv1_fwd_pool_tc(x, w, b, bn, None, p1, part, amask_u8=mask, row_operand=ro))
     print(f"row_operand={ro}: stats {t1:.3f} ms, pool+mask {t2:.3f} ms")
+big = torch.empty(B, S // 2, S // 2, 32, device=dev)
+t = timeit(lambda: p1.fill_(1.0)); print(f"fill 720 MB: {t:.3f} ms = {0.72 / t:.2f} TB/s")
+t = timeit(lambda: big.fill_(1.0)); print(f"fill 1440 MB: {t:.3f} ms = {1.44 / t:.2f} TB/s")
+t = timeit(lambda: p1.copy_(big[..., :16].contiguous() if False else p1)); 
+src = torch.empty_like(p1)
+t = timeit(lambda: p1.copy_(src)); print(f"copy 720 MB -> 720 MB: {t:.3f} ms = {1.44 / t:.2f} TB/s")
