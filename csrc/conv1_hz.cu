@@ -157,30 +157,47 @@ conv1_hz_kernel(const __grid_constant__ CUtensorMap tm_in, const __grid_constant
     const uint64_t a_pair = smem_desc_noswz(0, hz::kRowBytes, 128);      // chunk 2 of rows d, d+1
     const uint64_t b_tmpl = smem_desc_noswz(smem_u32(s_w), 2048, 128);
     const uint32_t ring16 = smem_u32(s_ring) >> 4;
-    // no divisions, no per-MMA address arithmetic beyond three slot bases: this one thread is the kernel's critical path
-    uint32_t a = 0, q = 0;
-    int yp = begin % g.nyp;
-    for (int item = begin; item < end; ++item, ++q) {
-      const bool last = item + 1 == end || yp + 1 == g.nyp;
-      if ((q & 1) == mine) {
-      // (the two older row pairs were first waited for by the other warp: every warp observes the phases itself)
-      mbar_wait(&rfull[a % hz::kSlots], (a / hz::kSlots) & 1);
-      mbar_wait(&rfull[(a + 1) % hz::kSlots], ((a + 1) / hz::kSlots) & 1);
-      mbar_wait(&rfull[(a + 2) % hz::kSlots], ((a + 2) / hz::kSlots) & 1);
-      const uint32_t ts = q % hz::kTStages;
-      mbar_wait(&tempty[ts], ((q / hz::kTStages) & 1) ^ 1);
+    // The issuing thread is the kernel's critical path: every mbarrier wait costs it ~100 cycles even when the phase
+    // has long completed, and the tensor pipe only covers what is already queued.  So: no divisions, three slot bases
+    // per item, and the waits of the warp's NEXT item sit between the fifth and sixth MMA of the current one, where
+    // the queue is full anyway.  A row pair this warp waited for two items ago is not waited for again.
+    auto step = [&](uint32_t& a_, int& yp_) {
+      const bool last_ = yp_ + 1 == g.nyp;
+      a_ += last_ ? 3u : 1u;
+      yp_ = last_ ? 0 : yp_ + 1;
+    };
+    auto wait_item = [&](uint32_t a_, uint32_t q_, int yp_, int item_) {
+      if (yp_ < 2 || item_ - begin < 2) mbar_wait(&rfull[a_ % hz::kSlots], (a_ / hz::kSlots) & 1);
+      mbar_wait(&rfull[(a_ + 1) % hz::kSlots], ((a_ + 1) / hz::kSlots) & 1);
+      mbar_wait(&rfull[(a_ + 2) % hz::kSlots], ((a_ + 2) / hz::kSlots) & 1);
+      mbar_wait(&tempty[q_ % hz::kTStages], ((q_ / hz::kTStages) & 1) ^ 1);
       tc_fence_after();
+    };
+    uint32_t a = 0, q = mine;
+    int yp = begin % g.nyp, item = begin + (int)mine;
+    if (mine) step(a, yp);
+    if (item < end) wait_item(a, q, yp, item);
+    for (; item < end; item += 2, q += 2) {
+      const uint32_t ts = q % hz::kTStages;
+      const uint32_t dcol = tmem_base + ts * 128;
+      const uint64_t sb0 = ring16 + (a % hz::kSlots) * (hz::kSlotBytes >> 4);
+      const uint64_t sb1 = ring16 + ((a + 1) % hz::kSlots) * (hz::kSlotBytes >> 4);
+      const uint64_t sb2 = ring16 + ((a + 2) % hz::kSlots) * (hz::kSlotBytes >> 4);
+      constexpr uint64_t kRow = hz::kRowBytes >> 4, kW = 4096 >> 4;
       if (elect_one()) {
-        const uint32_t dcol = tmem_base + ts * 128;
-        const uint64_t sb0 = ring16 + (a % hz::kSlots) * (hz::kSlotBytes >> 4);
-        const uint64_t sb1 = ring16 + ((a + 1) % hz::kSlots) * (hz::kSlotBytes >> 4);
-        const uint64_t sb2 = ring16 + ((a + 2) % hz::kSlots) * (hz::kSlotBytes >> 4);
-        constexpr uint64_t kRow = hz::kRowBytes >> 4, kW = 4096 >> 4;
         umma_tf32(dcol, a_row + sb0, b_tmpl, idesc, 0u);
         umma_tf32(dcol, a_row + sb0 + kRow, b_tmpl + kW, idesc, 1u);
         umma_tf32(dcol, a_row + sb1, b_tmpl + 2 * kW, idesc, 1u);
         umma_tf32(dcol, a_row + sb1 + kRow, b_tmpl + 3 * kW, idesc, 1u);
         umma_tf32(dcol, a_row + sb2, b_tmpl + 4 * kW, idesc, 1u);
+      }
+      __syncwarp();
+      uint32_t a2 = a;
+      int yp2 = yp;
+      step(a2, yp2);
+      step(a2, yp2);
+      if (item + 2 < end) wait_item(a2, q + 2, yp2, item + 2);
+      if (elect_one()) {
         umma_tf32(dcol, a_row + sb2 + kRow, b_tmpl + 5 * kW, idesc, 1u);
         umma_tf32(dcol, a_pair + sb0 + 2, b_tmpl + 6 * kW, idesc, 1u);
         umma_tf32(dcol, a_pair + sb1 + 2, b_tmpl + 7 * kW, idesc, 1u);
@@ -188,9 +205,8 @@ conv1_hz_kernel(const __grid_constant__ CUtensorMap tm_in, const __grid_constant
         umma_commit(&tfull[ts]);     // the only commit: the epilogue hands the ring slots back (every tcgen05 instruction
       }                              // of this thread queues behind the MMAs)
       __syncwarp();
-      }
-      a += last ? 3u : 1u;
-      yp = (yp + 1 == g.nyp) ? 0 : yp + 1;
+      a = a2;
+      yp = yp2;
     }
   } else if (warp == 1) {
     // ================= TMA producer: two new input rows per item (six at the top of a column strip) =================
