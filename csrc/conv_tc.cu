@@ -614,7 +614,7 @@ conv5x5_rs_kernel(const __grid_constant__ CUtensorMap tm_act, const ET* __restri
         }
       }
     } else if (lane == 0) {
-      uint32_t gcount = 0;
+      uint32_t gcount = 0, qbase = 0;
       for (int item = blockIdx.x; item < g.nitems; item += gridDim.x) {
         const int seg = item % g.nseg;
         const int strip = (item / g.nseg) % g.nstrips;
@@ -623,6 +623,15 @@ conv5x5_rs_kernel(const __grid_constant__ CUtensorMap tm_act, const ET* __restri
         const int rows = min(g.rseg, g.H - y0);
         const int x0 = strip * kBM;
         for (int i = 0; i < rows + 4; ++i, ++gcount) {
+          if constexpr (SWZ) {
+            // The input row that opens output row i is not fetched before that row's accumulator has been drained:
+            // the issuing thread then needs no wait of its own for it (each mbarrier wait costs that thread, the one
+            // serial role of the kernel, ~100 cycles even when the phase completed long ago; here it is free).
+            if (i < rows) {
+              const uint32_t qn = qbase + (uint32_t)i;
+              mbar_wait(&tempty[qn % RT], ((qn / RT) & 1) ^ 1);
+            }
+          }
           const uint32_t slot = gcount % Cfg::kSlots, use = gcount / Cfg::kSlots;
           mbar_wait(&empty[slot], (use & 1) ^ 1);
           mbar_expect_tx(&full[slot], Cfg::kSlotBytes);
@@ -635,6 +644,7 @@ conv5x5_rs_kernel(const __grid_constant__ CUtensorMap tm_act, const ET* __restri
               tma_load_5d(dst + p * kPlaneBytes, &tm_act, &full[slot], 0, p, x0 - 2, y0 - 2 + i, b);
           }
         }
+        qbase += rows;
       }
     }
   } else if (warp == 1) {
@@ -661,7 +671,7 @@ conv5x5_rs_kernel(const __grid_constant__ CUtensorMap tm_act, const ET* __restri
       for (int i = 0; i < rows + 4; ++i, ++gcount) {
         const int jj_lo = max(0, 4 - i), jj_hi = min(4, rows + 3 - i);     // output row j = i-4+jj in [0, rows)
         const bool starts_row = i < rows;                                  // block jj=4 opens output row i
-        if (starts_row) {
+        if (!SWZ && starts_row) {               // SWZ: implied by the row's full barrier (the feed waited for it)
           const uint32_t qn = qbase + i;
           mbar_wait(&tempty[qn % RT], ((qn / RT) & 1) ^ 1);
         }
@@ -715,7 +725,9 @@ conv5x5_rs_kernel(const __grid_constant__ CUtensorMap tm_act, const ET* __restri
             }
           }
           }
-          umma_commit(&empty[slot]);                                        // this input row is consumed
+          // SWZ: one commit per row - the epilogue, which learns from tfull(j) that input rows <= j+4 are consumed,
+          // hands the slots back (every tcgen05 instruction of this thread queues behind its MMAs)
+          if (!SWZ) umma_commit(&empty[slot]);                              // this input row is consumed
           if (i >= 4) umma_commit(&tfull[(qbase + (uint32_t)(i - 4)) % RT]);  // output row i-4 is complete
         }
         __syncwarp();
@@ -740,7 +752,8 @@ conv5x5_rs_kernel(const __grid_constant__ CUtensorMap tm_act, const ET* __restri
         kB[c] = -(s_bnp[c] * inv + s_bnp[2 * COUT + c]) * rs;
       }
     }
-    uint32_t q = 0;
+    uint32_t q = 0, gbase = 0;                    // gbase: input rows fed before this item
+    const bool leader = (ew & 3) == 0 && lane == 0;
     for (int item = blockIdx.x; item < g.nitems; item += gridDim.x) {
       const int seg = item % g.nseg;
       const int strip = (item / g.nseg) % g.nstrips;
@@ -749,6 +762,8 @@ conv5x5_rs_kernel(const __grid_constant__ CUtensorMap tm_act, const ET* __restri
       const int rows = min(g.rseg, g.H - y0);
       const int x = strip * kBM + m;
       const bool valid = x < g.W;
+      const uint32_t gitem = gbase;
+      gbase += (uint32_t)rows + 4u;
       for (int j = 0; j < rows; ++j, ++q) {
         if ((int)(q & 1u) != grp) continue;
         const uint32_t stage = q % RT, use = q / RT;
@@ -762,6 +777,15 @@ conv5x5_rs_kernel(const __grid_constant__ CUtensorMap tm_act, const ET* __restri
         }
         mbar_wait(&tfull[stage], use & 1);
         tc_fence_after();
+        if constexpr (SWZ) {
+          if (leader) {      // output row j complete => input rows 0 .. j+4 of the item have been read by their MMAs
+            if (j == 0) {
+#pragma unroll
+              for (uint32_t k = 0; k < 4; ++k) mbar_arrive(&empty[(gitem + k) % Cfg::kSlots]);
+            }
+            mbar_arrive(&empty[(gitem + (uint32_t)j + 4u) % Cfg::kSlots]);
+          }
+        }
         const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + stage * COUT;
         uint32_t v[COUT];
 #pragma unroll
@@ -1251,7 +1275,9 @@ conv5x5_wgrad_tf32_kernel(const __grid_constant__ CUtensorMap tm_dxo, const floa
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < wt::kSlotsA; ++i) { mbar_init(&fullA[i], 32); mbar_init(&emptyA[i], 1); }
-    for (int i = 0; i < wt::kSlotsB; ++i) { mbar_init(&fullB[i], TMAB ? 1 : 32); mbar_init(&emptyB[i], 1); }
+    // fullB[row]: the dx2 row (TMA: 1 arrival + bytes, cp.async: 32) AND the act row fed in the same iteration (32
+    // arrivals) - the issuing thread waits for one barrier per output row, not two
+    for (int i = 0; i < wt::kSlotsB; ++i) { mbar_init(&fullB[i], TMAB ? 33 : 64); mbar_init(&emptyB[i], 1); }
     mbar_init(done, 1);
     mbar_fence_init();
     if (TMAB) tma_prefetch_desc(&tm_dxo);
@@ -1267,7 +1293,7 @@ conv5x5_wgrad_tf32_kernel(const __grid_constant__ CUtensorMap tm_dxo, const floa
     //              act: one instruction = 8 pixels x 4 pieces (512 contiguous bytes), written to half h of atom j.
     const int bp = lane >> 3, bq = lane & 7;           // dx2: pixel-in-group, 16-byte piece (unit = bq >> 1)
     const int ap = lane >> 2, aq = lane & 3;           // act: pixel-in-group, 16-byte piece of the 64-byte pixel
-    uint32_t ga = 0, gb = 0;
+    uint32_t ga = 0, gb = 0, xb_mine = 0;
     for (int item = blockIdx.x; item < g.nitems; item += gridDim.x) {
       const int seg = item % g.nseg;
       const int strip = (item / g.nseg) % g.nstrips;
@@ -1275,7 +1301,9 @@ conv5x5_wgrad_tf32_kernel(const __grid_constant__ CUtensorMap tm_dxo, const floa
       const int r0 = seg * g.rseg;
       const int rows = min(g.rseg, g.H - r0);
       const int x0 = strip * wt::kSP;
+      const uint32_t gb0 = gb;                           // dx2-row counter at the start of the item
       for (int i = 0; i < rows + 4; ++i) {
+        const uint32_t slotb = gb % wt::kSlotsB;
         if constexpr (TMAB) {
           const uint32_t slot = gb % wt::kSlotsB, use = gb / wt::kSlotsB;
           if (lane == 0) {
@@ -1307,8 +1335,14 @@ conv5x5_wgrad_tf32_kernel(const __grid_constant__ CUtensorMap tm_dxo, const floa
           ++gb;
         }
         if (i >= 4) {
-          const uint32_t slot = ga % wt::kSlotsA, use = ga / wt::kSlotsA;
-          mbar_wait(&emptyA[slot], (use & 1) ^ 1);
+          // An act slot is free when the MMAs of the output row it served have completed - which is what the commit on
+          // that row's OLDEST dx2 slot (index xb) already says, so the issuing thread makes one commit per row, not two.
+          // Lane s keeps xb of act slot s.  If the feed has since refilled that dx2 slot it has seen the phase complete.
+          const uint32_t slot = ga % wt::kSlotsA;
+          const uint32_t xb_old = __shfl_sync(0xffffffffu, xb_mine, (int)slot);
+          if (ga >= (uint32_t)wt::kSlotsA && xb_old + (uint32_t)wt::kSlotsB >= gb)
+            mbar_wait(&emptyB[xb_old % wt::kSlotsB], (xb_old / wt::kSlotsB) & 1);
+          if (lane == (int)slot) xb_mine = gb0 + (uint32_t)(i - 4);
           const int y = r0 + i - 4;                                            // always inside the image
           const char* row = reinterpret_cast<const char*>(act) + ((int64_t)b * g.H + y) * g.W * 64;
           uint8_t* dst = s_a + slot * wt::kSlotA;
@@ -1323,8 +1357,10 @@ conv5x5_wgrad_tf32_kernel(const __grid_constant__ CUtensorMap tm_dxo, const floa
                          row + (int64_t)(nbytes ? x : 0) * 64 + aq * 16, nbytes);
             }
           }
-          cp_async_mbar_arrive_noinc(&fullA[slot]);
+          cp_async_mbar_arrive_noinc(&fullB[slotb]);      // lands with this iteration's dx2 row: output row i-4 is ready
           ++ga;
+        } else {
+          mbar_arrive(&fullB[slotb]);                     // no act row in the first four iterations of an item
         }
       }
     }
@@ -1345,8 +1381,7 @@ conv5x5_wgrad_tf32_kernel(const __grid_constant__ CUtensorMap tm_dxo, const floa
           const uint32_t gc = gbase + i + k;
           mbar_wait(&fullB[gc % wt::kSlotsB], (gc / wt::kSlotsB) & 1);
         }
-        const uint32_t slotA = ga % wt::kSlotsA;
-        mbar_wait(&fullA[slotA], (ga / wt::kSlotsA) & 1);
+        const uint32_t slotA = ga % wt::kSlotsA;          // its act row arrived on the newest dx2 row's barrier
         tc_fence_after();
         const uint32_t s0 = (gbase + i) % wt::kSlotsB;
         const uint32_t arow = a_base + slotA * (wt::kSlotA >> 4);
@@ -1357,8 +1392,7 @@ conv5x5_wgrad_tf32_kernel(const __grid_constant__ CUtensorMap tm_dxo, const floa
           for (int kb = 0; kb < wt::kKSteps; ++kb)       // 8 pixels = 1 KB further down every atom
             umma_tf32(tmem_base, ((uint64_t)a_hi << 32) | (uint64_t)(arow + kb * 64),
                       ((uint64_t)b_hi << 32) | (uint64_t)(brow + kb * 64), idesc, kb == 0 ? acc0 : 1u);
-          umma_commit(&emptyA[slotA]);
-          umma_commit(&emptyB[(gbase + i) % wt::kSlotsB]);
+          umma_commit(&emptyB[(gbase + i) % wt::kSlotsB]);     // frees the oldest dx2 row AND this row's act slot (feed)
         }
         __syncwarp();
         first = 0;
