@@ -105,9 +105,13 @@ class FusedConvNet:
         self.conv1_no_x1 = (os.environ.get("B200DP_CONV1_NO_X1", "1") == "1" and self.precision == "tf32" and
                             self.conv1_two_pass and self.fuse_bwd_stats and conv_backend == "tc" and
                             H % 8 == 0 and W % 4 == 0)
-        # ... and run both forward passes on the kind::tf32 kernel that takes the image rows themselves as its MMA
-        # operand (csrc/conv1_hz.cu); "vt" = the bf16 hi/lo vertical-Toeplitz kernel of conv1_tc.cu
-        self.conv1_row_operand = self.conv1_no_x1 and os.environ.get("B200DP_CONV1_FWD", "hz") != "vt"
+        # Layer-1 forward kernels of the two-pass path.  "vt" (default): bf16 hi/lo vertical-Toeplitz kernel, fp32-level
+        # products - what the reference effectively computes at 3000x3000, where cuDNN picks fp32 algorithms.  "hz": the
+        # kind::tf32 kernel that takes the image rows themselves as its MMA operand (csrc/conv1_hz.cu), 0.29 ms faster per
+        # step; a 2^-11 operand rounding in THIS conv is amplified by the BatchNorm-backward cancellation to tens of percent
+        # in single-step conv-weight gradients at >= 1000x1000 (profiles/precision_error_vs_cudnn_tf32.txt), loss curves
+        # are unaffected (profiles/convergence_3000_lr1e-6_hz.txt) - so it is the opt-in.
+        self.conv1_row_operand = self.conv1_no_x1 and os.environ.get("B200DP_CONV1_FWD", "vt") == "hz"
         self.F = rn.feature_size((H, W))
         self.comm = None           # set by parallel.ddp for data-parallel runs
         self._b = int(batch_size)  # size of the batch currently in the buffers (<= B: short last batch)
