@@ -108,7 +108,7 @@ def main():
         log(f"reference  batch {b:3d}: {'fits' if ok else 'OOM '}  peak {peak:5.1f} GiB")
         if not ok:
             break
-    for prec, batches in (("bf16", (64, 128, 256, 288)), ("tf32", (64, 128, 144))):
+    for prec, batches in (("bf16", (64, 128, 256, 288)), ("tf32", (64, 128, 256, 288))):
         for b in batches:
             ok, peak, ms = try_engine(b, timeit=True, precision=prec)
             log(f"b200dp {prec} batch {b:3d}: {'fits' if ok else 'OOM '}  peak {peak:5.1f} GiB" +
