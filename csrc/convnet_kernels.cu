@@ -424,23 +424,31 @@ pool_bn_bwd_kernel(const T* __restrict__ x, const T* __restrict__ dp,
 __global__ void bn_bwd_finalize_kernel(const float* __restrict__ partials, int nparts, int C, double count,
                                        float* __restrict__ red, float* __restrict__ dgamma,
                                        float* __restrict__ dbeta, float gscale) {
-  const int c = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  if (c >= C) return;
-  double s = 0.0, q = 0.0;
-  for (int i = lane; i < nparts; i += 32) {
-    s += (double)partials[(size_t)i * 2 * C + c];
-    q += (double)partials[(size_t)i * 2 * C + C + c];
+  // thread = (row group, column of the [nparts][2C] partial matrix): every load of a warp is one contiguous row
+  // piece (a warp per channel striding over rows touched 32 lines per load: 24 us for 1184 rows)
+  __shared__ double s_acc[1024];
+  const int ncol = 2 * C, ngrp = (int)blockDim.x / ncol;
+  const int col = (int)threadIdx.x % ncol, grp = (int)threadIdx.x / ncol;
+  double a0 = 0.0, a1 = 0.0;
+  int i = grp;
+  for (; i + ngrp < nparts; i += 2 * ngrp) {
+    a0 += (double)partials[(size_t)i * ncol + col];
+    a1 += (double)partials[(size_t)(i + ngrp) * ncol + col];
   }
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) {
-    s += __shfl_xor_sync(0xffffffffu, s, o);
-    q += __shfl_xor_sync(0xffffffffu, q, o);
-  }
-  if (lane == 0) {
-    red[c] = (float)(s / count);
-    red[C + c] = (float)(q / count);
-    dgamma[c] = (float)(q * (double)gscale);
-    dbeta[c] = (float)(s * (double)gscale);
+  if (i < nparts) a0 += (double)partials[(size_t)i * ncol + col];
+  s_acc[threadIdx.x] = a0 + a1;
+  __syncthreads();
+  if ((int)threadIdx.x < ncol) {
+    double t = 0.0;
+    for (int g2 = 0; g2 < ngrp; ++g2) t += s_acc[g2 * ncol + threadIdx.x];
+    const int c = (int)threadIdx.x % C;
+    if ((int)threadIdx.x < C) {
+      red[c] = (float)(t / count);
+      dbeta[c] = (float)(t * (double)gscale);
+    } else {
+      red[C + c] = (float)(t / count);
+      dgamma[c] = (float)(t * (double)gscale);
+    }
   }
 }
 
@@ -1077,8 +1085,8 @@ B200_API int b200_pool_bn_bwd_f32(const void* x, const void* dp, const void* bn,
 
 B200_API int b200_bn_bwd_finalize(const void* partials, int nparts, int C, double count, void* red,
                                   void* dgamma, void* dbeta, float gscale, void* stream) {
-  B200_CHECK(C <= 32, "bn_bwd_finalize: C must be <= 32");
-  bn_bwd_finalize_kernel<<<1, 32 * C, 0, (cudaStream_t)stream>>>((const float*)partials, nparts, C, count,
+  B200_CHECK(C >= 1 && C <= 32 && 1024 % (2 * C) == 0, "bn_bwd_finalize: C must divide 512 and be <= 32");
+  bn_bwd_finalize_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>((const float*)partials, nparts, C, count,
                                                                   (float*)red, (float*)dgamma, (float*)dbeta, gscale);
   B200_LAUNCH_CHECK();
   return 0;

@@ -276,3 +276,32 @@ def test_checkpoint_loads_into_the_installed_reference_convnet(tmp_path):
     want = model(x.to(DEV))                                  # train mode: batch statistics, like the engine
     got = eng.forward(x.to(DEV))
     assert rel(got, want) < 2e-3, rel(got, want)
+
+
+def test_graphed_step_equals_eager_step(monkeypatch):
+    """The single-GPU training step replayed as one CUDA graph (engine._train_step_graphed) is bit-identical to the same
+    steps launched one kernel at a time, counts its kernels, and survives a short batch in between."""
+    from torch_distributed_sandbox_b200 import ops
+    from torch_distributed_sandbox_b200.models.engine import FusedConvNet
+    from torch_distributed_sandbox_b200.data.mnist import synthetic_digits
+    shape, B, steps = (64, 96), 4, 7
+    imgs, labs = synthetic_digits(B * steps, seed=9)
+    imgs = torch.from_numpy(imgs).view(steps, B, 28, 28).to(DEV)
+    labs = torch.from_numpy(labs.astype("int64")).view(steps, B).to(DEV)
+    out = {}
+    for mode in ("0", "1"):
+        monkeypatch.setenv("B200DP_CUDA_GRAPH", mode)
+        eng = FusedConvNet(shape, batch_size=B, device=DEV, lr=1e-3, seed=0, precision="tf32")
+        losses, l0 = [], ops.LAUNCHES
+        for s in range(steps):
+            if s == 4:      # a short batch in the middle: eager (its own key has not warmed up), same buffers
+                losses.append(float(eng.train_step(imgs[s, :3], labs[s, :3])))
+            else:
+                losses.append(float(eng.train_step(imgs[s], labs[s])))
+        out[mode] = (losses, {k: v.clone() for k, v in eng.state_dict().items()}, ops.LAUNCHES - l0,
+                     sum(1 for g in eng._graphs.values() if g[0] is not None))
+    assert out["1"][3] == 1 and out["0"][3] == 0          # one captured graph (the full batch), none when disabled
+    assert out["0"][0] == out["1"][0], (out["0"][0], out["1"][0])
+    for k, v in out["0"][1].items():
+        assert torch.equal(v, out["1"][1][k]), k
+    assert out["0"][2] == out["1"][2] > 0                 # replayed kernels are counted

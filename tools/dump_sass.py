@@ -4,7 +4,7 @@ import os, re, subprocess, sys, collections
 root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 out = os.path.join(root, "profiles", "sass")
 os.makedirs(out, exist_ok=True)
-KEEP = re.compile(r"conv1_fwd_tc_kernel|conv1_wgrad_tc_kernel|conv1_wgrad_tf32_kernel|conv1_wgrad_tf32_tma_kernel|conv1_wgrad_nox1|conv5x5_rs_kernel.*Lb0E(f|13__nv_bfloat16)Lb1EE|"
+KEEP = re.compile(r"conv1_fwd_tc_kernel|conv1_hz_kernel|conv1_wgrad_tc_kernel|conv1_wgrad_tf32_kernel|conv1_wgrad_tf32_tma_kernel|conv1_wgrad_nox1|conv5x5_rs_kernel.*Lb0E(f|13__nv_bfloat16)Lb1EE|"
                   r"conv5x5_wgrad_rep_kernelI13|conv5x5_wgrad_tf32_kernel|bn_relu_pool_kernel|pool_bn_bwd_kernelILi32ELi1E|"
                   r"fc_fwd_kernelILi5E|fc_bwd_kernelILi5E|fc_bwd_anybatch|fc_reduce|ce_kernel|bn_finalize|bn_bwd_finalize|"
                   r"reduce_partials|sgd_kernel|resize_pil|allreduce_nvls_f32_excl|allreduce_tile_f32_kernelILb1|allreduce_tile_f32_kernelILb0|"

@@ -114,6 +114,8 @@ class FusedConvNet:
         self.conv1_row_operand = self.conv1_no_x1 and os.environ.get("B200DP_CONV1_FWD", "vt") == "hz"
         self.F = rn.feature_size((H, W))
         self.comm = None           # set by parallel.ddp for data-parallel runs
+        self._graph_enabled = os.environ.get("B200DP_CUDA_GRAPH", "1") == "1"
+        self._graphs = {}          # (batch, src h, src w, lr, grad scale) -> (CUDAGraph | None, launches | eager count, key)
         self._b = int(batch_size)  # size of the batch currently in the buffers (<= B: short last batch)
         self._fc_fused_done = False
         self._fc_pending = False
@@ -204,6 +206,7 @@ class FusedConvNet:
                        bn_flat: Optional[torch.Tensor] = None, small_grad: Optional[torch.Tensor] = None) -> None:
         """Move fc.weight / its gradient / the BN buffer blob into caller-provided storage
         (symmetric memory under DDP); current values are preserved."""
+        self._graphs.clear()                # captured steps address the old storage
         if fcw is not None:
             fcw = fcw.view(10, self.F)
             fcw.copy_(self.fcw)
@@ -211,6 +214,7 @@ class FusedConvNet:
         if fcw_grad is not None:
             self.fcw_grad = fcw_grad.view(10, self.F)
         if small_grad is not None:
+            small_grad.zero_()      # the conv-bias slots are never written again (analytically zero gradients)
             self.small_grad = small_grad
             off = 0
             for name, shape in SMALL_LAYOUT:
@@ -292,6 +296,7 @@ class FusedConvNet:
                                    torch.from_numpy(pil_bilinear_table(sh, self.H)).to(self.device))
             if self._u8 is None or self._u8.shape[1:] != images.shape[1:]:
                 self._u8 = torch.empty((self.B,) + tuple(images.shape[1:]), device=self.device, dtype=torch.uint8)
+                self._graphs.clear()        # captured steps read the old staging buffer
             self._u8[:b].copy_(images, non_blocking=True)
             xt, yt = self._tabs[key]
             ops.resize_pil_bilinear(self._u8[:b], xt, yt, self.x[:b])
@@ -415,7 +420,9 @@ class FusedConvNet:
                 ops.conv2_dgrad_tc(dx2, P["layer2.0.weight"], dp1)
         else:
             self._conv2_bwd_torch(gs)
-        G["layer2.0.bias"].zero_()      # a bias feeding BatchNorm has an analytically zero gradient
+            G["layer2.0.bias"].zero_()
+        # a bias feeding BatchNorm has an analytically zero gradient: its slot of the gradient buffer is zeroed once, when
+        # the buffer is created, and no native kernel writes it (two fill launches per step less)
         # ---- layer 1
         if fuse_stats:
             ops.bn_bwd_finalize(self.part_bwd, n1, 16, B * H * W, self.red1, G["layer1.1.weight"],
@@ -430,7 +437,6 @@ class FusedConvNet:
         else:
             wg1 = ops.conv1_wgrad_tc if self.conv1_backend == "tc" else ops.conv1_wgrad
             wg1(x, x1, dp1, self.bn1, self.red1, self.part_wg1, G["layer1.0.weight"], gs)
-        G["layer1.0.bias"].zero_()
 
     def step(self) -> None:
         """SGD (lr, no momentum / weight decay: mnist_onegpu.py:49) on every parameter.  Under DDP the
@@ -455,6 +461,8 @@ class FusedConvNet:
 
     def train_step(self, images: torch.Tensor, labels: torch.Tensor) -> torch.Tensor:
         if not trace.nvtx_enabled():
+            if self._graph_enabled and self.comm is None and images.dtype == torch.uint8:
+                return self._train_step_graphed(images, labels)
             self.forward(images)
             self.loss_backward(labels)
             self.step()
@@ -465,6 +473,66 @@ class FusedConvNet:
             self.loss_backward(labels)
         with trace.nvtx_range("b200dp.optimizer"):
             self.step()
+        return self.loss
+
+    # ------------------------------------------------------------ CUDA graph --
+    def _step_body(self, b: int, key) -> None:
+        """The whole step on static buffers: resize of the staged digits, forward, loss, backward, SGD."""
+        xt, yt = self._tabs[key]
+        ops.resize_pil_bilinear(self._u8[:b], xt, yt, self.x[:b])
+        self.forward()
+        ops.cross_entropy(self.logits[:b], self._labels[:b], self.loss, self.dlogits[:b], self.grads["fc.bias"],
+                          self.grad_scale)
+        self._backward(allow_fused_sgd=True)
+        self.step()
+
+    def _train_step_graphed(self, images: torch.Tensor, labels: torch.Tensor) -> torch.Tensor:
+        """Single-GPU step as ONE graph launch (the ~20 kernels of a step on static buffers; the step's inputs are
+        copied into the staging tensors first).  A step that follows a host synchronisation - every end-to-end step
+        does: the loss is read back - otherwise starts with the GPU idle while Python issues the launches one by one.
+        Two eager steps per (batch, source size, lr) come first; a failed capture disables the path for good.
+        (Under DDP the collectives carry a per-step epoch argument, so those steps stay eager.)"""
+        if images.dim() == 4:
+            images = images[:, 0]
+        b = int(images.shape[0])
+        gkey = (b, int(images.shape[-2]), int(images.shape[-1]), float(self.lr), float(self.grad_scale))
+        ent = self._graphs.get(gkey)
+        if ent is None or ent[0] is None:
+            n = 0 if ent is None else ent[1]
+            if n < 2 or not (1 <= b <= self.B):
+                self._graphs[gkey] = (None, n + 1)
+                self.forward(images)
+                self.loss_backward(labels)
+                self.step()
+                return self.loss
+            key = (int(images.shape[-2]), int(images.shape[-1]))
+            try:
+                self._u8[:b].copy_(images, non_blocking=True)
+                self._labels[:b].copy_(labels, non_blocking=True)
+                self._b = b
+                torch.cuda.current_stream().synchronize()
+                graph = torch.cuda.CUDAGraph()
+                l0 = ops.LAUNCHES
+                with torch.cuda.graph(graph):
+                    self._step_body(b, key)
+                ent = (graph, ops.LAUNCHES - l0, key)
+                ops._count(-(ops.LAUNCHES - l0))          # capture launched nothing
+                self._graphs[gkey] = ent
+            except Exception as e:                        # noqa: BLE001 - any capture failure: stay eager
+                self._graph_enabled = False
+                import warnings
+                warnings.warn(f"b200dp: CUDA-graph capture of the training step failed ({e}); running eagerly")
+                self.forward(images)
+                self.loss_backward(labels)
+                self.step()
+                return self.loss
+        graph, nlaunch, _ = ent
+        assert labels.shape[0] == b, f"{labels.shape[0]} labels for a batch of {b}"
+        self._b = b
+        self._u8[:b].copy_(images, non_blocking=True)
+        self._labels[:b].copy_(labels, non_blocking=True)
+        graph.replay()
+        ops._count(nlaunch)                               # the kernels of the replayed step
         return self.loss
 
     __call__ = forward
