@@ -512,6 +512,43 @@ allreduce_nvls_bf16_kernel(Peers P, size_t n16, float scale, uint32_t epoch) {
   sys_barrier(P, epoch + 1);
 }
 
+// DDP bucket exchanged in bf16 (ref: torch DDP's bf16_compress_hook on top of mnist_distributed.py:67 - the
+// reference itself moves fp32): the fc backward writes its gradient as bf16 into a symmetric bucket, the switch adds
+// the ranks' values in fp32 (multimem.ld_reduce ... acc::f32 ... bf16x2), and the 1/world scale, the SGD update of the
+// fp32 master weights and the multicast of the new WEIGHTS are the epilogue of the same pass.  Half the gradient
+// bytes on the wire and in HBM; the weights stay fp32 everywhere.  Few fat CTAs that own their SMs, like
+// allreduce_nvls_f32_excl_kernel.
+__global__ void __launch_bounds__(1024, 1)
+allreduce_nvls_bf16_sgd_excl_kernel(Peers P, Peers Wp, size_t n8, float scale, float lr, uint32_t epoch) {
+  const int r = P.rank, n = P.world;
+  const size_t per = (n8 + n - 1) / n;
+  const size_t lo = per * r, hi = min(n8, lo + per);
+  const uint4* src = reinterpret_cast<const uint4*>(P.mc);
+  float4* wdst = reinterpret_cast<float4*>(Wp.mc);
+  const float4* wl = reinterpret_cast<const float4*>(Wp.ptr[r]);
+  const float a = -lr * scale;
+  sys_barrier(P, epoch);
+  constexpr int U = 4;
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  size_t i = lo + (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  auto apply = [&](size_t idx, const uint4& v) {
+    const float4 w0 = wl[2 * idx], w1 = wl[2 * idx + 1];
+    mc_st_f32(wdst + 2 * idx, make_float4(fmaf(a, b2::bf16_lo(v.x), w0.x), fmaf(a, b2::bf16_hi(v.x), w0.y),
+                                          fmaf(a, b2::bf16_lo(v.y), w0.z), fmaf(a, b2::bf16_hi(v.y), w0.w)));
+    mc_st_f32(wdst + 2 * idx + 1, make_float4(fmaf(a, b2::bf16_lo(v.z), w1.x), fmaf(a, b2::bf16_hi(v.z), w1.y),
+                                              fmaf(a, b2::bf16_lo(v.w), w1.z), fmaf(a, b2::bf16_hi(v.w), w1.w)));
+  };
+  for (; i + (U - 1) * stride < hi; i += U * stride) {
+    uint4 v[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) v[u] = mc_ld_reduce_bf16(src + i + u * stride);
+#pragma unroll
+    for (int u = 0; u < U; ++u) apply(i + u * stride, v[u]);
+  }
+  for (; i < hi; i += stride) apply(i, mc_ld_reduce_bf16(src + i));
+  sys_barrier(P, epoch + 1);
+}
+
 // broadcast: every rank copies `bytes` (multiple of 16) from the root's symmetric buffer
 __global__ void __launch_bounds__(512)
 broadcast_kernel(Peers P, float4* __restrict__ out, size_t n16, int root, uint32_t epoch) {
@@ -701,6 +738,21 @@ B200_API int b200_ar_nvls_bf16(void* mc, void* const* flags, int rank, int world
   B200_CHECK(mc != nullptr && n % 8 == 0, "nvls_bf16: needs a multicast mapping and n %% 8 == 0");
   Peers P = make_peers(nullptr, flags, mc, rank, world);
   allreduce_nvls_bf16_kernel<<<blocks, 512, 0, (cudaStream_t)stream>>>(P, n / 8, scale, epoch);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+// bf16 gradient bucket (symmetric, multicast `mc`) -> fp32 weights (symmetric `wptrs`, multicast `wmc`):
+// weights -= lr * scale * sum_over_ranks(grad), written to every rank.  n = number of gradient elements (multiple of 8).
+B200_API int b200_ar_nvls_bf16_sgd(void* mc, void* const* flags, void* const* wptrs, void* wmc, int rank, int world,
+                                   size_t n, float scale, float lr, int blocks, uint32_t epoch, void* stream) {
+  B200_CHECK(mc != nullptr && wptrs != nullptr && wmc != nullptr, "nvls_bf16_sgd: needs multicast mappings of both buckets");
+  B200_CHECK(n % 8 == 0 && world <= kMaxRanks && blocks >= 1 && blocks <= kMaxBlocks, "nvls_bf16_sgd: bad n/world/blocks");
+  Peers P = make_peers(nullptr, flags, mc, rank, world);
+  Peers Wp = make_peers(wptrs, nullptr, wmc, rank, world);
+  B200_CUDA(set_max_smem(allreduce_nvls_bf16_sgd_excl_kernel, kExclusiveSmem));
+  allreduce_nvls_bf16_sgd_excl_kernel<<<blocks, 1024, kExclusiveSmem, (cudaStream_t)stream>>>(P, Wp, n / 8, scale, lr,
+                                                                                            epoch);
   B200_LAUNCH_CHECK();
   return 0;
 }

@@ -772,10 +772,15 @@ fc_bwd_kernel(const float* __restrict__ dl, const T* __restrict__ p2, float* W,
         g.z = fmaf(d[b][k], av[b][2], g.z); g.w = fmaf(d[b][k], av[b][3], g.w);
       }
       if (dW) {
-        float4* gp = reinterpret_cast<float4*>(dW + (size_t)k * F + 4 * j);
         float4 o = make_float4(g.x * gscale, g.y * gscale, g.z * gscale, g.w * gscale);
-        if (accumulate) { float4 prev = *gp; o.x += prev.x; o.y += prev.y; o.z += prev.z; o.w += prev.w; }
-        *gp = o;
+        if (accumulate == 2) {          // dW is a bf16 bucket (gradient exchange in bf16: half the bytes on the wire)
+          *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(dW) + (size_t)k * F + 4 * j) =
+              make_uint2(pack_bf16x2(o.x, o.y), pack_bf16x2(o.z, o.w));
+        } else {
+          float4* gp = reinterpret_cast<float4*>(dW + (size_t)k * F + 4 * j);
+          if (accumulate) { float4 prev = *gp; o.x += prev.x; o.y += prev.y; o.z += prev.z; o.w += prev.w; }
+          *gp = o;
+        }
       }
       if (lr != 0.f) {
         float4 o = make_float4(fmaf(-lr, g.x, w[k].x), fmaf(-lr, g.y, w[k].y),
@@ -821,7 +826,7 @@ template <typename T>
 __global__ void __launch_bounds__(256)
 fc_bwd_anybatch_kernel(const float* __restrict__ dl, const T* __restrict__ p2, float* W, float* dW,
                        T* __restrict__ dp2, int B, size_t F, float lr, float gscale,
-                       const float* __restrict__ bn2, float* __restrict__ bwd_partials) {
+                       const float* __restrict__ bn2, float* __restrict__ bwd_partials, int dw_bf16) {
   extern __shared__ float s_dl_dyn[];                  // [B][12]: ten dlogits per row, padded to 48 bytes
   __shared__ float s_bp[8][64];
   for (int i = threadIdx.x; i < B * kNC; i += 256) s_dl_dyn[(i / kNC) * 12 + (i % kNC)] = dl[i];
@@ -894,9 +899,14 @@ fc_bwd_anybatch_kernel(const float* __restrict__ dl, const T* __restrict__ p2, f
     }
 #pragma unroll
     for (int k = 0; k < kNC; ++k) {
-      if (dW)
-        *reinterpret_cast<float4*>(dW + (size_t)k * F + 4 * j) =
-            make_float4(g[k].x * gscale, g[k].y * gscale, g[k].z * gscale, g[k].w * gscale);
+      if (dW) {
+        if (dw_bf16)
+          *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(dW) + (size_t)k * F + 4 * j) =
+              make_uint2(pack_bf16x2(g[k].x * gscale, g[k].y * gscale), pack_bf16x2(g[k].z * gscale, g[k].w * gscale));
+        else
+          *reinterpret_cast<float4*>(dW + (size_t)k * F + 4 * j) =
+              make_float4(g[k].x * gscale, g[k].y * gscale, g[k].z * gscale, g[k].w * gscale);
+      }
       if (lr != 0.f)
         *reinterpret_cast<float4*>(W + (size_t)k * F + 4 * j) =
             make_float4(fmaf(-lr, g[k].x, w[k].x), fmaf(-lr, g[k].y, w[k].y), fmaf(-lr, g[k].z, w[k].z),
@@ -1243,11 +1253,12 @@ static int fc_bwd_t(const void* dlogits, const void* p2, void* W, void* dW, void
   cudaStream_t s = (cudaStream_t)stream;
   const int grid = b200_fc_grid();
   if (bt > 8) {          // any-batch kernel: one pass over W for the whole batch (no accumulate, no slab counters)
-    B200_CHECK(!accumulate && !ready, "fc_bwd: batches > 8 run in one pass (accumulate / slab counters do not apply)");
+    B200_CHECK(accumulate != 1 && !ready, "fc_bwd: batches > 8 run in one pass (accumulate / slab counters do not apply)");
     const size_t smem = (size_t)bt * 12 * sizeof(float);
     B200_CUDA(set_max_smem(fc_bwd_anybatch_kernel<T>, (int)smem));
     fc_bwd_anybatch_kernel<T><<<grid, 256, smem, s>>>((const float*)dlogits, (const T*)p2, (float*)W, (float*)dW, (T*)dp2,
-                                                     bt, F, lr, gscale, (const float*)bn2, (float*)bwd_partials);
+                                                     bt, F, lr, gscale, (const float*)bn2, (float*)bwd_partials,
+                                                     accumulate == 2 ? 1 : 0);
     B200_LAUNCH_CHECK();
     return 0;
   }

@@ -103,6 +103,8 @@ int b200_fc_fwd(const void* p2_bf16, const void* W, const void* bias, void* part
                 void* stream);
 int b200_cross_entropy(const void* logits, const void* labels_i64, int B, void* loss, void* dlogits, void* dbias,
                        float gscale, void* stream);
+/* accumulate: 0 = dW (fp32) overwritten, 1 = added to (batch chunks of the <= 8-row kernel), 2 = dW is a BF16 bucket
+ * [10][F], overwritten (DDP gradient exchange in bf16, b200_ar_nvls_bf16_sgd). */
 int b200_fc_bwd(const void* dlogits, const void* p2_bf16, void* W, void* dW_or_null, void* dp2_bf16, int bt, size_t F,
                 float lr_fused_sgd, int accumulate, float gscale, const void* bn2_or_null, void* bwd_partials_or_null,
                 void* stream);
@@ -211,6 +213,12 @@ int b200_ar_broadcast(void* const* ptrs, void* const* flags, int rank, int world
                       int blocks, uint32_t epoch, void* stream);
 int b200_ar_allgather(void* const* ptrs, void* const* flags, int rank, int world, void* out, size_t bytes, int blocks,
                       uint32_t epoch, void* stream);
+/* DDP bucket exchanged in bf16 (torch's bf16_compress_hook for the reference's DistributedDataParallel,
+ * mnist_distributed.py:67): `mc` = multicast address of the symmetric bf16 gradient bucket (b200_fc_bwd* writes it with
+ * accumulate = 2), `wptrs` / `wmc` = the fp32 master weights.  One pass: switch-side fp32 accumulation of the ranks'
+ * bf16 values, weights -= lr * scale * sum, new weights multicast to every rank.  n = gradient elements (multiple of 8). */
+int b200_ar_nvls_bf16_sgd(void* mc, void* const* flags, void* const* wptrs, void* wmc, int rank, int world, size_t n,
+                          float scale, float lr, int blocks, uint32_t epoch, void* stream);
 /* Small all-reduce through per-peer push rings (each rank writes its data + flag into every peer's slot; two ring
  * halves, no trailing barrier): the <= 64 KB path of SymmBackend.all_reduce. */
 int b200_ar_push(void* const* ptrs, void* const* flags, int rank, int world, const void* in, void* out, size_t n,

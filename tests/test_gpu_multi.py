@@ -138,8 +138,12 @@ def _ddp_engine(rank, world, port, out_path, env=None):
     g = torch.Generator().manual_seed(1234)
     xs = torch.rand(steps, world, B, 1, *shape, generator=g)
     ys = torch.randint(0, 10, (steps, world, B), generator=g)
+    fcw_after_first = None
     for s in range(steps):
         ddp.train_step(xs[s, rank].to(dev), ys[s, rank].to(dev))
+        if s == 0:
+            model.engine._sync_fc()                  # the bucket all-reduce of step 0 has updated fc.weight
+            fcw_after_first = model.engine.fcw.clone()
     torch.cuda.synchronize()
     sd = model.engine.state_dict()
     # every rank must hold bit-identical parameters (BatchNorm buffers are rank-local between a
@@ -156,6 +160,7 @@ def _ddp_engine(rank, world, port, out_path, env=None):
                 for _ in range(world)]
         for e in engs:
             e.load_state_dict(init_sd)
+        w0 = engs[0].fcw.clone()
         for s in range(steps):
             grads = []
             for r, e in enumerate(engs):
@@ -167,11 +172,25 @@ def _ddp_engine(rank, world, port, out_path, env=None):
             for e in engs:
                 e.small.add_(sm, alpha=-lr)
                 e.fcw.add_(fw, alpha=-lr)
+            if s == 0:
+                ref_after_first = engs[0].fcw.clone()
         ref = engs[0]
         e1 = float((model.engine.fcw - ref.fcw).norm() / ref.fcw.norm())
         e2 = float((model.engine.small - ref.small).norm() / ref.small.norm())
         print(f"[multi] DDP vs manual averaging: fc.weight {e1:.2e}, small {e2:.2e}", flush=True)
-        assert e1 < 1e-6 and e2 < 1e-5
+        bf16g = (env or {}).get("B200DP_GRAD_DTYPE") == "bf16"
+        if bf16g:      # the bucket really travelled as bf16 (no silent fp32 fallback): half the bytes, bf16-level error
+            assert ddp._engine_sync.describe()["gradient_exchange_dtype"] == "bf16"
+            assert model.engine.fcw_grad.dtype == torch.bfloat16 and ddp.bucket_sizes()[0] == 10 * model.engine.F * 2
+            # one step: pure rounding (each rank's gradient and their sum are rounded to bf16: <= 2 x 2^-9 of the update);
+            # three steps at this lr (each update is ~30 % of |W|): the perturbation feeds back through bf16 activations
+            e1s = float((fcw_after_first - ref_after_first).norm() / (ref_after_first - w0).norm())
+            e1u = float((model.engine.fcw - ref.fcw).norm() / (ref.fcw - w0).norm())
+            print(f"[multi] bf16 gradient exchange: fc.weight error / update size: {e1s:.2e} after one step, "
+                  f"{e1u:.2e} after three", flush=True)
+            assert 0.0 < e1s < 5e-3, f"bf16 gradient exchange, one step: {e1s:.3e} of the update"
+            assert e1u < 0.2, f"bf16 gradient exchange, three steps: {e1u:.3e} of the update (e1 {e1:.3e})"
+        assert (bf16g or e1 < 1e-6) and e2 < (0.2 if bf16g else 1e-5)      # bf16g: two trajectories, see above
         open(out_path, "w").write("ok")
     dist.barrier()
     dist.destroy_process_group()
@@ -183,7 +202,8 @@ def _ddp_engine(rank, world, port, out_path, env=None):
     {"B200DP_AR_START": "tile", "B200DP_AR_ALGO": "p2p"},         # same pipeline over plain peer loads / stores
     {"B200DP_AR_START": "pool"},                                  # whole-bucket two-shot after the pool backward
     {"B200DP_AR_START": "fc", "B200DP_AR_ALGO": "p2p"},
-], ids=["tiles-nvls", "tiles-p2p", "bucket-nvls", "bucket-p2p"])
+    {"B200DP_AR_START": "pool", "B200DP_GRAD_DTYPE": "bf16"},     # fc.weight gradient produced / exchanged as bf16 (NVLS)
+], ids=["tiles-nvls", "tiles-p2p", "bucket-nvls", "bucket-p2p", "bucket-nvls-bf16grad"])
 def test_ddp_engine_matches_manual_gradient_averaging(tmp_path, env):
     world = 2
     out = str(tmp_path / "ok")

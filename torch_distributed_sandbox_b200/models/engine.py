@@ -275,8 +275,9 @@ class FusedConvNet:
         """Gradients of the last backward in the reference's layouts (tests / generic DDP)."""
         out = OrderedDict((k, v.clone()) for k, v in self.grads.items())
         if self.fcw_grad is not None:
-            g = torch.empty_like(self.fcw_grad)
-            ops.fcw_permute(self.fcw_grad, g, 32, self.H // 4, self.W // 4, to_hwc=False)
+            src = self.fcw_grad.float() if self.fcw_grad.dtype != torch.float32 else self.fcw_grad   # bf16 DDP bucket
+            g = torch.empty_like(src)
+            ops.fcw_permute(src, g, 32, self.H // 4, self.W // 4, to_hwc=False)
             out["fc.weight"] = g
         return out
 
@@ -450,14 +451,20 @@ class FusedConvNet:
         if self.comm is not None:
             self._fc_pending = True
         elif not self._fc_fused_done:
+            self._sgd_fcw()
+
+    def _sgd_fcw(self) -> None:
+        if self.fcw_grad.dtype == torch.float32:
             ops.sgd(self.fcw, self.fcw_grad, self.lr)
+        else:                                              # bf16 gradient bucket without the fused all-reduce epilogue
+            self.fcw.add_(self.fcw_grad.float(), alpha=-self.lr)
 
     def _sync_fc(self) -> None:
         """Make fc.weight current (DDP: wait for the bucket all-reduce; apply SGD if it was not fused)."""
         if self._fc_pending:
             self._fc_pending = False
             if not self.comm.wait_fc_grad(self):
-                ops.sgd(self.fcw, self.fcw_grad, self.lr)
+                self._sgd_fcw()
 
     def train_step(self, images: torch.Tensor, labels: torch.Tensor) -> torch.Tensor:
         if not trace.nvtx_enabled():

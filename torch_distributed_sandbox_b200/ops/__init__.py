@@ -323,8 +323,14 @@ def fc_bwd(dlogits, p2_bf16, W, dW, dp2_bf16, lr=0.0, accumulate=False, gscale=1
     reductions are produced too (partials [fc_grid()][64]), replacing a pass over x2."""
     bt, F = p2_bf16.shape[0], p2_bf16[0].numel()
     assert p2_bf16.dtype == dp2_bf16.dtype
+    # dW mode of the C entry point: 0 = overwrite fp32, 1 = accumulate fp32, 2 = overwrite a bf16 bucket (DDP gradient
+    # exchange in bf16)
+    mode = 1 if accumulate else 0
+    if dW is not None and dW.dtype == torch.bfloat16:
+        assert not accumulate, "a bf16 gradient bucket is overwritten, never accumulated into"
+        mode = 2
     _native.check(_fn("b200_fc_bwd", p2_bf16)(_p(dlogits), _p(p2_bf16), _p(W), _p(dW), _p(dp2_bf16), bt, F, lr,
-                                              1 if accumulate else 0, gscale, _p(bn2), _p(bwd_partials), _stream()),
+                                              mode, gscale, _p(bn2), _p(bwd_partials), _stream()),
                   "fc_bwd")
     _count(1)
 

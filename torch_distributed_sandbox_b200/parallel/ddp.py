@@ -61,7 +61,8 @@ class DistributedDataParallel(nn.Module):
     def __init__(self, module: nn.Module, device_ids=None, output_device=None, dim: int = 0,
                  broadcast_buffers: bool = True, init_sync: bool = True, process_group=None,
                  bucket_cap_mb: Optional[float] = None, find_unused_parameters: bool = False,
-                 gradient_as_bucket_view: bool = False, static_graph: bool = False):
+                 gradient_as_bucket_view: bool = False, static_graph: bool = False,
+                 gradient_dtype: Optional[str] = None):
         super().__init__()
         if not dist.is_initialized():
             raise RuntimeError("DistributedDataParallel needs an initialised process group")
@@ -81,7 +82,7 @@ class DistributedDataParallel(nn.Module):
             from .engine_sync import EngineGradSync
             self._verify_shapes([("fc.weight", engine.fcw)] + list(engine.params.items()))
             self._engine_sync = EngineGradSync(engine, self.process_group, init_sync=init_sync,
-                                               broadcast_buffers=broadcast_buffers)
+                                               broadcast_buffers=broadcast_buffers, gradient_dtype=gradient_dtype)
             return
         self._params = [p for p in module.parameters() if p.requires_grad]
         if not self._params:

@@ -26,8 +26,15 @@ from ..utils import trace
 
 
 class EngineGradSync:
-    def __init__(self, engine, group, init_sync: bool = True, broadcast_buffers: bool = True):
+    def __init__(self, engine, group, init_sync: bool = True, broadcast_buffers: bool = True,
+                 gradient_dtype: str = None):
         self.engine, self.group = engine, group
+        # "bf16": the fc.weight gradient (99.99 % of the bytes) is produced, exchanged and reduced as bf16 - what torch's
+        # bf16_compress_hook does for DDP - with fp32 accumulation in the switch and the fp32 SGD update fused into the
+        # same pass.  Lower gradient precision than the reference's fp32 exchange: opt-in.
+        self.gradient_dtype = (gradient_dtype or os.environ.get("B200DP_GRAD_DTYPE", "fp32")).lower()
+        if self.gradient_dtype not in ("fp32", "bf16"):
+            raise ValueError(f"gradient_dtype must be 'fp32' or 'bf16', not {self.gradient_dtype!r}")
         self.backend = group.backend
         self.world = group.size()
         self.broadcast_buffers = broadcast_buffers
@@ -64,9 +71,15 @@ class EngineGradSync:
         if self.world > 1:
             n = 10 * engine.F
             with torch.cuda.device(engine.device):
-                grad = be.alloc_symmetric(n, torch.float32)
+                bn = be.alloc_symmetric(128, torch.float32, multicast=False)       # (first: brings the backend up)
+                if self.gradient_dtype == "bf16" and not (self.fuse_sgd and be.multicast and self.ar_start != "tile"
+                                                          and not self.onepass and n % 8 == 0):
+                    import warnings
+                    warnings.warn("b200dp: bf16 gradient exchange needs NVLS multicast and the fused SGD epilogue "
+                                  "(and neither the tile pipeline nor the one-pass kernel); exchanging fp32")
+                    self.gradient_dtype = "fp32"
+                grad = be.alloc_symmetric(n, torch.bfloat16 if self.gradient_dtype == "bf16" else torch.float32)
                 wsym = be.alloc_symmetric(n, torch.float32) if self.fuse_sgd else None
-                bn = be.alloc_symmetric(128, torch.float32, multicast=False)
                 sg = be.alloc_symmetric(engine.small_grad.numel(), torch.float32, multicast=False)
                 engine.rebind_storage(fcw=wsym, fcw_grad=grad, bn_flat=bn, small_grad=sg)
                 if self.ar_start == "tile" and self.fuse_sgd and engine.B <= 8:
@@ -117,14 +130,14 @@ class EngineGradSync:
             algo = ("nvls" if mc and self.algo not in ("p2p",) else "p2p") + f"(starts after {self.ar_start})"
         d.update({"fc_bucket_algo": (f"one-pass-{algo}" if (self.tile_ready is not None or self._onepass_ready is not None)
                                      else f"two-shot-{algo}"),
-                  "fused_sgd_in_allreduce": self.fuse_sgd,
+                  "fused_sgd_in_allreduce": self.fuse_sgd, "gradient_exchange_dtype": self.gradient_dtype,
                   "sm_partition": self.reserved_sms if algo == "nvls_excl" else 0,
                   "small_bucket_algo": "one-shot", "comm_blocks": self.blocks, "nccl_calls_on_grad_path": 0})
         return d
 
     def bucket_sizes(self) -> List[int]:
         from ..models.engine import SMALL_NUMEL
-        return [10 * self.engine.F * 4, SMALL_NUMEL * 4]
+        return [10 * self.engine.F * (2 if self.gradient_dtype == "bf16" else 4), SMALL_NUMEL * 4]
 
     # ------------------------------------------------------------ per step --
     def before_forward(self) -> None:
@@ -158,9 +171,13 @@ class EngineGradSync:
             return
         with torch.cuda.stream(self.comm_stream), trace.nvtx_range("b200dp.allreduce.fc_bucket"):
             self.comm_stream.wait_event(ready)
-            self.backend.all_reduce(engine.fcw_grad, dist.ReduceOp.SUM, channel=1, scale=1.0 / self.world,
-                                    sgd=(engine.fcw, engine.lr) if self.fuse_sgd else None, algo=self.algo,
-                                    blocks=self.blocks)
+            if self.gradient_dtype == "bf16":
+                self.backend.all_reduce_bf16_sgd(engine.fcw_grad, engine.fcw, engine.lr, 1.0 / self.world, channel=1,
+                                                 blocks=self.blocks)
+            else:
+                self.backend.all_reduce(engine.fcw_grad, dist.ReduceOp.SUM, channel=1, scale=1.0 / self.world,
+                                        sgd=(engine.fcw, engine.lr) if self.fuse_sgd else None, algo=self.algo,
+                                        blocks=self.blocks)
             self._fc_event = torch.cuda.Event()
             self._fc_event.record(self.comm_stream)
 

@@ -54,6 +54,8 @@ def _lib():
         lib.b200_ar_large_f32.argtypes = [PP, c_void_p, PP, PP, c_void_p, c_int, c_int, c_size_t, c_float, c_float,
                                           c_int, c_int, c_uint32, c_void_p]
         lib.b200_ar_nvls_bf16.argtypes = [c_void_p, PP, c_int, c_int, c_size_t, c_float, c_int, c_uint32, c_void_p]
+        lib.b200_ar_nvls_bf16_sgd.argtypes = [c_void_p, PP, PP, c_void_p, c_int, c_int, c_size_t, c_float, c_float,
+                                              c_int, c_uint32, c_void_p]
         lib.b200_ar_broadcast.argtypes = [PP, PP, c_int, c_int, c_void_p, c_size_t, c_int, c_int, c_uint32, c_void_p]
         lib.b200_ar_allgather.argtypes = [PP, PP, c_int, c_int, c_void_p, c_size_t, c_int, c_uint32, c_void_p]
         lib._b200_symm_bound = True
@@ -276,6 +278,26 @@ class SymmBackend:
         return max(1, min(64, (nbytes + (1 << 16) - 1) >> 16))
 
     # --------------------------------------------------------- collectives --
+    @_on_device
+    def all_reduce_bf16_sgd(self, grad_bf16: torch.Tensor, weights: torch.Tensor, lr: float, scale: float,
+                            channel: int = 1, blocks: int = 8):
+        """DDP bucket exchanged in bf16: ``weights -= lr * scale * sum_ranks(grad_bf16)`` on every rank in one pass
+        (switch-side fp32 accumulation of the bf16 values, SGD on the fp32 master weights, new weights multicast).
+        Both tensors must be symmetric with a multicast mapping (NVLS)."""
+        if self.size == 1:
+            weights.add_(grad_bf16.view_as(weights).float(), alpha=-float(lr) * scale)
+            return
+        self._ensure(grad_bf16)
+        g, w = self.lookup(grad_bf16.view(-1)), self.lookup(weights.view(-1))
+        if g is None or w is None or not g[0].mc or not w[0].mc:
+            raise RuntimeError("all_reduce_bf16_sgd needs both buckets in symmetric memory with NVLS multicast")
+        assert grad_bf16.dtype == torch.bfloat16 and weights.dtype == torch.float32
+        assert grad_bf16.numel() == weights.numel() and grad_bf16.numel() % 8 == 0 and g[1] % 16 == 0 and w[1] % 16 == 0
+        rc = _lib().b200_ar_nvls_bf16_sgd(g[0].mc + g[1], self._flag_arr[channel], w[0].ptr_array(w[1]), w[0].mc + w[1],
+                                          self.rank, self.size, grad_bf16.numel(), float(scale), float(lr), int(blocks),
+                                          self._next_epoch(channel), self._stream())
+        _native.check(rc, "all_reduce_bf16_sgd")
+
     @_on_device
     def all_reduce(self, t: torch.Tensor, op, channel: int = 0, sgd: Optional[Tuple[torch.Tensor, float]] = None,
                    scale: Optional[float] = None, algo: Optional[str] = None, blocks: Optional[int] = None):
