@@ -1392,30 +1392,33 @@ conv1_fwd_tc_kernel(const float* __restrict__ in, const float* __restrict__ w1, 
             if constexpr (POOL) {
               // second pass of the two-pass forward: the batch statistics are known (first pass), so BN + ReLU + the
               // 2x2 max-pool run here and the separate pass over the 2.88 GB conv output (K5) disappears.  The two
-              // rows of a window are this chunk's two rows, the two columns are this lane and its neighbour.
+              // rows of a window are this chunk's two rows, the two columns are this lane and its neighbour - and the
+              // two lanes SHARE the window's work: the even lane takes channels 0..7, the odd lane 8..15; each sends
+              // the other the half it does not keep (one shuffle per value instead of both lanes computing all 16).
               // amask (optional): one byte per pooled element = arg-max position (first maximum in row-major order,
               // as ATen picks it) | ReLU-active << 2 - all the backward needs to route dp1 without the conv output.
-              uint32_t pm[16], mb[4] = {0u, 0u, 0u, 0u};
+              const bool odd = lane & 1;
+              uint32_t pm[8], mb[2] = {0u, 0u};
 #pragma unroll
-              for (int c = 0; c < 16; ++c) {
-                const float sc = s_bn[c], sh = s_bn[16 + c];
-                const float y0 = fmaf(__uint_as_float(v[c]), sc, sh), y1 = fmaf(__uint_as_float(v[16 + c]), sc, sh);
-                const float n0 = __shfl_xor_sync(0xffffffffu, y0, 1), n1 = __shfl_xor_sync(0xffffffffu, y1, 1);
-                // on the even lane: y0 = (row 0, col 0), n0 = (row 0, col 1), y1 = (row 1, col 0), n1 = (row 1, col 1)
-                float best = y0;
-                uint32_t am = 0;
-                if (n0 > best) { best = n0; am = 1; }
-                if (y1 > best) { best = y1; am = 2; }
-                if (n1 > best) { best = n1; am = 3; }
-                pm[c] = __float_as_uint(fmaxf(best, 0.f));
-                mb[c >> 2] |= (am | (best > 0.f ? 4u : 0u)) << (8 * (c & 3));
+              for (int i = 0; i < 8; ++i) {
+                // v already holds conv + bias.  mine = my column, theirs = the neighbour's, channel c = 8 * odd + i
+                const float m0 = __uint_as_float(odd ? v[8 + i] : v[i]), m1 = __uint_as_float(odd ? v[24 + i] : v[16 + i]);
+                const float s0 = __uint_as_float(odd ? v[i] : v[8 + i]), s1 = __uint_as_float(odd ? v[16 + i] : v[24 + i]);
+                const float t0 = __shfl_xor_sync(0xffffffffu, s0, 1), t1 = __shfl_xor_sync(0xffffffffu, s1, 1);
+                const float sc = s_bn[(odd ? 8 : 0) + i], sh = s_bn[16 + (odd ? 8 : 0) + i];
+                const float ym0 = fmaf(m0, sc, sh), ym1 = fmaf(m1, sc, sh), yt0 = fmaf(t0, sc, sh), yt1 = fmaf(t1, sc, sh);
+                // window in row-major order: (row 0, left), (row 0, right), (row 1, left), (row 1, right); left = even lane
+                const float l0 = odd ? yt0 : ym0, r0 = odd ? ym0 : yt0, l1 = odd ? yt1 : ym1, r1 = odd ? ym1 : yt1;
+                const float a0 = fmaxf(l0, r0), a1 = fmaxf(l1, r1), best = fmaxf(a0, a1);
+                // a later candidate wins only if strictly greater
+                const uint32_t am = a1 > a0 ? (r1 > l1 ? 3u : 2u) : (r0 > l0 ? 1u : 0u);
+                pm[i] = __float_as_uint(fmaxf(best, 0.f));
+                mb[i >> 2] |= (am | (best > 0.f ? 4u : 0u)) << (8 * (i & 3));
               }
-              if (ok && !(lane & 1)) {
+              if (ok) {
                 const size_t pix = ((size_t)b * (g.H >> 1) + ((yb + (c0 >> 4)) >> 1)) * (g.W >> 1) + (x >> 1);
-                float* po = pooled + pix * 16;
-                st_global_v8(po, &pm[0]);
-                st_global_v8(po + 8, &pm[8]);
-                if (amask != nullptr) *reinterpret_cast<uint4*>(amask + pix * 16) = make_uint4(mb[0], mb[1], mb[2], mb[3]);
+                st_global_v8(pooled + pix * 16 + (odd ? 8 : 0), &pm[0]);      // the pair writes the pixel's 64 bytes
+                if (amask != nullptr) *reinterpret_cast<uint2*>(amask + pix * 16 + (odd ? 8 : 0)) = make_uint2(mb[0], mb[1]);
               }
             }
             if (k < 3) tmem_ld_wait();
