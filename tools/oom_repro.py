@@ -93,22 +93,27 @@ def try_engine(batch, steps=3, timeit=False, precision="bf16"):
 def main():
     total = torch.cuda.get_device_properties(0).total_memory
     log(f"device: {torch.cuda.get_device_name(0)}, {total / 2 ** 30:.1f} GiB")
+    only = os.environ.get("OOM_ONLY")          # "tf32": just the engine's tf32 rows (a cheap refresh of those lines)
     torch.cuda.set_per_process_memory_fraction(min(1.0, 24e9 / total), 0)
     log("== capped at 24 GB (the RTX A5000 of README.md:11)")
-    for b in (5, 10):
-        ok, peak = try_reference(b)
-        log(f"reference  batch {b:3d}: {'fits' if ok else 'OOM '}  peak {peak:5.1f} GiB")
-    for b in (5, 10, 20, 36):
-        ok, peak, _ = try_engine(b)
-        log(f"b200dp     batch {b:3d}: {'fits' if ok else 'OOM '}  peak {peak:5.1f} GiB")
+    if not only:
+        for b in (5, 10):
+            ok, peak = try_reference(b)
+            log(f"reference  batch {b:3d}: {'fits' if ok else 'OOM '}  peak {peak:5.1f} GiB")
+    for prec in (("bf16", "tf32") if not only else (only,)):
+        for b in (5, 10, 20, 36):
+            ok, peak, _ = try_engine(b, precision=prec)
+            log(f"b200dp {prec} batch {b:3d}: {'fits' if ok else 'OOM '}  peak {peak:5.1f} GiB")
     torch.cuda.set_per_process_memory_fraction(1.0, 0)
     log("== full device")
-    for b in (32, 48, 64):
-        ok, peak = try_reference(b, steps=1)
-        log(f"reference  batch {b:3d}: {'fits' if ok else 'OOM '}  peak {peak:5.1f} GiB")
-        if not ok:
-            break
-    for prec, batches in (("bf16", (64, 128, 256, 288)), ("tf32", (64, 128, 256, 288))):
+    if not only:
+        for b in (32, 48, 64):
+            ok, peak = try_reference(b, steps=1)
+            log(f"reference  batch {b:3d}: {'fits' if ok else 'OOM '}  peak {peak:5.1f} GiB")
+            if not ok:
+                break
+    for prec, batches in ((("bf16", (64, 128, 256, 288)), ("tf32", (64, 128, 256, 288))) if not only
+                          else ((only, (64, 128, 256, 288)),)):
         for b in batches:
             ok, peak, ms = try_engine(b, timeit=True, precision=prec)
             log(f"b200dp {prec} batch {b:3d}: {'fits' if ok else 'OOM '}  peak {peak:5.1f} GiB" +
