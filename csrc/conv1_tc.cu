@@ -959,34 +959,37 @@ conv1_wgrad_nox1_tf32_kernel(const __grid_constant__ CUtensorMap tm_dp1, const _
   if (warp == 0) { __syncwarp(); tmem_dealloc<256>(tmem_base); }
 }
 
-// dW1 = gscale * (routed + ca * S + cb * (w1 . M + b1 * S)), from the fp64-reduced partial rows
-__global__ void conv1_wgrad_nox1_combine_kernel(const float* __restrict__ partials, int nparts,
-                                                const float* __restrict__ w1, const float* __restrict__ b1,
-                                                const float* __restrict__ bn, const float* __restrict__ red,
-                                                float* __restrict__ dw1, float gscale) {
-  __shared__ double s_red[tn::kPartial];
-  for (int t = threadIdx.x; t < tn::kPartial; t += blockDim.x) {
-    // four independent chains: the 148 loads of a column are otherwise one dependent sequence (this launch took 32 us)
-    double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
-    int i = 0;
-    for (; i + 4 <= nparts; i += 4) {
-      a0 += (double)partials[(size_t)i * tn::kPartial + t];
-      a1 += (double)partials[(size_t)(i + 1) * tn::kPartial + t];
-      a2 += (double)partials[(size_t)(i + 2) * tn::kPartial + t];
-      a3 += (double)partials[(size_t)(i + 3) * tn::kPartial + t];
-    }
-    for (; i < nparts; ++i) a0 += (double)partials[(size_t)i * tn::kPartial + t];
-    s_red[t] = (a0 + a1) + (a2 + a3);
-  }
+// dW1 = gscale * (routed + ca * S + cb * (w1 . M + b1 * S)), from the fp64-reduced partial rows.
+// One block per tap: the 16 outputs of a tap need 42 column sums of the partial matrix (16 routed, column `tap` of the
+// 25x25 Gram matrix, S[tap]) and nothing else, so 25 blocks reduce disjoint columns - eight threads per column, every
+// load of a thread independent of the others (one block walking the 148 rows of all 1050 columns took 32 us, all of it
+// load latency).
+__global__ void __launch_bounds__(384)
+conv1_wgrad_nox1_combine_kernel(const float* __restrict__ partials, int nparts,
+                                const float* __restrict__ w1, const float* __restrict__ b1,
+                                const float* __restrict__ bn, const float* __restrict__ red,
+                                float* __restrict__ dw1, float gscale) {
+  __shared__ double s_col[48];
+  const int tap = blockIdx.x;
+  const int j = threadIdx.x >> 3, part = threadIdx.x & 7;
+  const bool valid = j < 42;
+  const int idx = j < 16 ? j * 25 + tap : (j < 41 ? 400 + (j - 16) * 25 + tap : 1025 + tap);
+  double a = 0.0;
+  if (valid)
+    for (int i = part; i < nparts; i += 8) a += (double)partials[(size_t)i * tn::kPartial + idx];
+  a += __shfl_xor_sync(0xffffffffu, a, 1);                   // (every lane takes part: j >= 42 carries zeros)
+  a += __shfl_xor_sync(0xffffffffu, a, 2);
+  a += __shfl_xor_sync(0xffffffffu, a, 4);
+  if (valid && part == 0) s_col[j] = a;
   __syncthreads();
-  for (int t = threadIdx.x; t < 400; t += blockDim.x) {
-    const int c = t / 25, tap = t % 25;
+  if (threadIdx.x < kC1) {
+    const int c = threadIdx.x;
     const double sc = bn[c], mu = bn[2 * kC1 + c], rs = bn[3 * kC1 + c], mdy = red[c], mdyx = red[kC1 + c];
     const double ca = sc * (rs * mdyx * mu - mdy), cb = -sc * rs * mdyx;
-    const double S = s_red[1025 + tap];
+    const double S = s_col[41];
     double R = (double)b1[c] * S;
-    for (int t1 = 0; t1 < 25; ++t1) R += (double)w1[c * 25 + t1] * s_red[400 + t1 * 25 + tap];
-    dw1[t] = (float)((double)gscale * (s_red[t] + ca * S + cb * R));
+    for (int t1 = 0; t1 < 25; ++t1) R += (double)w1[c * 25 + t1] * s_col[16 + t1];
+    dw1[c * 25 + tap] = (float)((double)gscale * (s_col[c] + ca * S + cb * R));
   }
 }
 
@@ -1145,7 +1148,7 @@ B200_API int b200_conv1_wgrad_nox1_f32(const void* in_f32, const void* dp1, cons
   B200_CUDA(set_max_smem(conv1_wgrad_nox1_tf32_kernel, tn::kSmemBytes));
   conv1_wgrad_nox1_tf32_kernel<<<grid, tn::kThreads, tn::kSmemBytes, s>>>(tg, tmk, ti, (const float*)bn, (float*)partials, g);
   B200_LAUNCH_CHECK();
-  conv1_wgrad_nox1_combine_kernel<<<1, 512, 0, s>>>((const float*)partials, grid, (const float*)w1, (const float*)b1,
+  conv1_wgrad_nox1_combine_kernel<<<25, 384, 0, s>>>((const float*)partials, grid, (const float*)w1, (const float*)b1,
                                                     (const float*)bn, (const float*)red, (float*)dw1, gscale);
   B200_LAUNCH_CHECK();
   return 0;
