@@ -36,8 +36,9 @@ def train(gpu, args):
     batch_size = args.batch_size                    # per GPU: effective batch = batch_size * world_size
     if args.model == "fused":
         from torch_distributed_sandbox_b200.models.module import FusedModule
-        model = FusedModule(args.image_shape, batch_size=batch_size, device=torch.device("cuda", gpu), lr=1e-4, seed=0)
-        model = DistributedDataParallel(model, device_ids=[gpu])
+        model = FusedModule(args.image_shape, batch_size=batch_size, device=torch.device("cuda", gpu), lr=1e-4, seed=0,
+                            precision=args.precision)
+        model = DistributedDataParallel(model, device_ids=[gpu], gradient_dtype=args.grad_dtype)
         criterion = optimizer = None
     else:
         from torch_distributed_sandbox_b200.models import reference_init
@@ -96,6 +97,12 @@ def parse(argv=None):
                              "else 60000 generated digits)")
     parser.add_argument("--max-steps", default=None, type=int)
     parser.add_argument("--log-every", default=100, type=int)
+    parser.add_argument("--grad-dtype", default="fp32", choices=["fp32", "bf16"],
+                        help="fused model: dtype of the fc.weight gradient exchange (bf16 = half the all-reduce bytes, "
+                             "fp32 accumulation in the switch; like torch DDP's bf16_compress_hook)")
+    parser.add_argument("--precision", default="tf32", choices=["tf32", "bf16"],
+                        help="fused model: tf32 = fp32 storage + TF32 conv math (the reference's numerics, default); "
+                             "bf16 = bf16 activations/gradients (faster, lower precision)")
     parser.add_argument("--save", default=None)
     args = parser.parse_args(argv)
     args.world_size = args.gpus * args.nodes

@@ -25,7 +25,8 @@ def train(gpu, args):
     torch.manual_seed(0)
     torch.cuda.set_device(gpu)
     batch_size = args.batch_size            # 5 in the reference (10 OOMs a 24 GB card: mnist_onegpu.py:44-45)
-    model = FusedModule(args.image_shape, batch_size=batch_size, device=torch.device("cuda", gpu), lr=1e-4, seed=0)
+    model = FusedModule(args.image_shape, batch_size=batch_size, device=torch.device("cuda", gpu), lr=1e-4, seed=0,
+                            precision=args.precision)
     dataset = open_dataset(args.data, synthetic=args.synthetic, quiet=(gpu != 0))
     loader = DataLoader(dataset, batch_size=batch_size, shuffle=True, pin_memory=True)
     start = datetime.now()
@@ -58,6 +59,9 @@ def parse(argv=None):
                              "else 60000 generated digits)")
     parser.add_argument("--max-steps", default=None, type=int)
     parser.add_argument("--log-every", default=100, type=int)
+    parser.add_argument("--precision", default="tf32", choices=["tf32", "bf16"],
+                        help="fused model: tf32 = fp32 storage + TF32 conv math (the reference's numerics, default); "
+                             "bf16 = bf16 activations/gradients (faster, lower precision)")
     parser.add_argument("--save", default=None, help="write a torch state_dict checkpoint here")
     args = parser.parse_args(argv)
     return args
